@@ -1,0 +1,129 @@
+/* vitk.h — C ABI of libvitk.so: B200 (sm_100a) ViT embed + k-NN vote hot path.
+ *
+ * The reference (Gurinder-Vasanta/vit-research) is pure Python and has no FFI of its own; the
+ * de-facto boundary of this path is a handful of Python callables.  Each entry
+ * point below names the reference call it stands behind.  A maintainer binds this header with
+ * ctypes (INTEGRATION.md shows the stub); `vit-research_b200/_lib.py` is that binding.
+ *
+ * Conventions: every function returns 0 on success, non-zero on error (message via
+ * vitk_last_error); no C++ exceptions cross the ABI; device pointers are caller-owned
+ * (torch tensor .data_ptr()); the library owns only its weight copy, bank copy and workspace;
+ * calls are asynchronous on the given cudaStream_t (passed as void*) unless named *_host;
+ * one handle per (device, stream) user, not thread-safe per handle.  There is no CPU fallback:
+ * without a CUDA device every compute entry point fails.
+ */
+#ifndef VITK_H_
+#define VITK_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct vitk_ctx* vitk_handle;
+
+/* Model geometry.  Defaults of HF ViTConfig() == google/vit-base-patch16-224
+ * (nba_proj/ratt_write_clips_to_ragdb.py:58-60). Runtime, not compile-time. */
+typedef struct vitk_config {
+  int32_t image_h, image_w;   /* 224, 224 */
+  int32_t patch;              /* 16 */
+  int32_t channels;           /* 3 */
+  int32_t hidden;             /* 768  (ViT-L: 1024) */
+  int32_t heads;              /* 12   (ViT-L: 16); head dim must be 64 */
+  int32_t mlp;                /* 3072 (ViT-L: 4096) */
+  int32_t layers;             /* 12   (ViT-L: 24) */
+  float ln_eps;               /* HF 1e-12; TF Model Garden 1e-6 */
+  int32_t gelu_tanh;          /* 0: exact erf GELU (HF "gelu"); 1: tanh approximation (TF) */
+  int32_t max_batch;          /* frames per vitk_embed call the workspace is sized for */
+} vitk_config;
+
+enum { VITK_PIX_F32_NCHW = 0, VITK_PIX_BF16_NCHW = 1, VITK_PIX_U8_NHWC = 2 };
+enum { VITK_METRIC_COSINE = 0, VITK_METRIC_L2 = 1 };
+enum {
+  VITK_EPI_BIAS_BF16 = 0, VITK_EPI_BIAS_GELU_BF16 = 1, VITK_EPI_BIAS_GELUT_BF16 = 2,
+  VITK_EPI_BIAS_RESID_F32 = 3, VITK_EPI_TABLE_F32 = 4, VITK_EPI_F32 = 5
+};
+
+/* Library / build identification (no device needed). */
+const char* vitk_version(void);
+/* 1 if a CUDA device of compute capability 10.x is visible, else 0. */
+int vitk_device_ok(int device);
+
+/* ---- lifecycle ------------------------------------------------------------------------ */
+/* Stands behind `ViTModel.from_pretrained(...).to(device).eval()`
+ * (ratt_write_clips_to_ragdb.py:58-60). Allocates weights + workspace on `device`. */
+int vitk_create(const vitk_config* cfg, int device, vitk_handle* out);
+int vitk_destroy(vitk_handle h);
+const char* vitk_last_error(vitk_handle h); /* h may be NULL: last create error */
+
+/* Load one tensor by its HF ViTModel state-dict key (e.g.
+ * "encoder.layer.0.attention.attention.query.weight"); host float32, row-major, shape checked.
+ * Stands behind `model.load_weights` / `from_pretrained` (write_embeddings.py:243, chroma.py:159).
+ * "pooler.*" keys are accepted and ignored (the reference never reads pooler_output). */
+int vitk_set_weight(vitk_handle h, const char* name, const float* host, const int64_t* shape,
+                    int ndim);
+/* Checks every tensor was supplied, builds the fused tables (pos-emb + conv bias / CLS row). */
+int vitk_finalize_weights(vitk_handle h);
+
+/* ---- embedding ------------------------------------------------------------------------ */
+/* Device-resident forward: pixels -> CLS embedding.  Stands behind
+ * `vit_model(pixel_values=...).last_hidden_state[:,0,:]` (+ the numpy row normalisation
+ * `cls / (norm + 1e-8)` when l2_normalise != 0) — ratt_write_clips_to_ragdb.py:146-153.
+ *   pixels_dev : VITK_PIX_F32_NCHW / BF16_NCHW: (n,C,H,W) already rescaled+normalised;
+ *                VITK_PIX_U8_NHWC: (n,H,W,C) raw uint8, the HF processor's rescale (1/255) and
+ *                normalise ((x-.5)/.5) are applied on the fly (image_processing_vit.py:20-27).
+ *   emb_f32_dev: (n, hidden) float32 out.  emb_bf16_dev: optional (n, hidden) bf16 out or NULL. */
+int vitk_embed(vitk_handle h, const void* pixels_dev, int pixel_format, int n, float* emb_f32_dev,
+               void* emb_bf16_dev, int l2_normalise, void* stream);
+
+/* Host-buffer convenience used by `hf_vit_embed_batch(frames_np)`
+ * (ratt_write_clips_to_ragdb.py:135-159): H2D copy, forward in max_batch chunks, D2H copy,
+ * synchronous.  frames_host: (n,H,W,C) uint8 (pinned or pageable). emb_host: (n, hidden) f32. */
+int vitk_embed_host_u8(vitk_handle h, const uint8_t* frames_host, int n, float* emb_host,
+                       int l2_normalise);
+
+/* ---- banks + k-NN vote ---------------------------------------------------------------- */
+/* Replicated embedding bank.  Stands behind np.load('*_embeddings.npz') + the Chroma bank
+ * build (clustering.py:26-36, write_per_vid_embeddings_chroma.py:229-265).
+ * rows_host (m,d) f32; labels_host (m) int32 in [0,n_classes) or NULL; normalise_rows != 0
+ * applies b / (||b|| + 1e-8) (ratt_chunk_retriever.py:116). */
+int vitk_bank_set(vitk_handle h, const float* rows_host, int m, int d, const int32_t* labels_host,
+                  int n_classes, int normalise_rows);
+
+/* Top-k + vote.  Stands behind `collection.query(query_embeddings, n_results=k)`
+ * (chroma.py:211-214; 'l2' space = squared L2 ascending) / RattChunkRetriever's
+ * `sims = Q @ C.T; argpartition; argsort` (ratt_chunk_retriever.py:123,144-148; cosine
+ * descending) followed by determine_class_pass2 (chroma.py:102-134).
+ *   q_dev (n,d) f32; normalise_queries: q / (||q|| + 1e-8) first.
+ *   idx_out (n,k) int32 bank rows in result order; score_out (n,k) f32 (cosine similarity, or
+ *   squared L2 distance); label_out (n) int32 (first-max of counts); counts_out (n,n_classes).
+ *   Any out pointer except idx_out/score_out may be NULL.  k <= 64. */
+int vitk_knn_vote(vitk_handle h, const float* q_dev, int n, int k, int metric,
+                  int normalise_queries, int32_t* idx_out, float* score_out, int32_t* label_out,
+                  int32_t* counts_out, void* stream);
+
+/* ---- operator-level entry points (used by the parity tests, one kernel each) ----------- */
+/* C[M,N] = A[M,K] (bf16) · W[N,K]^T (bf16) with epilogue `epi` (VITK_EPI_*).
+ * out is bf16 for the *_BF16 epilogues, f32 otherwise (row pitch = N elements). */
+int vitk_op_gemm(const void* a_bf16_dev, const void* w_bf16_dev, void* out_dev, int M, int N, int K,
+                 int epi, const float* bias_dev, const float* resid_dev, const float* table_dev,
+                 int table_rows, void* stream);
+/* y(bf16) = LayerNorm(x f32) over the last dim d (d in {768, 1024}). */
+int vitk_op_layernorm(const float* x_dev, const float* gamma_dev, const float* beta_dev,
+                      void* y_bf16_dev, int rows, int d, float eps, void* stream);
+/* out[frames,S,heads*64] (bf16) = softmax(q k^T / 8) v from qkv[frames,S,3*heads*64] (bf16). */
+int vitk_op_attention(const void* qkv_bf16_dev, void* out_bf16_dev, int frames, int S, int heads,
+                      void* stream);
+/* im2col + pixel-format conversion: out bf16 [n*(P+1), C*patch*patch] with a zero CLS row. */
+int vitk_op_patchify(const void* pixels_dev, int pixel_format, void* out_bf16_dev, int n, int C,
+                     int H, int W, int patch, void* stream);
+
+/* Kernel launches issued by this handle since creation (bench.py's gpu_launches). */
+int64_t vitk_launch_count(vitk_handle h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VITK_H_ */

@@ -1,0 +1,10 @@
+"""vit-research_b200 — B200-native ViT embed + k-NN vote hot path of Gurinder-Vasanta/vit-research.
+
+Import as `vit_research_b200` (the hyphenated directory is exposed by the shim package of that
+name at the repo root).  See DESIGN.md for the path, its boundary and the kernels.
+"""
+from ._lib import VitkError, build, load  # noqa: F401
+from .embed import (ViTEmbedder, ViTGeometry, extract_embeddings, hf_vit_embed_batch,  # noqa: F401
+                    install)
+from .knn import (BankCollection, BankIndex, RattChunkRetriever, determine_class_pass1,  # noqa: F401
+                  determine_class_pass2, load_label_banks, temp_smax, LABEL_NAMES)

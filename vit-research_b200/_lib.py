@@ -1,0 +1,139 @@
+"""ctypes binding of libvitk.so (include/vitk.h) + the in-tree nvcc build.
+
+This is the binding a maintainer of the reference would add: the reference is
+pure Python, so the FFI is ctypes over a C ABI with plain pointers and sizes.  There is no CPU
+fallback: if the shared library is missing or no sm_100 GPU is visible, the compute entry points
+raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import shutil
+import subprocess
+from pathlib import Path
+
+PKG_DIR = Path(__file__).resolve().parent
+CSRC = PKG_DIR / "csrc"
+LIB_PATH = PKG_DIR / "libvitk.so"
+INCLUDE = PKG_DIR.parent / "include"
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+    "--shared", "-Xcompiler", "-fPIC",
+]
+
+
+class VitkError(RuntimeError):
+    pass
+
+
+class VitkConfig(C.Structure):
+    _fields_ = [
+        ("image_h", C.c_int32), ("image_w", C.c_int32), ("patch", C.c_int32),
+        ("channels", C.c_int32), ("hidden", C.c_int32), ("heads", C.c_int32),
+        ("mlp", C.c_int32), ("layers", C.c_int32), ("ln_eps", C.c_float),
+        ("gelu_tanh", C.c_int32), ("max_batch", C.c_int32),
+    ]
+
+
+PIX_F32_NCHW, PIX_BF16_NCHW, PIX_U8_NHWC = 0, 1, 2
+METRIC_COSINE, METRIC_L2 = 0, 1
+EPI_BIAS_BF16, EPI_BIAS_GELU_BF16, EPI_BIAS_GELUT_BF16 = 0, 1, 2
+EPI_BIAS_RESID_F32, EPI_TABLE_F32, EPI_F32 = 3, 4, 5
+
+# name -> (restype, argtypes); every symbol include/vitk.h declares
+_vp, _i, _f = C.c_void_p, C.c_int, C.c_float
+SIGNATURES = {
+    "vitk_version": (C.c_char_p, []),
+    "vitk_device_ok": (_i, [_i]),
+    "vitk_create": (_i, [C.POINTER(VitkConfig), _i, C.POINTER(_vp)]),
+    "vitk_destroy": (_i, [_vp]),
+    "vitk_last_error": (C.c_char_p, [_vp]),
+    "vitk_set_weight": (_i, [_vp, C.c_char_p, _vp, C.POINTER(C.c_int64), _i]),
+    "vitk_finalize_weights": (_i, [_vp]),
+    "vitk_embed": (_i, [_vp, _vp, _i, _i, _vp, _vp, _i, _vp]),
+    "vitk_embed_host_u8": (_i, [_vp, _vp, _i, _vp, _i]),
+    "vitk_bank_set": (_i, [_vp, _vp, _i, _i, _vp, _i, _i]),
+    "vitk_knn_vote": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
+    "vitk_op_gemm": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _i, _vp]),
+    "vitk_op_layernorm": (_i, [_vp, _vp, _vp, _vp, _i, _i, _f, _vp]),
+    "vitk_op_attention": (_i, [_vp, _vp, _i, _i, _i, _vp]),
+    "vitk_op_patchify": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp]),
+    "vitk_launch_count": (C.c_int64, [_vp]),
+}
+
+
+def sources() -> list[Path]:
+    return sorted(CSRC.glob("*.cu")) + sorted(CSRC.glob("*.cuh")) + [INCLUDE / "vitk.h"]
+
+
+def needs_build() -> bool:
+    if not LIB_PATH.exists():
+        return True
+    t = LIB_PATH.stat().st_mtime
+    return any(s.stat().st_mtime > t for s in sources())
+
+
+def build(force: bool = False, verbose: bool = False) -> Path:
+    """Compile csrc/*.cu for sm_100a into libvitk.so next to this file (nvcc cross-compiles
+    without a GPU)."""
+    if not force and not needs_build():
+        return LIB_PATH
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(nvcc):
+        raise VitkError("nvcc not found: cannot build libvitk.so")
+    tmp = LIB_PATH.with_suffix(".so.tmp%d" % os.getpid())
+    cmd = [nvcc, *NVCC_FLAGS, "-o", str(tmp), str(CSRC / "vitk_api.cu")]
+    if verbose:
+        cmd.insert(1, "-Xptxas=-v")
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise VitkError("nvcc failed:\n" + r.stdout + r.stderr)
+    if verbose:
+        print(r.stderr)
+    os.replace(tmp, LIB_PATH)
+    return LIB_PATH
+
+
+_lib = None
+
+
+def load(auto_build: bool = True):
+    """dlopen libvitk.so and attach the prototypes.  Raises if it cannot be built/loaded."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if auto_build and needs_build():
+        build()
+    if not LIB_PATH.exists():
+        raise VitkError(f"{LIB_PATH} is missing (run __graft_entry__.build()); no CPU fallback")
+    lib = C.CDLL(str(LIB_PATH))
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is not exported
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc: int, handle=None, what: str = "vitk"):
+    if rc != 0:
+        msg = load().vitk_last_error(handle)
+        raise VitkError(f"{what} failed: {msg.decode() if msg else 'unknown error'}")
+
+
+def ptr(t):
+    """Device/host pointer of a torch tensor or numpy array (None -> NULL)."""
+    if t is None:
+        return None
+    if hasattr(t, "data_ptr"):
+        return C.c_void_p(t.data_ptr())
+    return C.c_void_p(t.ctypes.data)
+
+
+def stream_ptr(stream=None):
+    import torch
+
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return C.c_void_p(s.cuda_stream)

@@ -1,0 +1,853 @@
+// vitk_api.cu — C ABI (include/vitk.h) over the sm_100a kernels: handle, weights, workspace,
+// TMA tensor maps, launch orchestration of the ViT forward and the k-NN vote.
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <set>
+#include <string>
+#include <vector>
+
+#include "../../include/vitk.h"
+#include "attention_sm100.cuh"
+#include "elementwise.cuh"
+#include "gemm_sm100.cuh"
+#include "knn.cuh"
+
+using namespace vitk;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct Err {
+  std::string msg;
+  void set(const char* fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    msg = buf;
+  }
+};
+
+#define CK(e, call)                                                                        \
+  do {                                                                                     \
+    cudaError_t _s = (call);                                                               \
+    if (_s != cudaSuccess) {                                                               \
+      (e).set("%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(_s));        \
+      return 1;                                                                            \
+    }                                                                                      \
+  } while (0)
+
+// ------------------------------------------------------------------------------------------
+// TMA tensor maps (driver entry point resolved at run time: the .so links only libcudart)
+// ------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) ==
+            cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// rank-2 or rank-3 row-major tensor, innermost dim contiguous, 128B swizzle, zero OOB fill.
+// dims/box are innermost-first. strides_bytes has rank-1 entries (dims 1..rank-1).
+int make_tmap(Err& e, CUtensorMap* m, CUtensorMapDataType dt, int rank, void* base,
+              const uint64_t* dims, const uint64_t* strides_bytes, const uint32_t* box) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) {
+    e.set("cuTensorMapEncodeTiled entry point unavailable (no CUDA driver?)");
+    return 1;
+  }
+  cuuint64_t gd[5];
+  cuuint64_t gs[5];
+  cuuint32_t bx[5], es[5];
+  for (int i = 0; i < rank; ++i) {
+    gd[i] = dims[i];
+    bx[i] = box[i];
+    es[i] = 1;
+  }
+  for (int i = 0; i < rank - 1; ++i) gs[i] = strides_bytes[i];
+  CUresult r = fn(m, dt, (cuuint32_t)rank, base, gd, gs, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    e.set("cuTensorMapEncodeTiled failed (%d): rank %d dims [%llu,%llu,%llu] box [%u,%u,%u]",
+          (int)r, rank, (unsigned long long)dims[0], (unsigned long long)(rank > 1 ? dims[1] : 0),
+          (unsigned long long)(rank > 2 ? dims[2] : 0), box[0], rank > 1 ? box[1] : 0,
+          rank > 2 ? box[2] : 0);
+    return 1;
+  }
+  return 0;
+}
+
+// [rows, cols] bf16 row-major operand (A or W): box {64, box_rows}
+int tmap_operand(Err& e, CUtensorMap* m, const void* base, int rows, int cols, int box_rows) {
+  uint64_t dims[2] = {(uint64_t)cols, (uint64_t)rows};
+  uint64_t str[1] = {(uint64_t)cols * 2};
+  uint32_t box[2] = {64u, (uint32_t)box_rows};
+  return make_tmap(e, m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, str,
+                   box);
+}
+// [rows, cols] output: 32-row boxes, 128 B wide (64 bf16 / 32 f32)
+int tmap_output(Err& e, CUtensorMap* m, void* base, int rows, int cols, bool bf16) {
+  uint64_t dims[2] = {(uint64_t)cols, (uint64_t)rows};
+  uint64_t str[1] = {(uint64_t)cols * (bf16 ? 2u : 4u)};
+  uint32_t box[2] = {bf16 ? 64u : 32u, 32u};
+  return make_tmap(e, m, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32,
+                   2, base, dims, str, box);
+}
+// [frames, S, cols] bf16: box {64, box_rows, 1}
+int tmap_tokens(Err& e, CUtensorMap* m, const void* base, int frames, int S, int cols,
+                int box_rows) {
+  uint64_t dims[3] = {(uint64_t)cols, (uint64_t)S, (uint64_t)frames};
+  uint64_t str[2] = {(uint64_t)cols * 2, (uint64_t)S * cols * 2};
+  uint32_t box[3] = {64u, (uint32_t)box_rows, 1u};
+  return make_tmap(e, m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, str,
+                   box);
+}
+
+// ------------------------------------------------------------------------------------------
+// launchers
+// ------------------------------------------------------------------------------------------
+int g_num_sms = 0;
+int num_sms() {
+  if (!g_num_sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (g_num_sms <= 0) g_num_sms = 148;
+  }
+  return g_num_sms;
+}
+
+template <int BN, int EPI>
+int launch_gemm_t(Err& e, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& c,
+                  const GemmParams& p, cudaStream_t st) {
+  auto kern = gemm_bf16_tn_kernel<BN, EPI>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    CK(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               GemmCfg<BN>::kSmemBytes));
+    attr_set = true;
+  }
+  const int m_tiles = (p.M + GEMM_BM - 1) / GEMM_BM, n_tiles = (p.N + BN - 1) / BN;
+  const int tiles = m_tiles * n_tiles;
+  const int grid = tiles < num_sms() ? tiles : num_sms();
+  kern<<<grid, GEMM_THREADS, GemmCfg<BN>::kSmemBytes, st>>>(a, b, c, p);
+  CK(e, cudaGetLastError());
+  return 0;
+}
+
+int launch_gemm(Err& e, int epi, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& c,
+                const GemmParams& p, cudaStream_t st) {
+  if (p.K % GEMM_BK != 0 || p.K <= 0) {
+    e.set("gemm: K=%d must be a positive multiple of %d", p.K, GEMM_BK);
+    return 1;
+  }
+  switch (epi) {
+    case EPI_BIAS_BF16: return launch_gemm_t<256, EPI_BIAS_BF16>(e, a, b, c, p, st);
+    case EPI_BIAS_GELU_BF16: return launch_gemm_t<256, EPI_BIAS_GELU_BF16>(e, a, b, c, p, st);
+    case EPI_BIAS_GELUT_BF16: return launch_gemm_t<256, EPI_BIAS_GELUT_BF16>(e, a, b, c, p, st);
+    case EPI_BIAS_RESID_F32: return launch_gemm_t<256, EPI_BIAS_RESID_F32>(e, a, b, c, p, st);
+    case EPI_TABLE_F32: return launch_gemm_t<256, EPI_TABLE_F32>(e, a, b, c, p, st);
+    case EPI_F32: return launch_gemm_t<256, EPI_F32>(e, a, b, c, p, st);
+  }
+  e.set("gemm: unknown epilogue %d", epi);
+  return 1;
+}
+
+int launch_attention(Err& e, const CUtensorMap& tq, const CUtensorMap& tkv, const CUtensorMap& to,
+                     int frames, int S, int heads, cudaStream_t st) {
+  if (S < 1 || S > 256) {
+    e.set("attention: S=%d unsupported (1..256)", S);
+    return 1;
+  }
+  const AttnSmemLayout L = attn_smem_layout(S);
+  static int attr_bytes = 0;
+  if (L.total > attr_bytes) {
+    CK(e, cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               L.total));
+    attr_bytes = L.total;
+  }
+  AttnParams p;
+  p.S = S;
+  p.heads = heads;
+  p.frames = frames;
+  p.scale_log2e = 0.125f * 1.4426950408889634f;  // head dim 64 -> 1/sqrt(64)
+  attention_kernel<<<frames * heads, ATT_THREADS, L.total, st>>>(tq, tkv, to, p);
+  CK(e, cudaGetLastError());
+  return 0;
+}
+
+int launch_layernorm(Err& e, const float* x, const float* g, const float* b, __nv_bfloat16* y,
+                     int rows, int d, float eps, cudaStream_t st) {
+  const int blocks = (rows + 7) / 8;
+  if (d == 768)
+    layernorm_bf16_kernel<6><<<blocks, 256, 0, st>>>(x, g, b, y, rows, eps);
+  else if (d == 1024)
+    layernorm_bf16_kernel<8><<<blocks, 256, 0, st>>>(x, g, b, y, rows, eps);
+  else {
+    e.set("layernorm: hidden=%d unsupported (768 or 1024)", d);
+    return 1;
+  }
+  CK(e, cudaGetLastError());
+  return 0;
+}
+
+int launch_patchify(Err& e, const void* pix, int fmt, __nv_bfloat16* out, int n, int C, int H,
+                    int W, int ps, cudaStream_t st) {
+  if (ps % 8 != 0 || H % ps != 0 || W % ps != 0) {
+    e.set("patchify: patch %d must be a multiple of 8 dividing %dx%d", ps, H, W);
+    return 1;
+  }
+  if (fmt < 0 || fmt > 2) {
+    e.set("patchify: unknown pixel format %d", fmt);
+    return 1;
+  }
+  PatchifyParams p;
+  p.pix = pix;
+  p.out = out;
+  p.n = n; p.C = C; p.H = H; p.W = W; p.ps = ps;
+  p.gh = H / ps; p.gw = W / ps;
+  p.K = C * ps * ps;
+  p.fmt = fmt;
+  p.scale = 1.0f / 255.0f;  // HF ViTImageProcessor: rescale_factor 1/255, mean .5, std .5
+  p.mean = 0.5f;
+  p.inv_std = 2.0f;
+  long long total = (long long)n * (p.gh * p.gw + 1) * (p.K / 8);
+  long long blocks = (total + 255) / 256;
+  if (blocks > 148 * 32) blocks = 148 * 32;
+  patchify_kernel<<<(int)blocks, 256, 0, st>>>(p);
+  CK(e, cudaGetLastError());
+  return 0;
+}
+
+uint16_t f32_to_bf16_bits(float f) {
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return (uint16_t)((u >> 16) | 0x40);  // NaN
+  u += 0x7fffu + ((u >> 16) & 1u);  // round to nearest even
+  return (uint16_t)(u >> 16);
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------
+// handle
+// ------------------------------------------------------------------------------------------
+struct LayerW {
+  __nv_bfloat16 *w_qkv = nullptr, *w_o = nullptr, *w_fc1 = nullptr, *w_fc2 = nullptr;
+  float *b_qkv = nullptr, *b_o = nullptr, *b_fc1 = nullptr, *b_fc2 = nullptr;
+  float *ln1_g = nullptr, *ln1_b = nullptr, *ln2_g = nullptr, *ln2_b = nullptr;
+  CUtensorMap tm_qkv, tm_o, tm_fc1, tm_fc2;
+};
+
+struct BatchMaps {  // tensor maps that depend on the number of frames in the call
+  CUtensorMap a_patch, a_act, a_h;          // GEMM A operands
+  CUtensorMap c_resid, c_qkv, c_h;          // GEMM outputs
+  CUtensorMap att_q, att_kv, att_o;         // attention
+};
+
+struct vitk_ctx {
+  vitk_config cfg;
+  int device = 0;
+  int S = 0, P = 0, Kp = 0, D = 0, F = 0;
+  Err err;
+  std::vector<LayerW> layers;
+  __nv_bfloat16* w_patch = nullptr;
+  CUtensorMap tm_patch;
+  float *posb = nullptr, *lnf_g = nullptr, *lnf_b = nullptr;
+  std::vector<float> h_cls, h_pos, h_pbias;
+  std::set<std::string> have;
+  bool finalized = false;
+  // workspace
+  __nv_bfloat16 *act = nullptr, *qkv = nullptr, *hbuf = nullptr, *emb_bf16 = nullptr;
+  float *resid = nullptr, *emb = nullptr;
+  uint8_t* pix_stage = nullptr;  // device staging for vitk_embed_host_u8
+  std::map<int, BatchMaps> maps;
+  // bank
+  float *bank = nullptr, *bank_sqnorm = nullptr;
+  __nv_bfloat16* bank_bf16 = nullptr;
+  int32_t* bank_labels = nullptr;
+  int bank_m = 0, bank_d = 0, bank_classes = 0;
+  CUtensorMap tm_bank;
+  // knn workspace (grown on demand)
+  float *knn_q = nullptr, *knn_scores = nullptr;
+  __nv_bfloat16* knn_qb = nullptr;
+  int32_t* knn_cand = nullptr;
+  int knn_cap_q = 0, knn_cap_m = 0;
+  cudaStream_t own_stream = nullptr;
+  int64_t launches = 0;
+};
+
+namespace {
+
+template <typename T>
+int dev_alloc(Err& e, T** p, size_t count) {
+  CK(e, cudaMalloc(reinterpret_cast<void**>(p), count * sizeof(T)));
+  return 0;
+}
+
+int upload_bf16(Err& e, __nv_bfloat16* dst, const float* src, size_t count) {
+  std::vector<uint16_t> tmp(count);
+  for (size_t i = 0; i < count; ++i) tmp[i] = f32_to_bf16_bits(src[i]);
+  CK(e, cudaMemcpy(dst, tmp.data(), count * 2, cudaMemcpyHostToDevice));
+  return 0;
+}
+int upload_f32(Err& e, float* dst, const float* src, size_t count) {
+  CK(e, cudaMemcpy(dst, src, count * 4, cudaMemcpyHostToDevice));
+  return 0;
+}
+
+bool shape_is(const int64_t* shape, int ndim, std::initializer_list<int64_t> want) {
+  // compare after dropping leading 1s on both sides
+  std::vector<int64_t> a(shape, shape + ndim), b(want);
+  while (a.size() > 1 && a.front() == 1) a.erase(a.begin());
+  while (b.size() > 1 && b.front() == 1) b.erase(b.begin());
+  return a == b;
+}
+
+void free_ctx(vitk_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  for (auto& L : c->layers) {
+    cudaFree(L.w_qkv); cudaFree(L.w_o); cudaFree(L.w_fc1); cudaFree(L.w_fc2);
+    cudaFree(L.b_qkv); cudaFree(L.b_o); cudaFree(L.b_fc1); cudaFree(L.b_fc2);
+    cudaFree(L.ln1_g); cudaFree(L.ln1_b); cudaFree(L.ln2_g); cudaFree(L.ln2_b);
+  }
+  cudaFree(c->w_patch); cudaFree(c->posb); cudaFree(c->lnf_g); cudaFree(c->lnf_b);
+  cudaFree(c->act); cudaFree(c->qkv); cudaFree(c->hbuf); cudaFree(c->emb_bf16);
+  cudaFree(c->resid); cudaFree(c->emb); cudaFree(c->pix_stage);
+  cudaFree(c->bank); cudaFree(c->bank_sqnorm); cudaFree(c->bank_bf16); cudaFree(c->bank_labels);
+  cudaFree(c->knn_q); cudaFree(c->knn_scores); cudaFree(c->knn_qb); cudaFree(c->knn_cand);
+  if (c->own_stream) cudaStreamDestroy(c->own_stream);
+  delete c;
+}
+
+}  // namespace
+
+extern "C" const char* vitk_version(void) { return "vitk 0.1 (sm_100a, tcgen05/TMA)"; }
+
+extern "C" int vitk_device_ok(int device) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || device < 0 || device >= n) {
+    cudaGetLastError();
+    return 0;
+  }
+  int major = 0;
+  cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device);
+  return major == 10 ? 1 : 0;
+}
+
+extern "C" const char* vitk_last_error(vitk_handle h) {
+  return h ? h->err.msg.c_str() : g_create_error.c_str();
+}
+
+extern "C" int64_t vitk_launch_count(vitk_handle h) { return h ? h->launches : 0; }
+
+extern "C" int vitk_create(const vitk_config* cfg, int device, vitk_handle* out) {
+  Err e;
+  auto fail = [&](vitk_ctx* c) {
+    g_create_error = e.msg.empty() && c ? c->err.msg : e.msg;
+    free_ctx(c);
+    return 1;
+  };
+  if (!cfg || !out) { e.set("vitk_create: null argument"); return fail(nullptr); }
+  *out = nullptr;
+  if (!vitk_device_ok(device)) {
+    e.set("vitk_create: device %d is not a visible sm_100 GPU (no CPU fallback exists)", device);
+    return fail(nullptr);
+  }
+  if (cfg->hidden != cfg->heads * 64) { e.set("hidden must be heads*64"); return fail(nullptr); }
+  if (cfg->hidden != 768 && cfg->hidden != 1024) { e.set("hidden must be 768 or 1024"); return fail(nullptr); }
+  if (cfg->image_h % cfg->patch || cfg->image_w % cfg->patch || cfg->patch % 8) {
+    e.set("patch must divide the image and be a multiple of 8"); return fail(nullptr);
+  }
+  if (cfg->hidden % 256 || cfg->mlp % 256 || cfg->max_batch < 1) {
+    e.set("hidden/mlp must be multiples of 256 and max_batch >= 1"); return fail(nullptr);
+  }
+  vitk_ctx* c = new vitk_ctx();
+  c->cfg = *cfg;
+  c->device = device;
+  c->P = (cfg->image_h / cfg->patch) * (cfg->image_w / cfg->patch);
+  c->S = c->P + 1;
+  c->Kp = cfg->channels * cfg->patch * cfg->patch;
+  c->D = cfg->hidden;
+  c->F = cfg->mlp;
+  if (c->S > 256) { e.set("tokens per frame %d > 256 unsupported by the attention kernel", c->S); return fail(c); }
+  if (c->Kp % 64) { e.set("channels*patch^2 must be a multiple of 64"); return fail(c); }
+  if (cudaSetDevice(device) != cudaSuccess) { e.set("cudaSetDevice failed"); return fail(c); }
+  const size_t D = c->D, F = c->F, Kp = c->Kp;
+  c->layers.resize(cfg->layers);
+  int rc = 0;
+  for (auto& L : c->layers) {
+    rc |= dev_alloc(e, &L.w_qkv, 3 * D * D) | dev_alloc(e, &L.w_o, D * D) |
+          dev_alloc(e, &L.w_fc1, F * D) | dev_alloc(e, &L.w_fc2, D * F) |
+          dev_alloc(e, &L.b_qkv, 3 * D) | dev_alloc(e, &L.b_o, D) | dev_alloc(e, &L.b_fc1, F) |
+          dev_alloc(e, &L.b_fc2, D) | dev_alloc(e, &L.ln1_g, D) | dev_alloc(e, &L.ln1_b, D) |
+          dev_alloc(e, &L.ln2_g, D) | dev_alloc(e, &L.ln2_b, D);
+    if (rc) return fail(c);
+    rc |= tmap_operand(e, &L.tm_qkv, L.w_qkv, 3 * D, D, 256) |
+          tmap_operand(e, &L.tm_o, L.w_o, D, D, 256) |
+          tmap_operand(e, &L.tm_fc1, L.w_fc1, F, D, 256) |
+          tmap_operand(e, &L.tm_fc2, L.w_fc2, D, F, 256);
+    if (rc) return fail(c);
+  }
+  const size_t M = (size_t)cfg->max_batch * c->S;
+  const size_t actw = D > Kp ? D : Kp;
+  rc |= dev_alloc(e, &c->w_patch, D * Kp) | dev_alloc(e, &c->posb, (size_t)c->S * D) |
+        dev_alloc(e, &c->lnf_g, D) | dev_alloc(e, &c->lnf_b, D) | dev_alloc(e, &c->act, M * actw) |
+        dev_alloc(e, &c->qkv, M * 3 * D) | dev_alloc(e, &c->hbuf, M * F) |
+        dev_alloc(e, &c->resid, M * D) | dev_alloc(e, &c->emb, (size_t)cfg->max_batch * D) |
+        dev_alloc(e, &c->emb_bf16, (size_t)cfg->max_batch * D) |
+        dev_alloc(e, &c->pix_stage,
+                  (size_t)cfg->max_batch * cfg->image_h * cfg->image_w * cfg->channels);
+  if (rc) return fail(c);
+  if (tmap_operand(e, &c->tm_patch, c->w_patch, D, Kp, 256)) return fail(c);
+  if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess) {
+    e.set("cudaStreamCreate failed");
+    return fail(c);
+  }
+  *out = c;
+  return 0;
+}
+
+extern "C" int vitk_destroy(vitk_handle h) {
+  if (!h) return 0;
+  cudaSetDevice(h->device);
+  cudaDeviceSynchronize();
+  free_ctx(h);
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// weights (HF ViTModel state-dict keys, transformers modeling_vit.py)
+// ------------------------------------------------------------------------------------------
+extern "C" int vitk_set_weight(vitk_handle h, const char* name_c, const float* host,
+                               const int64_t* shape, int ndim) {
+  if (!h || !name_c || !host || !shape) return 1;
+  Err& e = h->err;
+  CK(e, cudaSetDevice(h->device));
+  std::string name(name_c);
+  if (name.rfind("vit.", 0) == 0) name = name.substr(4);
+  if (name.rfind("pooler.", 0) == 0) return 0;  // never read by the reference
+  const int64_t D = h->D, F = h->F, S = h->S, Kp = h->Kp;
+  const int64_t ps = h->cfg.patch, C = h->cfg.channels;
+  auto bad_shape = [&]() {
+    e.set("vitk_set_weight: unexpected shape for %s", name.c_str());
+    return 1;
+  };
+  int rc = 0;
+  if (name == "embeddings.cls_token") {
+    if (!shape_is(shape, ndim, {D})) return bad_shape();
+    h->h_cls.assign(host, host + D);
+  } else if (name == "embeddings.position_embeddings") {
+    if (!shape_is(shape, ndim, {S, D})) return bad_shape();
+    h->h_pos.assign(host, host + S * D);
+  } else if (name == "embeddings.patch_embeddings.projection.weight") {
+    if (!shape_is(shape, ndim, {D, C, ps, ps})) return bad_shape();
+    rc = upload_bf16(e, h->w_patch, host, D * Kp);
+  } else if (name == "embeddings.patch_embeddings.projection.bias") {
+    if (!shape_is(shape, ndim, {D})) return bad_shape();
+    h->h_pbias.assign(host, host + D);
+  } else if (name == "layernorm.weight") {
+    if (!shape_is(shape, ndim, {D})) return bad_shape();
+    rc = upload_f32(e, h->lnf_g, host, D);
+  } else if (name == "layernorm.bias") {
+    if (!shape_is(shape, ndim, {D})) return bad_shape();
+    rc = upload_f32(e, h->lnf_b, host, D);
+  } else if (name.rfind("encoder.layer.", 0) == 0) {
+    size_t pos = strlen("encoder.layer.");
+    size_t dot = name.find('.', pos);
+    if (dot == std::string::npos) { e.set("bad weight name %s", name.c_str()); return 1; }
+    int li = atoi(name.substr(pos, dot - pos).c_str());
+    if (li < 0 || li >= (int)h->layers.size()) { e.set("layer index out of range: %s", name.c_str()); return 1; }
+    LayerW& L = h->layers[li];
+    std::string rest = name.substr(dot + 1);
+    auto qkv_part = [&](int part, bool is_w) {
+      if (is_w) {
+        if (!shape_is(shape, ndim, {D, D})) return bad_shape();
+        return upload_bf16(e, L.w_qkv + (size_t)part * D * D, host, D * D);
+      }
+      if (!shape_is(shape, ndim, {D})) return bad_shape();
+      return upload_f32(e, L.b_qkv + (size_t)part * D, host, D);
+    };
+    auto mat = [&](__nv_bfloat16* dst, int64_t r, int64_t c) {
+      if (!shape_is(shape, ndim, {r, c})) return bad_shape();
+      return upload_bf16(e, dst, host, r * c);
+    };
+    auto vec = [&](float* dst, int64_t n) {
+      if (!shape_is(shape, ndim, {n})) return bad_shape();
+      return upload_f32(e, dst, host, n);
+    };
+    if (rest == "attention.attention.query.weight") rc = qkv_part(0, true);
+    else if (rest == "attention.attention.query.bias") rc = qkv_part(0, false);
+    else if (rest == "attention.attention.key.weight") rc = qkv_part(1, true);
+    else if (rest == "attention.attention.key.bias") rc = qkv_part(1, false);
+    else if (rest == "attention.attention.value.weight") rc = qkv_part(2, true);
+    else if (rest == "attention.attention.value.bias") rc = qkv_part(2, false);
+    else if (rest == "attention.output.dense.weight") rc = mat(L.w_o, D, D);
+    else if (rest == "attention.output.dense.bias") rc = vec(L.b_o, D);
+    else if (rest == "layernorm_before.weight") rc = vec(L.ln1_g, D);
+    else if (rest == "layernorm_before.bias") rc = vec(L.ln1_b, D);
+    else if (rest == "layernorm_after.weight") rc = vec(L.ln2_g, D);
+    else if (rest == "layernorm_after.bias") rc = vec(L.ln2_b, D);
+    else if (rest == "intermediate.dense.weight") rc = mat(L.w_fc1, F, D);
+    else if (rest == "intermediate.dense.bias") rc = vec(L.b_fc1, F);
+    else if (rest == "output.dense.weight") rc = mat(L.w_fc2, D, F);
+    else if (rest == "output.dense.bias") rc = vec(L.b_fc2, D);
+    else { e.set("vitk_set_weight: unknown key %s", name.c_str()); return 1; }
+  } else {
+    e.set("vitk_set_weight: unknown key %s", name.c_str());
+    return 1;
+  }
+  if (rc) return rc;
+  h->have.insert(name);
+  h->finalized = false;
+  return 0;
+}
+
+extern "C" int vitk_finalize_weights(vitk_handle h) {
+  if (!h) return 1;
+  Err& e = h->err;
+  const size_t want = 6 + 16 * h->layers.size();
+  if (h->have.size() != want) {
+    e.set("vitk_finalize_weights: %zu of %zu tensors supplied", h->have.size(), want);
+    return 1;
+  }
+  CK(e, cudaSetDevice(h->device));
+  // table[0] = cls + pos[0] (the CLS row of the patch matrix is all zeros, so the GEMM adds
+  // nothing); table[t>0] = pos[t] + conv bias.  HF modeling_vit.py:117-124.
+  const int S = h->S, D = h->D;
+  std::vector<float> tab((size_t)S * D);
+  for (int t = 0; t < S; ++t)
+    for (int j = 0; j < D; ++j)
+      tab[(size_t)t * D + j] =
+          h->h_pos[(size_t)t * D + j] + (t == 0 ? h->h_cls[j] : h->h_pbias[j]);
+  if (upload_f32(e, h->posb, tab.data(), tab.size())) return 1;
+  h->finalized = true;
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// forward
+// ------------------------------------------------------------------------------------------
+namespace {
+
+int get_maps(vitk_ctx* c, int n, BatchMaps** out) {
+  auto it = c->maps.find(n);
+  if (it != c->maps.end()) { *out = &it->second; return 0; }
+  Err& e = c->err;
+  BatchMaps m;
+  const int M = n * c->S, D = c->D, F = c->F;
+  const int sk = attn_smem_layout(c->S).sk;
+  int rc = tmap_operand(e, &m.a_patch, c->act, M, c->Kp, GEMM_BM) |
+           tmap_operand(e, &m.a_act, c->act, M, D, GEMM_BM) |
+           tmap_operand(e, &m.a_h, c->hbuf, M, F, GEMM_BM) |
+           tmap_output(e, &m.c_resid, c->resid, M, D, false) |
+           tmap_output(e, &m.c_qkv, c->qkv, M, 3 * D, true) |
+           tmap_output(e, &m.c_h, c->hbuf, M, F, true) |
+           tmap_tokens(e, &m.att_q, c->qkv, n, c->S, 3 * D, 128) |
+           tmap_tokens(e, &m.att_kv, c->qkv, n, c->S, 3 * D, sk) |
+           tmap_tokens(e, &m.att_o, c->act, n, c->S, D, 128);
+  if (rc) return 1;
+  *out = &c->maps.emplace(n, m).first->second;
+  return 0;
+}
+
+// One chunk of n <= max_batch frames, everything asynchronous on `st`.
+int forward_chunk(vitk_ctx* c, const void* pix, int fmt, int n, float* emb_f32,
+                  __nv_bfloat16* emb_bf16, int l2norm, cudaStream_t st) {
+  Err& e = c->err;
+  BatchMaps* mp = nullptr;
+  if (get_maps(c, n, &mp)) return 1;
+  const int M = n * c->S, D = c->D, F = c->F;
+  const vitk_config& cfg = c->cfg;
+  // (a3) im2col, (a3/a4) patch GEMM + CLS/pos/bias table -> fp32 residual stream
+  if (launch_patchify(e, pix, fmt, c->act, n, cfg.channels, cfg.image_h, cfg.image_w, cfg.patch, st))
+    return 1;
+  GemmParams gp{};
+  gp.M = M; gp.N = D; gp.K = c->Kp;
+  gp.table = c->posb; gp.table_rows = c->S;
+  if (launch_gemm(e, EPI_TABLE_F32, mp->a_patch, c->tm_patch, mp->c_resid, gp, st)) return 1;
+  c->launches += 2;
+  const int epi_fc1 = cfg.gelu_tanh ? EPI_BIAS_GELUT_BF16 : EPI_BIAS_GELU_BF16;
+  for (auto& L : c->layers) {
+    // (a5.1) LN1 -> (a5.2) fused QKV GEMM -> (a5.3) attention -> (a5.4) out-proj + residual
+    if (launch_layernorm(e, c->resid, L.ln1_g, L.ln1_b, c->act, M, D, cfg.ln_eps, st)) return 1;
+    GemmParams q{};
+    q.M = M; q.N = 3 * D; q.K = D; q.bias = L.b_qkv;
+    if (launch_gemm(e, EPI_BIAS_BF16, mp->a_act, L.tm_qkv, mp->c_qkv, q, st)) return 1;
+    if (launch_attention(e, mp->att_q, mp->att_kv, mp->att_o, n, c->S, cfg.heads, st)) return 1;
+    GemmParams o{};
+    o.M = M; o.N = D; o.K = D; o.bias = L.b_o; o.resid = c->resid; o.ldr = D;
+    if (launch_gemm(e, EPI_BIAS_RESID_F32, mp->a_act, L.tm_o, mp->c_resid, o, st)) return 1;
+    // (a5.1) LN2 -> (a5.5) fc1 + GELU -> fc2 + residual
+    if (launch_layernorm(e, c->resid, L.ln2_g, L.ln2_b, c->act, M, D, cfg.ln_eps, st)) return 1;
+    GemmParams f1{};
+    f1.M = M; f1.N = F; f1.K = D; f1.bias = L.b_fc1;
+    if (launch_gemm(e, epi_fc1, mp->a_act, L.tm_fc1, mp->c_h, f1, st)) return 1;
+    GemmParams f2{};
+    f2.M = M; f2.N = D; f2.K = F; f2.bias = L.b_fc2; f2.resid = c->resid; f2.ldr = D;
+    if (launch_gemm(e, EPI_BIAS_RESID_F32, mp->a_h, L.tm_fc2, mp->c_resid, f2, st)) return 1;
+    c->launches += 7;
+  }
+  // (a6) final LN on the CLS rows only, (a7) row normalisation
+  const int blocks = (n + 3) / 4;
+  if (D == 768)
+    cls_tail_kernel<6><<<blocks, 128, 0, st>>>(c->resid, c->lnf_g, c->lnf_b, emb_f32, emb_bf16, n,
+                                               c->S, cfg.ln_eps, l2norm);
+  else
+    cls_tail_kernel<8><<<blocks, 128, 0, st>>>(c->resid, c->lnf_g, c->lnf_b, emb_f32, emb_bf16, n,
+                                               c->S, cfg.ln_eps, l2norm);
+  CK(e, cudaGetLastError());
+  c->launches += 1;
+  return 0;
+}
+
+size_t pixel_bytes_per_frame(const vitk_config& cfg, int fmt) {
+  size_t px = (size_t)cfg.channels * cfg.image_h * cfg.image_w;
+  return fmt == PIX_F32_NCHW ? px * 4 : fmt == PIX_BF16_NCHW ? px * 2 : px;
+}
+
+}  // namespace
+
+extern "C" int vitk_embed(vitk_handle h, const void* pixels_dev, int pixel_format, int n,
+                          float* emb_f32_dev, void* emb_bf16_dev, int l2_normalise, void* stream) {
+  if (!h) return 1;
+  Err& e = h->err;
+  if (!h->finalized) { e.set("vitk_embed: weights not finalized"); return 1; }
+  if (!pixels_dev || !emb_f32_dev || n < 0) { e.set("vitk_embed: bad argument"); return 1; }
+  if (pixel_format < 0 || pixel_format > 2) { e.set("vitk_embed: bad pixel format"); return 1; }
+  CK(e, cudaSetDevice(h->device));
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const size_t fb = pixel_bytes_per_frame(h->cfg, pixel_format);
+  for (int off = 0; off < n; off += h->cfg.max_batch) {
+    const int cn = n - off < h->cfg.max_batch ? n - off : h->cfg.max_batch;
+    __nv_bfloat16* eb = emb_bf16_dev
+                            ? reinterpret_cast<__nv_bfloat16*>(emb_bf16_dev) + (size_t)off * h->D
+                            : nullptr;
+    if (forward_chunk(h, reinterpret_cast<const uint8_t*>(pixels_dev) + (size_t)off * fb,
+                      pixel_format, cn, emb_f32_dev + (size_t)off * h->D, eb, l2_normalise, st))
+      return 1;
+  }
+  return 0;
+}
+
+extern "C" int vitk_embed_host_u8(vitk_handle h, const uint8_t* frames_host, int n, float* emb_host,
+                                  int l2_normalise) {
+  if (!h) return 1;
+  Err& e = h->err;
+  if (!h->finalized) { e.set("vitk_embed_host_u8: weights not finalized"); return 1; }
+  if (!frames_host || !emb_host || n < 0) { e.set("vitk_embed_host_u8: bad argument"); return 1; }
+  CK(e, cudaSetDevice(h->device));
+  cudaStream_t st = h->own_stream;
+  const size_t fb = pixel_bytes_per_frame(h->cfg, PIX_U8_NHWC);
+  for (int off = 0; off < n; off += h->cfg.max_batch) {
+    const int cn = n - off < h->cfg.max_batch ? n - off : h->cfg.max_batch;
+    CK(e, cudaMemcpyAsync(h->pix_stage, frames_host + (size_t)off * fb, (size_t)cn * fb,
+                          cudaMemcpyHostToDevice, st));
+    if (forward_chunk(h, h->pix_stage, PIX_U8_NHWC, cn, h->emb, nullptr, l2_normalise, st)) return 1;
+    CK(e, cudaMemcpyAsync(emb_host + (size_t)off * h->D, h->emb, (size_t)cn * h->D * 4,
+                          cudaMemcpyDeviceToHost, st));
+  }
+  CK(e, cudaStreamSynchronize(st));
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// bank + k-NN vote
+// ------------------------------------------------------------------------------------------
+extern "C" int vitk_bank_set(vitk_handle h, const float* rows_host, int m, int d,
+                             const int32_t* labels_host, int n_classes, int normalise_rows) {
+  if (!h) return 1;
+  Err& e = h->err;
+  if (!rows_host || m < 1 || d < 64 || d % 64 != 0) {
+    e.set("vitk_bank_set: need m >= 1 rows and d a multiple of 64 (got m=%d d=%d)", m, d);
+    return 1;
+  }
+  if (n_classes < 0 || n_classes > KNN_MAX_CLASSES) {
+    e.set("vitk_bank_set: n_classes must be in [0,%d]", KNN_MAX_CLASSES);
+    return 1;
+  }
+  CK(e, cudaSetDevice(h->device));
+  CK(e, cudaDeviceSynchronize());
+  cudaFree(h->bank); cudaFree(h->bank_sqnorm); cudaFree(h->bank_bf16); cudaFree(h->bank_labels);
+  h->bank = nullptr; h->bank_sqnorm = nullptr; h->bank_bf16 = nullptr; h->bank_labels = nullptr;
+  h->bank_m = 0;
+  std::vector<float> rows(rows_host, rows_host + (size_t)m * d);
+  std::vector<float> sq(m);
+  for (int i = 0; i < m; ++i) {
+    float* r = rows.data() + (size_t)i * d;
+    if (normalise_rows) {
+      // numpy: np.linalg.norm (float32 in, float32 out) then x /= (norm + 1e-8)
+      double s = 0;
+      for (int j = 0; j < d; ++j) s += (double)r[j] * r[j];
+      const float inv_den = (float)std::sqrt(s) + 1e-8f;
+      for (int j = 0; j < d; ++j) r[j] = r[j] / inv_den;
+    }
+    double s2 = 0;
+    for (int j = 0; j < d; ++j) s2 += (double)r[j] * r[j];
+    sq[i] = (float)s2;
+  }
+  if (dev_alloc(e, &h->bank, (size_t)m * d) || dev_alloc(e, &h->bank_bf16, (size_t)m * d) ||
+      dev_alloc(e, &h->bank_sqnorm, (size_t)m) || dev_alloc(e, &h->bank_labels, (size_t)m))
+    return 1;
+  if (upload_f32(e, h->bank, rows.data(), rows.size()) ||
+      upload_bf16(e, h->bank_bf16, rows.data(), rows.size()) ||
+      upload_f32(e, h->bank_sqnorm, sq.data(), sq.size()))
+    return 1;
+  std::vector<int32_t> lab(m, 0);
+  if (labels_host) {
+    for (int i = 0; i < m; ++i) {
+      if (labels_host[i] < 0 || labels_host[i] >= (n_classes > 0 ? n_classes : 1)) {
+        e.set("vitk_bank_set: label %d of row %d outside [0,%d)", labels_host[i], i, n_classes);
+        return 1;
+      }
+      lab[i] = labels_host[i];
+    }
+  }
+  CK(e, cudaMemcpy(h->bank_labels, lab.data(), (size_t)m * 4, cudaMemcpyHostToDevice));
+  if (tmap_operand(e, &h->tm_bank, h->bank_bf16, m, d, 256)) return 1;
+  h->bank_m = m;
+  h->bank_d = d;
+  h->bank_classes = labels_host ? n_classes : 0;
+  h->knn_cap_m = 0;  // force workspace re-check
+  return 0;
+}
+
+namespace {
+int knn_candidates_for(int k, int m) {
+  // bf16 similarity error on unit vectors is ~1e-4..1e-3; the slack keeps every true top-k
+  // row inside the candidate set so the fp32 re-rank can restore the exact order.
+  int kc = 2 * k + 32;
+  if (kc > KNN_MAX_CAND) kc = KNN_MAX_CAND;
+  if (kc > m) kc = m;
+  if (kc < k) kc = k < m ? k : m;
+  return kc;
+}
+}  // namespace
+
+extern "C" int vitk_knn_vote(vitk_handle h, const float* q_dev, int n, int k, int metric,
+                             int normalise_queries, int32_t* idx_out, float* score_out,
+                             int32_t* label_out, int32_t* counts_out, void* stream) {
+  if (!h) return 1;
+  Err& e = h->err;
+  if (h->bank_m == 0) { e.set("vitk_knn_vote: no bank set"); return 1; }
+  if (!q_dev || !idx_out || !score_out || n < 0) { e.set("vitk_knn_vote: bad argument"); return 1; }
+  if (k < 1 || k > 64) { e.set("vitk_knn_vote: k=%d outside [1,64]", k); return 1; }
+  if (metric != METRIC_COSINE && metric != METRIC_L2) { e.set("vitk_knn_vote: bad metric"); return 1; }
+  if (n == 0) return 0;
+  CK(e, cudaSetDevice(h->device));
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int m = h->bank_m, d = h->bank_d;
+  const int ld = (m + 3) & ~3;  // TMA row pitch must be a multiple of 16 B
+  if (n > h->knn_cap_q || ld > h->knn_cap_m) {
+    CK(e, cudaStreamSynchronize(st));
+    cudaFree(h->knn_q); cudaFree(h->knn_qb); cudaFree(h->knn_scores); cudaFree(h->knn_cand);
+    h->knn_q = nullptr; h->knn_qb = nullptr; h->knn_scores = nullptr; h->knn_cand = nullptr;
+    const int cq = n > h->knn_cap_q ? n : h->knn_cap_q;
+    h->knn_cap_q = 0;
+    if (dev_alloc(e, &h->knn_q, (size_t)cq * d) || dev_alloc(e, &h->knn_qb, (size_t)cq * d) ||
+        dev_alloc(e, &h->knn_scores, (size_t)cq * ld) ||
+        dev_alloc(e, &h->knn_cand, (size_t)cq * KNN_MAX_CAND))
+      return 1;
+    h->knn_cap_q = cq;
+    h->knn_cap_m = ld;
+  }
+  const int kc = knn_candidates_for(k, m);
+  prep_queries_kernel<<<(n + 7) / 8, 256, 0, st>>>(q_dev, h->knn_q, h->knn_qb, n, d,
+                                                   normalise_queries);
+  CK(e, cudaGetLastError());
+  CUtensorMap ta, tc;
+  if (tmap_operand(e, &ta, h->knn_qb, n, d, GEMM_BM) ||
+      tmap_output(e, &tc, h->knn_scores, n, ld, false))
+    return 1;
+  GemmParams gp{};
+  gp.M = n; gp.N = m; gp.K = d;
+  if (launch_gemm(e, EPI_F32, ta, h->tm_bank, tc, gp, st)) return 1;
+  knn_candidates_kernel<<<(n + 3) / 4, 128, 0, st>>>(h->knn_scores, ld, h->bank_sqnorm, n, m, kc,
+                                                     metric, h->knn_cand);
+  CK(e, cudaGetLastError());
+  knn_rerank_vote_kernel<<<(n + 3) / 4, 128, 0, st>>>(
+      h->knn_q, h->bank, h->bank_classes ? h->bank_labels : nullptr, h->knn_cand, n, m, d, kc, k,
+      metric, h->bank_classes, idx_out, score_out, label_out, counts_out);
+  CK(e, cudaGetLastError());
+  h->launches += 4;
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// operator-level entry points
+// ------------------------------------------------------------------------------------------
+namespace {
+thread_local Err g_op_err;
+}
+
+extern "C" int vitk_op_gemm(const void* a, const void* w, void* out, int M, int N, int K, int epi,
+                            const float* bias, const float* resid, const float* table,
+                            int table_rows, void* stream) {
+  Err& e = g_op_err;
+  if (M < 1 || N < 4 || N % 4 || K < 64) { e.set("vitk_op_gemm: bad shape"); g_create_error = e.msg; return 1; }
+  const bool bf16_out = epi == EPI_BIAS_BF16 || epi == EPI_BIAS_GELU_BF16 || epi == EPI_BIAS_GELUT_BF16;
+  if (bf16_out && N % 8) { e.set("vitk_op_gemm: bf16 output needs N %% 8 == 0"); g_create_error = e.msg; return 1; }
+  CUtensorMap ta, tb, tc;
+  GemmParams p{};
+  p.M = M; p.N = N; p.K = K; p.bias = bias; p.resid = resid; p.ldr = N; p.table = table;
+  p.table_rows = table_rows > 0 ? table_rows : 1;
+  int rc = tmap_operand(e, &ta, a, M, K, GEMM_BM) || tmap_operand(e, &tb, w, N, K, 256) ||
+           tmap_output(e, &tc, out, M, N, bf16_out) ||
+           launch_gemm(e, epi, ta, tb, tc, p, reinterpret_cast<cudaStream_t>(stream));
+  if (rc) g_create_error = e.msg;
+  return rc;
+}
+
+extern "C" int vitk_op_layernorm(const float* x, const float* gamma, const float* beta, void* y,
+                                 int rows, int d, float eps, void* stream) {
+  Err& e = g_op_err;
+  int rc = launch_layernorm(e, x, gamma, beta, reinterpret_cast<__nv_bfloat16*>(y), rows, d, eps,
+                            reinterpret_cast<cudaStream_t>(stream));
+  if (rc) g_create_error = e.msg;
+  return rc;
+}
+
+extern "C" int vitk_op_attention(const void* qkv, void* out, int frames, int S, int heads,
+                                 void* stream) {
+  Err& e = g_op_err;
+  const int D = heads * 64;
+  CUtensorMap tq, tkv, to;
+  int rc = (S < 1 || S > 256) ? (e.set("vitk_op_attention: S outside [1,256]"), 1) : 0;
+  rc = rc || tmap_tokens(e, &tq, qkv, frames, S, 3 * D, 128) ||
+       tmap_tokens(e, &tkv, qkv, frames, S, 3 * D, attn_smem_layout(S).sk) ||
+       tmap_tokens(e, &to, out, frames, S, D, 128) ||
+       launch_attention(e, tq, tkv, to, frames, S, heads, reinterpret_cast<cudaStream_t>(stream));
+  if (rc) g_create_error = e.msg;
+  return rc;
+}
+
+extern "C" int vitk_op_patchify(const void* pixels, int fmt, void* out, int n, int C, int H, int W,
+                                int patch, void* stream) {
+  Err& e = g_op_err;
+  int rc = launch_patchify(e, pixels, fmt, reinterpret_cast<__nv_bfloat16*>(out), n, C, H, W, patch,
+                           reinterpret_cast<cudaStream_t>(stream));
+  if (rc) g_create_error = e.msg;
+  return rc;
+}

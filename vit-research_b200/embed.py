@@ -1,0 +1,219 @@
+"""Embedding entry points with the reference's call signatures, backed by libvitk (sm_100a).
+
+Mirrors, for the hot path only:
+  hf_vit_embed_batch(frames_np) -> (N,768) float32, unit rows
+      nba_proj/ratt_write_clips_to_ragdb.py:135-159 (+10 copies)
+  extract_embeddings(vit_model, image_paths, batch_size=1024) -> (N,768)
+      nba_proj/smarter_generate_clips.py:69-94
+  model.predict(x, batch_size=, verbose=)['pre_logits'] -> (B,1,1,768)
+      nba_proj/write_embeddings.py:185-188
+  vit_model(pixel_values=...).last_hidden_state[:, 0, :]
+      nba_proj/ratt_write_clips_to_ragdb.py:146-148
+PyTorch is used for device memory and streams only; all arithmetic runs in libvitk's kernels.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from types import SimpleNamespace
+
+import numpy as np
+
+from . import _lib
+from ._lib import VitkConfig, VitkError, check, ptr, stream_ptr
+
+
+@dataclass
+class ViTGeometry:
+    image_h: int = 224
+    image_w: int = 224
+    patch: int = 16
+    channels: int = 3
+    hidden: int = 768
+    heads: int = 12
+    mlp: int = 3072
+    layers: int = 12
+    ln_eps: float = 1e-12
+    gelu_tanh: bool = False
+
+    @property
+    def tokens(self) -> int:
+        return (self.image_h // self.patch) * (self.image_w // self.patch) + 1
+
+    @classmethod
+    def vit_b16(cls) -> "ViTGeometry":
+        return cls()
+
+    @classmethod
+    def vit_l16(cls) -> "ViTGeometry":
+        return cls(hidden=1024, heads=16, mlp=4096, layers=24)
+
+    @classmethod
+    def from_hf_config(cls, cfg) -> "ViTGeometry":
+        img = cfg.image_size if isinstance(cfg.image_size, (tuple, list)) else (cfg.image_size,) * 2
+        act = getattr(cfg, "hidden_act", "gelu")
+        if act not in ("gelu", "gelu_new", "gelu_pytorch_tanh"):
+            raise VitkError(f"unsupported hidden_act {act!r}")
+        return cls(image_h=int(img[0]), image_w=int(img[1]), patch=int(cfg.patch_size),
+                   channels=int(cfg.num_channels), hidden=int(cfg.hidden_size),
+                   heads=int(cfg.num_attention_heads), mlp=int(cfg.intermediate_size),
+                   layers=int(cfg.num_hidden_layers), ln_eps=float(cfg.layer_norm_eps),
+                   gelu_tanh=act != "gelu")
+
+
+class ViTEmbedder:
+    """Owns one vitk handle (weights + workspace on one GPU)."""
+
+    def __init__(self, geometry: ViTGeometry, state_dict, device: int = 0, max_batch: int = 256):
+        import torch
+
+        self.lib = _lib.load()
+        self.geometry = geometry
+        self.device = int(device)
+        self.max_batch = int(max_batch)
+        self.handle = C.c_void_p()
+        if not torch.cuda.is_available():
+            raise VitkError("no CUDA device visible: vitk has no CPU fallback")
+        torch.cuda.set_device(self.device)
+        g = geometry
+        cfg = VitkConfig(g.image_h, g.image_w, g.patch, g.channels, g.hidden, g.heads, g.mlp,
+                         g.layers, g.ln_eps, int(g.gelu_tanh), self.max_batch)
+        check(self.lib.vitk_create(C.byref(cfg), self.device, C.byref(self.handle)), None,
+              "vitk_create")
+        for name, t in state_dict.items():
+            if name.startswith("pooler.") or name.startswith("vit.pooler."):
+                continue
+            a = t.detach().cpu().float().contiguous().numpy() if hasattr(t, "detach") else \
+                np.ascontiguousarray(t, dtype=np.float32)
+            shape = (C.c_int64 * a.ndim)(*a.shape)
+            check(self.lib.vitk_set_weight(self.handle, name.encode(), ptr(a), shape, a.ndim),
+                  self.handle, f"vitk_set_weight({name})")
+        check(self.lib.vitk_finalize_weights(self.handle), self.handle, "vitk_finalize_weights")
+
+    @classmethod
+    def from_hf(cls, hf_model, device: int = 0, max_batch: int = 256) -> "ViTEmbedder":
+        """hf_model: transformers.ViTModel (the reference's `vit_model`)."""
+        return cls(ViTGeometry.from_hf_config(hf_model.config), hf_model.state_dict(), device,
+                   max_batch)
+
+    def close(self):
+        if getattr(self, "handle", None) and self.handle.value:
+            self.lib.vitk_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):  # pragma: no cover
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def launch_count(self) -> int:
+        return int(self.lib.vitk_launch_count(self.handle))
+
+    # ---- device-resident path -------------------------------------------------------------
+    def embed(self, pixels, l2_normalise: bool = True, out=None, out_bf16=None, stream=None):
+        """pixels: CUDA tensor — (N,3,H,W) float32/bfloat16 (already processed like
+        ViTImageProcessor) or (N,H,W,3) uint8 raw frames.  Returns (N,hidden) float32 CUDA."""
+        import torch
+
+        g = self.geometry
+        if not pixels.is_cuda:
+            raise VitkError("embed() wants a CUDA tensor; use embed_frames() for host arrays")
+        pixels = pixels.contiguous()
+        if pixels.dtype == torch.uint8:
+            fmt, want = _lib.PIX_U8_NHWC, (g.image_h, g.image_w, g.channels)
+        elif pixels.dtype == torch.float32:
+            fmt, want = _lib.PIX_F32_NCHW, (g.channels, g.image_h, g.image_w)
+        elif pixels.dtype == torch.bfloat16:
+            fmt, want = _lib.PIX_BF16_NCHW, (g.channels, g.image_h, g.image_w)
+        else:
+            raise VitkError(f"unsupported pixel dtype {pixels.dtype}")
+        if pixels.ndim != 4 or tuple(pixels.shape[1:]) != want:
+            # same failure mode as HF ViTPatchEmbeddings (modeling_vit.py:155-165)
+            raise ValueError(f"Input image size {tuple(pixels.shape)} doesn't match model "
+                             f"(N,{want[0]},{want[1]},{want[2]}) for dtype {pixels.dtype}.")
+        n = pixels.shape[0]
+        if out is None:
+            out = torch.empty((n, g.hidden), dtype=torch.float32, device=pixels.device)
+        check(self.lib.vitk_embed(self.handle, ptr(pixels), fmt, n, ptr(out), ptr(out_bf16),
+                                  int(l2_normalise), stream_ptr(stream)), self.handle, "vitk_embed")
+        return out
+
+    # ---- host path (what hf_vit_embed_batch does) -----------------------------------------
+    def embed_frames(self, frames_np: np.ndarray, l2_normalise: bool = True) -> np.ndarray:
+        """(N,H,W,3) uint8 host frames at the model's resolution -> (N,hidden) float32 host."""
+        g = self.geometry
+        frames_np = np.ascontiguousarray(frames_np)
+        if frames_np.dtype != np.uint8:
+            raise VitkError("embed_frames wants uint8")
+        if frames_np.ndim != 4 or frames_np.shape[1:] != (g.image_h, g.image_w, g.channels):
+            raise ValueError(f"frames {frames_np.shape} do not match (N,{g.image_h},{g.image_w},"
+                             f"{g.channels}); resize upstream (GPU resize is a SURVEY §8f item)")
+        out = np.empty((frames_np.shape[0], g.hidden), dtype=np.float32)
+        check(self.lib.vitk_embed_host_u8(self.handle, ptr(frames_np), frames_np.shape[0],
+                                          ptr(out), int(l2_normalise)), self.handle,
+              "vitk_embed_host_u8")
+        return out
+
+    # ---- HF-style call: vit_model(pixel_values=...).last_hidden_state[:,0,:] ---------------
+    def __call__(self, pixel_values=None, **_):
+        """Returns an object whose .last_hidden_state is (N,1,hidden): only the CLS row exists
+        (the reference never reads the other 196, ratt_write_clips_to_ragdb.py:148)."""
+        cls = self.embed(pixel_values, l2_normalise=False)
+        return SimpleNamespace(last_hidden_state=cls[:, None, :], pooler_output=None)
+
+    # ---- Keras-style call: model.predict(x)['pre_logits'] ---------------------------------
+    def predict(self, x, batch_size: int = 32, verbose: int = 0):
+        """x: (B,H,W,3) uint8/float host array.  Returns {'pre_logits': (B,1,1,hidden)}
+        (write_embeddings.py:185-188, rag_vit.py:463-464).  NOTE: applies the HF rescale /
+        normalise; the TF scripts feed raw 0..255 pixels to random weights."""
+        x = np.asarray(x)
+        if x.dtype != np.uint8:
+            x = np.clip(x, 0, 255).astype(np.uint8)
+        emb = self.embed_frames(x, l2_normalise=False)
+        return {"pre_logits": emb.reshape(-1, 1, 1, self.geometry.hidden)}
+
+
+# ---- module-global style used by the reference scripts ----------------------------------------
+_default: ViTEmbedder | None = None
+
+
+def install(embedder: ViTEmbedder) -> None:
+    """Set the module-global model, like the reference's `vit_model = ViTModel...to(device)`."""
+    global _default
+    _default = embedder
+
+
+def hf_vit_embed_batch(frames_np):
+    """
+    frames_np: (N, H, W, 3) uint8 or float32
+    returns: (N, 768) float32          [ratt_write_clips_to_ragdb.py:135-159]
+    """
+    if _default is None:
+        raise VitkError("call vit_research_b200.install(ViTEmbedder...) first")
+    frames_np = np.asarray(frames_np)
+    if frames_np.dtype != np.uint8:
+        frames_np = np.clip(frames_np, 0, 255).astype(np.uint8)
+    return _default.embed_frames(frames_np, l2_normalise=True)
+
+
+def extract_embeddings(vit_model, image_paths, batch_size=1024, loader=None):
+    """smarter_generate_clips.py:69-94: load + resize each path, predict in batches, stack the
+    un-normalised pre_logits.  `loader(path) -> (H,W,3) uint8` defaults to cv2 like the
+    reference (imread, BGR2RGB, INTER_AREA resize to the model resolution)."""
+    g = vit_model.geometry
+    if loader is None:
+        import cv2
+
+        def loader(p):
+            f = cv2.cvtColor(cv2.imread(p), cv2.COLOR_BGR2RGB)
+            return cv2.resize(f, (g.image_w, g.image_h), interpolation=cv2.INTER_AREA)
+    embs, batch = [], []
+    for i, p in enumerate(image_paths):
+        batch.append(loader(p))
+        if len(batch) == batch_size or i == len(image_paths) - 1:
+            out = vit_model.predict(np.array(batch), batch_size=batch_size, verbose=0)
+            embs.append(out["pre_logits"].reshape(len(batch), -1))
+            batch = []
+    return np.vstack(embs) if embs else np.zeros((0, g.hidden), np.float32)
