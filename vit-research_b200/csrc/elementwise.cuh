@@ -58,8 +58,10 @@ __global__ void __launch_bounds__(256) patchify_kernel(const PatchifyParams p) {
                            (((size_t)f * p.H + y) * p.W + x) * p.C + c;
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-          float u = (float)s[j * p.C] * p.scale;
-          v[j] = (u - p.mean) * p.inv_std;
+          // separate roundings (no FMA contraction): bit-identical to the HF processor's
+          // float32 rescale-then-normalise (image_processing_vit.py:20-27)
+          float u = __fmul_rn((float)s[j * p.C], p.scale);
+          v[j] = __fmul_rn(__fsub_rn(u, p.mean), p.inv_std);
         }
         o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]);
         o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
