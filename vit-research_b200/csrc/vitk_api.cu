@@ -806,7 +806,12 @@ extern "C" int vitk_op_gemm(const void* a, const void* w, void* out, int M, int 
                             const float* bias, const float* resid, const float* table,
                             int table_rows, void* stream) {
   Err& e = g_op_err;
-  if (M < 1 || N < 4 || N % 4 || K < 64) { e.set("vitk_op_gemm: bad shape"); g_create_error = e.msg; return 1; }
+  if (K < GEMM_BK || K % GEMM_BK) {
+    e.set("vitk_op_gemm: K=%d must be a positive multiple of %d", K, GEMM_BK);
+    g_create_error = e.msg;
+    return 1;
+  }
+  if (M < 1 || N < 4 || N % 4) { e.set("vitk_op_gemm: bad shape M=%d N=%d", M, N); g_create_error = e.msg; return 1; }
   const bool bf16_out = epi == EPI_BIAS_BF16 || epi == EPI_BIAS_GELU_BF16 || epi == EPI_BIAS_GELUT_BF16;
   if (bf16_out && N % 8) { e.set("vitk_op_gemm: bf16 output needs N %% 8 == 0"); g_create_error = e.msg; return 1; }
   CUtensorMap ta, tb, tc;
