@@ -104,6 +104,15 @@ int vitk_knn_vote(vitk_handle h, const float* q_dev, int n, int k, int metric,
                   int normalise_queries, int32_t* idx_out, float* score_out, int32_t* label_out,
                   int32_t* counts_out, void* stream);
 
+/* Host-buffer end-to-end call: what a frame-labelling loop does per batch
+ * (generate_clips_hmm.py:387-412 — embed, query, vote), on static banks.  H2D of the uint8
+ * frames, forward (L2-normalised rows), top-k + vote, D2H of the results; synchronous.
+ * emb_host (n,hidden) f32; label_host (n); idx_host/score_host (n,k); counts_host
+ * (n,n_classes); every output except emb_host may be NULL. */
+int vitk_embed_vote_host_u8(vitk_handle h, const uint8_t* frames_host, int n, int k, int metric,
+                            float* emb_host, int32_t* label_host, int32_t* idx_host,
+                            float* score_host, int32_t* counts_host);
+
 /* ---- operator-level entry points (used by the parity tests, one kernel each) ----------- */
 /* C[M,N] = A[M,K] (bf16) · W[N,K]^T (bf16) with epilogue `epi` (VITK_EPI_*).
  * out is bf16 for the *_BF16 epilogues, f32 otherwise (row pitch = N elements). */

@@ -5,6 +5,6 @@ name at the repo root).  See DESIGN.md for the path, its boundary and the kernel
 """
 from ._lib import VitkError, build, load  # noqa: F401
 from .embed import (ViTEmbedder, ViTGeometry, extract_embeddings, hf_vit_embed_batch,  # noqa: F401
-                    install)
+                    install, random_init_state_dict)
 from .knn import (BankCollection, BankIndex, RattChunkRetriever, determine_class_pass1,  # noqa: F401
                   determine_class_pass2, load_label_banks, temp_smax, LABEL_NAMES)

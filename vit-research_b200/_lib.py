@@ -54,6 +54,7 @@ SIGNATURES = {
     "vitk_finalize_weights": (_i, [_vp]),
     "vitk_embed": (_i, [_vp, _vp, _i, _i, _vp, _vp, _i, _vp]),
     "vitk_embed_host_u8": (_i, [_vp, _vp, _i, _vp, _i]),
+    "vitk_embed_vote_host_u8": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "vitk_bank_set": (_i, [_vp, _vp, _i, _i, _vp, _i, _i]),
     "vitk_knn_vote": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "vitk_op_gemm": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _i, _vp]),

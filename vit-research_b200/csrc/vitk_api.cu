@@ -294,6 +294,8 @@ struct vitk_ctx {
   __nv_bfloat16* knn_qb = nullptr;
   int32_t* knn_cand = nullptr;
   int knn_cap_q = 0, knn_cap_m = 0;
+  int32_t *res_idx = nullptr, *res_label = nullptr, *res_counts = nullptr;
+  float* res_score = nullptr;
   cudaStream_t own_stream = nullptr;
   int64_t launches = 0;
 };
@@ -337,6 +339,7 @@ void free_ctx(vitk_ctx* c) {
   cudaFree(c->act); cudaFree(c->qkv); cudaFree(c->hbuf); cudaFree(c->emb_bf16);
   cudaFree(c->resid); cudaFree(c->emb); cudaFree(c->pix_stage);
   cudaFree(c->bank); cudaFree(c->bank_sqnorm); cudaFree(c->bank_bf16); cudaFree(c->bank_labels);
+  cudaFree(c->res_idx); cudaFree(c->res_label); cudaFree(c->res_counts); cudaFree(c->res_score);
   cudaFree(c->knn_q); cudaFree(c->knn_scores); cudaFree(c->knn_qb); cudaFree(c->knn_cand);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
   delete c;
@@ -420,6 +423,11 @@ extern "C" int vitk_create(const vitk_config* cfg, int device, vitk_handle* out)
         dev_alloc(e, &c->emb_bf16, (size_t)cfg->max_batch * D) |
         dev_alloc(e, &c->pix_stage,
                   (size_t)cfg->max_batch * cfg->image_h * cfg->image_w * cfg->channels);
+  if (rc) return fail(c);
+  rc |= dev_alloc(e, &c->res_idx, (size_t)cfg->max_batch * 64) |
+        dev_alloc(e, &c->res_score, (size_t)cfg->max_batch * 64) |
+        dev_alloc(e, &c->res_label, (size_t)cfg->max_batch) |
+        dev_alloc(e, &c->res_counts, (size_t)cfg->max_batch * KNN_MAX_CLASSES);
   if (rc) return fail(c);
   if (tmap_operand(e, &c->tm_patch, c->w_patch, D, Kp, 256)) return fail(c);
   if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess) {
@@ -855,4 +863,51 @@ extern "C" int vitk_op_patchify(const void* pixels, int fmt, void* out, int n, i
                            reinterpret_cast<cudaStream_t>(stream));
   if (rc) g_create_error = e.msg;
   return rc;
+}
+
+// ------------------------------------------------------------------------------------------
+// host-buffer end-to-end call: frames in, embeddings + labels (+ neighbours) out
+// ------------------------------------------------------------------------------------------
+extern "C" int vitk_embed_vote_host_u8(vitk_handle h, const uint8_t* frames_host, int n, int k,
+                                       int metric, float* emb_host, int32_t* label_host,
+                                       int32_t* idx_host, float* score_host,
+                                       int32_t* counts_host) {
+  if (!h) return 1;
+  Err& e = h->err;
+  if (!h->finalized) { e.set("vitk_embed_vote_host_u8: weights not finalized"); return 1; }
+  if (h->bank_m == 0) { e.set("vitk_embed_vote_host_u8: no bank set"); return 1; }
+  if (!frames_host || !emb_host || n < 0 || k < 1 || k > 64) {
+    e.set("vitk_embed_vote_host_u8: bad argument");
+    return 1;
+  }
+  if (h->bank_d != h->D) { e.set("bank width %d != hidden %d", h->bank_d, h->D); return 1; }
+  CK(e, cudaSetDevice(h->device));
+  cudaStream_t st = h->own_stream;
+  const size_t fb = pixel_bytes_per_frame(h->cfg, PIX_U8_NHWC);
+  const int nc = h->bank_classes > 0 ? h->bank_classes : 1;
+  for (int off = 0; off < n; off += h->cfg.max_batch) {
+    const int cn = n - off < h->cfg.max_batch ? n - off : h->cfg.max_batch;
+    CK(e, cudaMemcpyAsync(h->pix_stage, frames_host + (size_t)off * fb, (size_t)cn * fb,
+                          cudaMemcpyHostToDevice, st));
+    // the reference stores / queries L2-normalised rows (ratt_write_clips_to_ragdb.py:152)
+    if (forward_chunk(h, h->pix_stage, PIX_U8_NHWC, cn, h->emb, nullptr, 1, st)) return 1;
+    if (vitk_knn_vote(h, h->emb, cn, k, metric, 0, h->res_idx, h->res_score, h->res_label,
+                      h->res_counts, st))
+      return 1;
+    CK(e, cudaMemcpyAsync(emb_host + (size_t)off * h->D, h->emb, (size_t)cn * h->D * 4,
+                          cudaMemcpyDeviceToHost, st));
+    if (label_host)
+      CK(e, cudaMemcpyAsync(label_host + off, h->res_label, (size_t)cn * 4, cudaMemcpyDeviceToHost, st));
+    if (idx_host)
+      CK(e, cudaMemcpyAsync(idx_host + (size_t)off * k, h->res_idx, (size_t)cn * k * 4,
+                            cudaMemcpyDeviceToHost, st));
+    if (score_host)
+      CK(e, cudaMemcpyAsync(score_host + (size_t)off * k, h->res_score, (size_t)cn * k * 4,
+                            cudaMemcpyDeviceToHost, st));
+    if (counts_host)
+      CK(e, cudaMemcpyAsync(counts_host + (size_t)off * nc, h->res_counts, (size_t)cn * nc * 4,
+                            cudaMemcpyDeviceToHost, st));
+  }
+  CK(e, cudaStreamSynchronize(st));
+  return 0;
 }

@@ -61,6 +61,46 @@ class ViTGeometry:
                    gelu_tanh=act != "gelu")
 
 
+def random_init_state_dict(geometry: "ViTGeometry", seed: int = 0) -> dict:
+    """Random-init weights with HF ViT's initialiser statistics (modeling_vit.py:384-399:
+    trunc-normal(0, 0.02) for Linear/Conv/pos-emb/CLS, zero biases, LayerNorm gamma=1 beta=0),
+    keyed like the HF state dict.  Used by bench.py / smoke() — there is no network for
+    checkpoints, and the product path must not depend on transformers or the oracle."""
+    import torch
+
+    g = geometry
+    gen = torch.Generator().manual_seed(seed)
+    D, F, ps, C_ = g.hidden, g.mlp, g.patch, g.channels
+
+    def tn(*shape):
+        t = torch.empty(*shape)
+        torch.nn.init.trunc_normal_(t, mean=0.0, std=0.02, generator=gen)
+        return t
+
+    sd = {
+        "embeddings.cls_token": tn(1, 1, D),
+        "embeddings.position_embeddings": tn(1, g.tokens, D),
+        "embeddings.patch_embeddings.projection.weight": tn(D, C_, ps, ps),
+        "embeddings.patch_embeddings.projection.bias": torch.zeros(D),
+        "layernorm.weight": torch.ones(D), "layernorm.bias": torch.zeros(D),
+    }
+    for i in range(g.layers):
+        p = f"encoder.layer.{i}."
+        for n in ("query", "key", "value"):
+            sd[p + f"attention.attention.{n}.weight"] = tn(D, D)
+            sd[p + f"attention.attention.{n}.bias"] = torch.zeros(D)
+        sd[p + "attention.output.dense.weight"] = tn(D, D)
+        sd[p + "attention.output.dense.bias"] = torch.zeros(D)
+        sd[p + "intermediate.dense.weight"] = tn(F, D)
+        sd[p + "intermediate.dense.bias"] = torch.zeros(F)
+        sd[p + "output.dense.weight"] = tn(D, F)
+        sd[p + "output.dense.bias"] = torch.zeros(D)
+        for n in ("layernorm_before", "layernorm_after"):
+            sd[p + n + ".weight"] = torch.ones(D)
+            sd[p + n + ".bias"] = torch.zeros(D)
+    return sd
+
+
 class ViTEmbedder:
     """Owns one vitk handle (weights + workspace on one GPU)."""
 
@@ -155,6 +195,28 @@ class ViTEmbedder:
                                           ptr(out), int(l2_normalise)), self.handle,
               "vitk_embed_host_u8")
         return out
+
+    def embed_and_vote(self, frames_np: np.ndarray, index, k: int = 25, out=None):
+        """Host frames -> (embeddings (N,hidden) f32, labels (N,) i32, idx (N,k) i32,
+        score (N,k) f32, counts (N,classes) i32), all host arrays: the per-batch work of the
+        reference's labelling loops (generate_clips_hmm.py:387-412) in one call.  `index` is the
+        BankIndex set on this embedder; `out` may hold preallocated arrays (e.g. pinned)."""
+        g = self.geometry
+        frames_np = np.ascontiguousarray(frames_np)
+        if frames_np.dtype != np.uint8 or frames_np.ndim != 4 or \
+                frames_np.shape[1:] != (g.image_h, g.image_w, g.channels):
+            raise ValueError(f"frames {frames_np.shape}/{frames_np.dtype} do not match uint8 "
+                             f"(N,{g.image_h},{g.image_w},{g.channels})")
+        n, nc = frames_np.shape[0], max(index.n_classes, 1)
+        if out is None:
+            out = (np.empty((n, g.hidden), np.float32), np.empty((n,), np.int32),
+                   np.empty((n, k), np.int32), np.empty((n, k), np.float32),
+                   np.empty((n, nc), np.int32))
+        emb, label, idx, score, counts = out
+        check(self.lib.vitk_embed_vote_host_u8(self.handle, ptr(frames_np), n, int(k), index.metric,
+                                               ptr(emb), ptr(label), ptr(idx), ptr(score),
+                                               ptr(counts)), self.handle, "vitk_embed_vote_host_u8")
+        return emb, label, idx, score, counts
 
     # ---- HF-style call: vit_model(pixel_values=...).last_hidden_state[:,0,:] ---------------
     def __call__(self, pixel_values=None, **_):
