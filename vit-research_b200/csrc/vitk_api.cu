@@ -191,8 +191,9 @@ int launch_attention(Err& e, const CUtensorMap& tq, const CUtensorMap& tkv, cons
   p.S = S;
   p.heads = heads;
   p.frames = frames;
+  p.nblk = S > 128 ? 2 : 1;
   p.scale_log2e = 0.125f * 1.4426950408889634f;  // head dim 64 -> 1/sqrt(64)
-  attention_kernel<<<frames * heads, ATT_THREADS, L.total, st>>>(tq, tkv, to, p);
+  attention_kernel<<<frames * heads * p.nblk, ATT_THREADS, L.total, st>>>(tq, tkv, to, p);
   CK(e, cudaGetLastError());
   return 0;
 }

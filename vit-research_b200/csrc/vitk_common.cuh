@@ -197,6 +197,17 @@ __device__ __forceinline__ void umma_bf16_ss(uint32_t tmem_d, uint64_t desc_a, u
       "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// D[tmem] (+)= A[tmem] * B[smem]: A is M x K bf16 held in TMEM, row i on lane i, two
+// consecutive-K elements per 32-bit cell (K = 16 per instruction -> 8 cells).  K-major only.
+__device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b,
+                                             uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}\n" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 // mbarrier arrives once all previously issued tcgen05.mma of this thread have completed
 // (implies tcgen05.fence::before_thread_sync).
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
@@ -233,6 +244,24 @@ __device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&r)
       : "r"(taddr)
       : "memory");
 }
+// registers -> TMEM, same 32x32b shape (thread i writes lane base+i, N consecutive cells)
+__device__ __forceinline__ void tmem_st_32x32b_x8(uint32_t taddr, const uint32_t (&r)[8]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};\n" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_32x32b_x16(uint32_t taddr, const uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};\n" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+      "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() {
+  asm volatile("tcgen05.wait::st.sync.aligned;\n" ::: "memory");
+}
 __device__ __forceinline__ void tmem_ld_wait() {
   asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
 }
@@ -244,8 +273,26 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
 }
-__device__ __forceinline__ float gelu_erf(float x) {  // HF hidden_act="gelu" (exact erf)
-  return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f));
+// HF hidden_act="gelu" (exact erf): gelu(x) = x*Phi(x) = max(x,0) - |x| * 0.5*erfc(|x|/sqrt2).
+// 0.5*erfc(a/sqrt2) = 2^q(a) with q a degree-6 minimax fit of log2 on [0,6] (tools/fit_gelu.py):
+// max |error| vs the float64 erf form is 2.5e-7 over [-8,8] (fp32 rounding level), at 11
+// FMA-pipe instructions + one MUFU.EX2 instead of erff's two divergent branches (~25) — the
+// fc1 epilogue was issue-bound on erff (profiles/r01_v1_ncu_gemm.txt: 64 % issue active).
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float gelu_erf(float x) {
+  const float a = fminf(fabsf(x), 6.0f);
+  float q = 3.291235043e-05f;
+  q = fmaf(q, a, -7.622243138e-04f);
+  q = fmaf(q, a, 8.038992994e-03f);
+  q = fmaf(q, a, -5.331545696e-02f);
+  q = fmaf(q, a, -4.588715434e-01f);
+  q = fmaf(q, a, -1.151156664e+00f);
+  q = fmaf(q, a, -9.999995828e-01f);
+  return fmaxf(x, 0.0f) - fabsf(x) * ex2_approx(q);
 }
 __device__ __forceinline__ float gelu_tanh(float x) {  // TF Model Garden activations.gelu
   const float k0 = 0.7978845608028654f, k1 = 0.044715f;
