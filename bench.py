@@ -172,13 +172,21 @@ def time_kernels(v, lib, torch, n_frames):
     b3, b1, bF = torch.zeros(3 * D, device=dev), torch.zeros(D, device=dev), torch.zeros(F, device=dev)
     g1 = torch.ones(D, device=dev)
     st = stream_ptr()
+    parts = 2 * D // 256
+    xb = torch.empty(M, D, device=dev, dtype=bf)
+    stats = torch.empty(M, parts, 2, device=dev)
+    stats2 = torch.empty(M, parts, 2, device=dev)
+    assert lib.vitk_op_rowstats(ptr(resid), ptr(xb), ptr(stats), M, D, parts, st) == 0
+    c3, cF = torch.zeros(3 * D, device=dev), torch.zeros(F, device=dev)
+    fused = lib.vitk_op_gemm_fused
     ops = {
-        "gemm_qkv": (lambda: lib.vitk_op_gemm(ptr(x), ptr(w_qkv), ptr(out_qkv), M, 3 * D, D, 0, ptr(b3), None, None, 1, st), 2.0 * M * 3 * D * D),
-        "gemm_proj_resid": (lambda: lib.vitk_op_gemm(ptr(x), ptr(w_o), ptr(resid), M, D, D, 3, ptr(b1), ptr(resid), None, 1, st), 2.0 * M * D * D),
-        "gemm_fc1_gelu": (lambda: lib.vitk_op_gemm(ptr(x), ptr(w_1), ptr(out_h), M, F, D, 1, ptr(bF), None, None, 1, st), 2.0 * M * F * D),
-        "gemm_fc2_resid": (lambda: lib.vitk_op_gemm(ptr(h), ptr(w_2), ptr(resid), M, D, F, 3, ptr(b1), ptr(resid), None, 1, st), 2.0 * M * D * F),
+        # the four GEMMs exactly as the forward launches them (LayerNorm folded / residual fused)
+        "gemm_qkv": (lambda: fused(ptr(xb), ptr(w_qkv), ptr(out_qkv), M, 3 * D, D, 0, ptr(b3), ptr(c3), ptr(stats), parts, 1e-12, None, None, None, st), 2.0 * M * 3 * D * D),
+        "gemm_proj_resid": (lambda: fused(ptr(x), ptr(w_o), ptr(resid), M, D, D, 3, ptr(b1), None, None, 0, 0.0, ptr(resid), ptr(xb), ptr(stats2), st), 2.0 * M * D * D),
+        "gemm_fc1_gelu": (lambda: fused(ptr(xb), ptr(w_1), ptr(out_h), M, F, D, 1, ptr(bF), ptr(cF), ptr(stats), parts, 1e-12, None, None, None, st), 2.0 * M * F * D),
+        "gemm_fc2_resid": (lambda: fused(ptr(h), ptr(w_2), ptr(resid), M, D, F, 3, ptr(b1), None, None, 0, 0.0, ptr(resid), ptr(xb), ptr(stats2), st), 2.0 * M * D * F),
         "attention": (lambda: lib.vitk_op_attention(ptr(qkv), ptr(ln_out), n_frames, S, H, st), 4.0 * n_frames * H * S * S * 64),
-        "layernorm": (lambda: lib.vitk_op_layernorm(ptr(resid), ptr(g1), ptr(b1), ptr(ln_out), M, D, 1e-12, st), None),
+        "rowstats_cast": (lambda: lib.vitk_op_rowstats(ptr(resid), ptr(ln_out), ptr(stats2), M, D, parts, st), None),
     }
     res = {}
     for name, (fn, flops) in ops.items():
@@ -198,6 +206,9 @@ def time_kernels(v, lib, torch, n_frames):
             r["tflops"] = round(flops / ms / 1e9, 1)
         else:
             r["gbs"] = round(M * D * 6 / ms / 1e6, 1)  # f32 read + bf16 write
+        if name == "gemm_proj_resid":
+            # HBM-bound: A bf16 + residual f32 in/out + bf16 copy (+ weights, negligible)
+            r["gbs"] = round(M * D * (2 + 4 + 4 + 2) / ms / 1e6, 1)
         res[name] = r
     return res
 

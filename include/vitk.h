@@ -119,6 +119,27 @@ int vitk_embed_vote_host_u8(vitk_handle h, const uint8_t* frames_host, int n, in
 int vitk_op_gemm(const void* a_bf16_dev, const void* w_bf16_dev, void* out_dev, int M, int N, int K,
                  int epi, const float* bias_dev, const float* resid_dev, const float* table_dev,
                  int table_rows, void* stream);
+/* The two fused forms the forward actually runs (HF modeling_vit.py:325-346):
+ *  - LayerNorm folded into the consuming GEMM (epi = VITK_EPI_BIAS[_GELU|_GELUT]_BF16):
+ *      out = act( rstd[m] * (acc[m,n] - mean[m]*c1[n]) + bias[n] )
+ *    where A is the RAW (un-normalised) row in bf16, W is pre-scaled by gamma, c1[n] =
+ *    sum_k W[n,k], bias[n] = b[n] + sum_k beta[k]*W0[n,k], and mean/rstd come from
+ *    stats_dev: per row `stats_parts` partial (sum, sumsq) float pairs over the K = d columns.
+ *  - residual GEMM that also emits the next LayerNorm's inputs (epi = VITK_EPI_BIAS_RESID_F32):
+ *      out f32 = acc + bias + resid;  xb_out (bf16 copy of out, may be NULL);  stats_out
+ *      (may be NULL): per row 2*ceil(N/256) partial (sum, sumsq) pairs of out, pair index
+ *      2*(n/256) + (n%256)/128.
+ * NULL c1/stats/xb_out/stats_out reduce to vitk_op_gemm. */
+int vitk_op_gemm_fused(const void* a_bf16_dev, const void* w_bf16_dev, void* out_dev, int M, int N,
+                       int K, int epi, const float* bias_dev, const float* c1_dev,
+                       const float* stats_dev, int stats_parts, float ln_eps,
+                       const float* resid_dev, void* xb_out_bf16_dev, float* stats_out_dev,
+                       void* stream);
+/* Row statistics + bf16 cast of an f32 matrix [rows, d] (d in {768,1024}): xb = bf16(x),
+ * stats[row] = `parts` (sum, sumsq) pairs, pair 0 = the full-row sums, the rest zero.  Seeds
+ * the folded LayerNorm of layer 0 from the patch-embedding output. */
+int vitk_op_rowstats(const float* x_dev, void* xb_bf16_dev, float* stats_dev, int rows, int d,
+                     int parts, void* stream);
 /* y(bf16) = LayerNorm(x f32) over the last dim d (d in {768, 1024}). */
 int vitk_op_layernorm(const float* x_dev, const float* gamma_dev, const float* beta_dev,
                       void* y_bf16_dev, int rows, int d, float eps, void* stream);

@@ -103,9 +103,61 @@ def patchify_case(n, fmt):
     return report(f"patchify n={n} fmt={fmt} rc={rc}", out, ref.bfloat16(), 1e-6)
 
 
+def fused_ln_case(M, N, K, epi):
+    """LayerNorm folded into the GEMM epilogue vs torch LN -> linear (-> gelu)."""
+    x = (torch.randn(M, K, generator=g) * 2 + 0.3).to(dev)
+    gm = (torch.randn(K, generator=g) * 0.3 + 1).to(dev); bt = (torch.randn(K, generator=g) * 0.2).to(dev)
+    W = (torch.randn(N, K, generator=g) * 0.05).to(dev); b = torch.randn(N, generator=g).to(dev)
+    parts = 2 * K // 256
+    xb = torch.empty(M, K, device=dev, dtype=torch.bfloat16)
+    stats = torch.full((M, parts, 2), float("nan"), device=dev)
+    rc = lib.vitk_op_rowstats(ptr(x), ptr(xb), ptr(stats), M, K, parts, stream_ptr())
+    Wf = (W * gm).bfloat16()
+    c1 = Wf.float().sum(1).contiguous()
+    c2 = (b + W @ bt).contiguous()
+    out = torch.full((M, N), float("nan"), device=dev, dtype=torch.bfloat16)
+    rc |= lib.vitk_op_gemm_fused(ptr(xb), ptr(Wf), ptr(out), M, N, K, epi, ptr(c2), ptr(c1), ptr(stats), parts,
+                                 1e-12, None, None, None, stream_ptr())
+    torch.cuda.synchronize()
+    if rc:
+        print("fused ln rc", rc, lib.vitk_last_error(None)); return False
+    ref = torch.nn.functional.layer_norm(x, (K,), gm, bt, 1e-12) @ W.t() + b
+    if epi == 1: ref = torch.nn.functional.gelu(ref)
+    ok = report(f"fused LN gemm M={M} N={N} K={K} epi={epi}", out, ref, 3e-2)
+    sref = torch.stack([x.sum(1), (x * x).sum(1)], 1)
+    ok &= report("   rowstats sums", stats[:, 0, :], sref, 1e-4)
+    ok &= report("   rowstats xb", xb, x.bfloat16(), 1e-6)
+    return ok
+
+
+def fused_resid_case(M, N, K, inplace=True):
+    A = (torch.randn(M, K, generator=g) * 0.5).to(dev).bfloat16()
+    W = (torch.randn(N, K, generator=g) * 0.05).to(dev).bfloat16()
+    bias = torch.randn(N, generator=g).to(dev)
+    resid = torch.randn(M, N, generator=g).to(dev)
+    ref = A.float() @ W.float().t() + bias + resid
+    out = resid.clone() if inplace else torch.full((M, N), float("nan"), device=dev)
+    parts = 2 * ((N + 255) // 256)
+    xb = torch.full((M, N), float("nan"), device=dev, dtype=torch.bfloat16)
+    st = torch.full((M, parts, 2), float("nan"), device=dev)
+    rc = lib.vitk_op_gemm_fused(ptr(A), ptr(W), ptr(out), M, N, K, 3, ptr(bias), None, None, 0, 0.0,
+                                ptr(out) if inplace else ptr(resid), ptr(xb), ptr(st), stream_ptr())
+    torch.cuda.synchronize()
+    if rc:
+        print("fused resid rc", rc, lib.vitk_last_error(None)); return False
+    ok = report(f"fused resid gemm M={M} N={N} K={K} inplace={inplace}", out, ref, 2e-3)
+    ok &= report("   xb copy", xb, out.bfloat16(), 1e-6)
+    cols = torch.arange(N, device=dev) // 128
+    sref = torch.zeros(M, parts, 2, device=dev)
+    sref[:, :, 0].index_add_(1, cols, out)
+    sref[:, :, 1].index_add_(1, cols, out * out)
+    ok &= report("   partial stats", st, sref, 1e-4)
+    return ok
+
+
 if __name__ == "__main__":
     print(torch.cuda.get_device_name(0), lib.vitk_version(), "device_ok", lib.vitk_device_ok(0), flush=True)
-    which = sys.argv[1:] or ["gemm", "ln", "attn", "patch"]
+    which = sys.argv[1:] or ["gemm", "fused", "ln", "attn", "patch"]
     ok = True
     if "gemm" in which:
         ok &= gemm_case(128, 256, 64, 5)
@@ -116,6 +168,14 @@ if __name__ == "__main__":
         ok &= gemm_case(197 * 64, 2304, 768, 0)
         ok &= gemm_case(197 * 64, 768, 3072, 3)
         ok &= gemm_case(256, 1472, 768, 5)
+    if "fused" in which:
+        ok &= fused_ln_case(300, 768, 768, 0)
+        ok &= fused_ln_case(197 * 16, 3072, 768, 1)
+        ok &= fused_ln_case(200, 2048, 1024, 0)
+        ok &= fused_resid_case(300, 768, 768, True)
+        ok &= fused_resid_case(300, 768, 768, False)
+        ok &= fused_resid_case(197 * 16, 768, 3072, True)
+        ok &= fused_resid_case(333, 1024, 1024, True)
     if "ln" in which:
         ok &= ln_case(1000, 768); ok &= ln_case(77, 1024)
     if "patch" in which:

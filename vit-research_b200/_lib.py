@@ -58,6 +58,8 @@ SIGNATURES = {
     "vitk_bank_set": (_i, [_vp, _vp, _i, _i, _vp, _i, _i]),
     "vitk_knn_vote": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "vitk_op_gemm": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _i, _vp]),
+    "vitk_op_gemm_fused": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _i, _f, _vp, _vp, _vp, _vp]),
+    "vitk_op_rowstats": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
     "vitk_op_layernorm": (_i, [_vp, _vp, _vp, _vp, _i, _i, _f, _vp]),
     "vitk_op_attention": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "vitk_op_patchify": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp]),

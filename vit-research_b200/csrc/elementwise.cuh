@@ -111,6 +111,36 @@ layernorm_bf16_kernel(const float* __restrict__ x, const float* __restrict__ gam
   }
 }
 
+// Row statistics + bf16 cast: seeds the folded LayerNorm (gemm_sm100.cuh) of layer 0 from the
+// patch-embedding output.  xb = bf16(x); stats[row] = `parts` (sum, sumsq) pairs, pair 0 holds
+// the full-row sums and the others are zero (same layout the residual GEMM epilogue writes).
+template <int VEC>  // D = 128 * VEC
+__global__ void __launch_bounds__(256)
+rowstats_cast_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ xb,
+                     float* __restrict__ stats, int rows, int parts) {
+  constexpr int D = 128 * VEC;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp >= rows) return;
+  const float4* xr = reinterpret_cast<const float4*>(x + (size_t)warp * D);
+  uint2* yr = reinterpret_cast<uint2*>(xb + (size_t)warp * D);
+  float s = 0.f, ss = 0.f;
+#pragma unroll
+  for (int j = 0; j < VEC; ++j) {
+    const float4 v = xr[lane + 32 * j];
+    s += (v.x + v.y) + (v.z + v.w);
+    ss += (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
+    uint2 o;
+    o.x = pack_bf16x2(v.x, v.y);
+    o.y = pack_bf16x2(v.z, v.w);
+    yr[lane + 32 * j] = o;
+  }
+  s = warp_sum(s);
+  ss = warp_sum(ss);
+  float2* sp = reinterpret_cast<float2*>(stats + (size_t)warp * parts * 2);
+  if (lane < parts) sp[lane] = lane == 0 ? make_float2(s, ss) : make_float2(0.f, 0.f);
+}
+
 // CLS tail: final LayerNorm on token 0 of every frame (HF modeling_vit.py:455 then
 // last_hidden_state[:,0,:], ratt_write_clips_to_ragdb.py:148) and the reference's row
 // normalisation  cls / (||cls|| + 1e-8)  (ratt_write_clips_to_ragdb.py:152).

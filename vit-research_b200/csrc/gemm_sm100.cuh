@@ -2,18 +2,28 @@
 //
 // Replaces, for the hot path, every dense contraction the reference runs through cuBLAS/cuDNN:
 //   patch embedding  (HF modeling_vit.py:131-167 — Conv2d k16 s16 == GEMM over im2col'd patches)
-//   Q/K/V projection (modeling_vit.py:216-230, fused into one N=3D GEMM)
+//   Q/K/V projection (modeling_vit.py:216-230, fused into one N=3D GEMM) with layernorm_before
+//                    (modeling_vit.py:325) folded into the epilogue
 //   attention output (modeling_vit.py:254-268) + residual (modeling_vit.py:337)
-//   MLP fc1 + GELU   (modeling_vit.py:287-299), fc2 + residual (modeling_vit.py:302-312)
+//   MLP fc1 + GELU   (modeling_vit.py:287-299) with layernorm_after (modeling_vit.py:340) folded
+//   fc2 + residual   (modeling_vit.py:302-312)
 //   similarity GEMM  (nba_proj/retrieval/ratt_chunk_retriever.py:123  sims = Q @ C.T)
+//
+// LayerNorm folding.  LN(x)·Wᵀ + b = rstd·(x·(γ∘W)ᵀ − mean·c1) + c2 with c1[n] = Σ_k γ_k W[n,k],
+// c2[n] = b[n] + Σ_k β_k W[n,k].  The GEMM therefore runs on a bf16 copy of the RAW residual
+// stream against γ-scaled weights, and the epilogue applies the per-row (mean, rstd) and the
+// per-column (c1, c2).  The per-row statistics come for free from the epilogue of the GEMM that
+// produced the residual (EPI_RESID_F32 below), so no LayerNorm kernel runs between GEMMs and
+// the normalised activations never touch HBM.
 //
 // Shape of the kernel (one CTA per SM, 384 threads):
 //   warp 0      TMA producer: A tile 128x64 and W tile BNx64 (bf16, 128B swizzle) per k-block
 //   warp 1      MMA issuer: one thread issues tcgen05.mma (M=128, N=BN, K=16) x4 per k-block,
 //               accumulating in TMEM; tcgen05.commit releases smem stages / publishes the tile
 //   warp 2      TMEM allocator (2 accumulator stages x BN columns)
-//   warps 4-11  epilogue: tcgen05.ld TMEM->registers, bias/GELU/residual/table, swizzled
-//               st.shared into a per-warp staging tile, TMA store to global (coalesced, async)
+//   warps 4-11  epilogue: tcgen05.ld TMEM->registers, epilogue math, swizzled st.shared into a
+//               per-warp staging tile, TMA store to global (coalesced, async).  The residual
+//               epilogue TMA-LOADS the residual tile into the same staging buffer first.
 // The TMEM accumulator is double buffered so the epilogue of tile i overlaps the MMAs of tile i+1.
 #pragma once
 #include "vitk_common.cuh"
@@ -21,19 +31,28 @@
 namespace vitk {
 
 enum GemmEpilogue : int {
-  EPI_BIAS_BF16 = 0,       // out bf16 = acc + bias[n]
-  EPI_BIAS_GELU_BF16 = 1,  // out bf16 = gelu_erf(acc + bias[n])
-  EPI_BIAS_GELUT_BF16 = 2, // out bf16 = gelu_tanh(acc + bias[n])
-  EPI_BIAS_RESID_F32 = 3,  // out f32  = acc + bias[n] + resid[m,n]   (resid may alias out)
+  EPI_BIAS_BF16 = 0,       // out bf16 = y                    y = rstd[m]*(acc - mean[m]*c1[n]) + c2[n]
+  EPI_BIAS_GELU_BF16 = 1,  // out bf16 = gelu_erf(y)          (stats == null: mean = 0, rstd = 1,
+  EPI_BIAS_GELUT_BF16 = 2, // out bf16 = gelu_tanh(y)          i.e. y = acc + bias[n])
+  EPI_BIAS_RESID_F32 = 3,  // out f32  = acc + bias[n] + resid[m,n]   (resid may alias out);
+                           //   optional: xb bf16 copy of out, per-row partial (sum, sumsq)
   EPI_TABLE_F32 = 4,       // out f32  = acc + table[m % table_rows, n]  (patch embed: pos+bias/CLS)
   EPI_F32 = 5,             // out f32  = acc                              (similarity scores)
 };
 
 struct GemmParams {
   int M, N, K;
-  const float* bias;   // [N]
-  const float* resid;  // [M, ldr]
-  int ldr;
+  const float* bias;   // [N]   bias, or c2 when stats != null
+  const float* c1;     // [N]   LN fold column term (only read when stats != null)
+  const float* stats;  // LN fold: per-row partial (sum, sumsq) pairs; null = plain bias epilogue
+  int stats_parts;          // partial pairs per row
+  long long stats_stride;   // floats between consecutive rows of `stats`
+  float inv_d, eps;         // 1/width of the normalised row, LayerNorm epsilon
+  // EPI_BIAS_RESID_F32 extras (all optional)
+  __nv_bfloat16* xb;        // bf16 copy of the output rows
+  long long xb_ld;          // elements between rows of xb
+  float* stats_out;         // [row*stats_out_stride + part*2 + {0,1}], part = 2*n_blk + half
+  long long stats_out_stride;
   const float* table;  // [table_rows, N]
   int table_rows;
 };
@@ -43,6 +62,7 @@ constexpr int GEMM_BK = 64;
 constexpr int GEMM_THREADS = 384;
 constexpr int GEMM_EPI_WARPS = 8;
 constexpr int GEMM_STAGING_BYTES = 4096;  // 32 rows x 128 B per buffer
+constexpr int GEMM_MAX_SMEM = 232448;     // 227 KB opt-in limit per CTA
 
 template <int BN>
 struct GemmCfg {
@@ -51,22 +71,36 @@ struct GemmCfg {
   static constexpr int kBBytes = BN * GEMM_BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStagingBytes = GEMM_EPI_WARPS * GEMM_STAGING_BYTES;  // 32 KB
-  static constexpr int kBarBytes = 256;
-  static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + kBarBytes + 1024;
+  static constexpr int kVecBytes = 2 * BN * 4;   // c1 | c2 (bias) of the current N tile
+  static constexpr int kBarBytes = 256;          // 2*kStages + 4 + 8 mbarriers + TMEM slot
+  static constexpr int kCarveBytes = kStages * kStageBytes + kStagingBytes + kVecBytes + kBarBytes;
+  // the carve-up starts at the first 1024-B boundary of the dynamic window; ask for as much
+  // alignment slack as the 227 KB limit leaves (the kernel traps if it is ever insufficient)
+  static constexpr int kSmemBytes =
+      kCarveBytes + 1024 <= GEMM_MAX_SMEM ? kCarveBytes + 1024 : GEMM_MAX_SMEM;
   static constexpr uint32_t kTmemCols = 2 * BN;
+  static_assert(kCarveBytes + 128 <= GEMM_MAX_SMEM, "GEMM shared memory carve-up too large");
 };
 
 template <int EPI>
 struct EpiTraits {
   static constexpr bool kOutBf16 = (EPI == EPI_BIAS_BF16 || EPI == EPI_BIAS_GELU_BF16 ||
                                     EPI == EPI_BIAS_GELUT_BF16);
+  static constexpr bool kUsesVec = kOutBf16 || EPI == EPI_BIAS_RESID_F32;
   static constexpr int kChunkCols = kOutBf16 ? 64 : 32;  // 128 B of output per row per chunk
 };
+
+__device__ __forceinline__ uint32_t dynamic_smem_size() {
+  uint32_t v;
+  asm volatile("mov.u32 %0, %%dynamic_smem_size;" : "=r"(v));
+  return v;
+}
 
 template <int BN, int EPI>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                    const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
+                    const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmR,
+                    const GemmParams p) {
   using Cfg = GemmCfg<BN>;
   constexpr int kStages = Cfg::kStages;
   constexpr int CH = EpiTraits<EPI>::kChunkCols;
@@ -74,15 +108,23 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
+  if (threadIdx.x == 0 &&
+      static_cast<uint32_t>(smem - smem_raw) + Cfg::kCarveBytes > dynamic_smem_size()) {
+    printf("vitk: gemm dynamic smem window misaligned (%u B needed)\n",
+           static_cast<uint32_t>(smem - smem_raw) + Cfg::kCarveBytes);
+    __trap();
+  }
   uint8_t* sA = smem;
   uint8_t* sB = smem + kStages * Cfg::kABytes;
   uint8_t* sStage = smem + kStages * Cfg::kStageBytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sStage + Cfg::kStagingBytes);
+  float* sVec = reinterpret_cast<float*>(sStage + Cfg::kStagingBytes);  // [2][BN]: c1 | c2
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sStage + Cfg::kStagingBytes + Cfg::kVecBytes);
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + kStages;
   uint64_t* tfull_bar = bars + 2 * kStages;
   uint64_t* tempty_bar = bars + 2 * kStages + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+  uint64_t* resid_bar = bars + 2 * kStages + 4;  // [GEMM_EPI_WARPS]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4 + GEMM_EPI_WARPS);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -96,6 +138,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     tma_prefetch_desc(&tmC);
+    if constexpr (EPI == EPI_BIAS_RESID_F32) tma_prefetch_desc(&tmR);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < kStages; ++i) {
@@ -106,6 +149,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       mbar_init(&tfull_bar[i], 1);
       mbar_init(&tempty_bar[i], GEMM_EPI_WARPS);
     }
+    for (int i = 0; i < GEMM_EPI_WARPS; ++i) mbar_init(&resid_bar[i], 1);
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
@@ -166,22 +210,65 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int ew = warp - 4;            // 0..7
     const int q = warp & 3;             // TMEM lane quarter this warp may access
     const int half = ew >> 2;           // which half of the BN columns
+    const int et = threadIdx.x - 128;   // 0..255 among the epilogue threads
     constexpr int kColsPerWarp = BN / 2;
     constexpr int kChunks = kColsPerWarp / CH;
     uint8_t* sbuf = sStage + ew * GEMM_STAGING_BYTES;
     int acc = 0;
     uint32_t acc_phase = 0;
+    uint32_t resid_phase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
       const int row0 = m_blk * GEMM_BM + q * 32;
       const int row = row0 + lane;
+      if constexpr (EpiTraits<EPI>::kUsesVec) {
+        // per-column vectors of this N tile -> smem (read back as broadcast float4s)
+        named_bar_sync(1, GEMM_EPI_WARPS * 32);  // every warp is done with the previous tile's
+        for (int i = et; i < BN; i += GEMM_EPI_WARPS * 32) {
+          const int n = n_blk * BN + i;
+          sVec[i] = (p.stats != nullptr && n < p.N) ? __ldg(p.c1 + n) : 0.f;
+          sVec[BN + i] = (n < p.N) ? __ldg(p.bias + n) : 0.f;
+        }
+        named_bar_sync(1, GEMM_EPI_WARPS * 32);
+      }
+      // LayerNorm fold: per-row mean / rstd from the partial sums left by the producing GEMM
+      float mean = 0.f, rstd = 1.f;
+      if constexpr (EpiTraits<EPI>::kOutBf16) {
+        if (p.stats != nullptr && row < p.M) {
+          const float2* sp = reinterpret_cast<const float2*>(p.stats + (size_t)row * p.stats_stride);
+          float s = 0.f, ss = 0.f;
+          for (int i = 0; i < p.stats_parts; ++i) {
+            const float2 t = __ldg(sp + i);
+            s += t.x;
+            ss += t.y;
+          }
+          mean = s * p.inv_d;
+          const float var = fmaxf(fmaf(-mean, mean, ss * p.inv_d), 0.f);
+          rstd = rsqrtf(var + p.eps);
+        }
+      }
+      const float nmr = -mean * rstd;  // y = rstd*acc + nmr*c1 + c2
+      float st_s = 0.f, st_ss = 0.f;   // EPI_BIAS_RESID_F32: this warp's partial row statistics
+      if constexpr (EPI == EPI_BIAS_RESID_F32) {
+        // residual chunk 0 -> staging while the accumulator is still being produced
+        if (lane == 0) {
+          tma_store_wait_read<0>();
+          const int col0 = n_blk * BN + half * kColsPerWarp;
+          if (col0 < p.N && row0 < p.M) {
+            mbar_arrive_expect_tx(&resid_bar[ew], GEMM_STAGING_BYTES);
+            tma_load_2d(sbuf, &tmR, &resid_bar[ew], col0, row0);
+          }
+        }
+      }
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after_sync();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
                              static_cast<uint32_t>(acc * BN + half * kColsPerWarp);
 #pragma unroll 1
       for (int c = 0; c < kChunks; ++c) {
-        const int col0 = n_blk * BN + half * kColsPerWarp + c * CH;
+        const int lcol0 = half * kColsPerWarp + c * CH;  // column inside the N tile
+        const int col0 = n_blk * BN + lcol0;
+        const bool live = col0 < p.N && row0 < p.M;      // warp-uniform
         if constexpr (CH == 32) {
           uint32_t r[32];
           tmem_ld_32x32b_x32(t_row + c * CH, r);
@@ -190,19 +277,35 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
           if constexpr (EPI == EPI_BIAS_RESID_F32) {
-            if (row < p.M) {
-              const float4* rp = reinterpret_cast<const float4*>(p.resid + (size_t)row * p.ldr + col0);
-#pragma unroll
-              for (int j = 0; j < 8; ++j) {
-                if (col0 + 4 * j < p.N) {
-                  float4 x = rp[j];
-                  v[4 * j + 0] += x.x; v[4 * j + 1] += x.y; v[4 * j + 2] += x.z; v[4 * j + 3] += x.w;
-                }
-              }
+            if (live) {
+              mbar_wait(&resid_bar[ew], resid_phase);
+              resid_phase ^= 1u;
             }
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (col0 + j < p.N) v[j] += __ldg(p.bias + col0 + j);
+            for (int j = 0; j < 8; ++j) {
+              const float4 b = *reinterpret_cast<const float4*>(sVec + BN + lcol0 + 4 * j);
+              float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (live) x = *reinterpret_cast<const float4*>(sbuf + lane * 128 + ((j ^ (lane & 7)) << 4));
+              v[4 * j + 0] += x.x + b.x; v[4 * j + 1] += x.y + b.y;
+              v[4 * j + 2] += x.z + b.z; v[4 * j + 3] += x.w + b.w;
+            }
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              st_s += v[j];
+              st_ss = fmaf(v[j], v[j], st_ss);
+            }
+            if (p.xb != nullptr && live && row < p.M) {
+              uint4* xp = reinterpret_cast<uint4*>(p.xb + (size_t)row * p.xb_ld + col0);
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                uint4 o;
+                o.x = pack_bf16x2(v[8 * j + 0], v[8 * j + 1]);
+                o.y = pack_bf16x2(v[8 * j + 2], v[8 * j + 3]);
+                o.z = pack_bf16x2(v[8 * j + 4], v[8 * j + 5]);
+                o.w = pack_bf16x2(v[8 * j + 6], v[8 * j + 7]);
+                xp[j] = o;
+              }
+            }
           } else if constexpr (EPI == EPI_TABLE_F32) {
             if (row < p.M) {
               const float4* tp = reinterpret_cast<const float4*>(
@@ -217,8 +320,11 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             }
           }
           // the TMA store that last read the staging tile must have finished reading it
-          if (lane == 0) tma_store_wait_read<0>();
-          __syncwarp();
+          // (the residual epilogue already waited before loading the residual into it)
+          if constexpr (EPI != EPI_BIAS_RESID_F32) {
+            if (lane == 0) tma_store_wait_read<0>();
+            __syncwarp();
+          }
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             float4 o = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
@@ -236,12 +342,18 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             v[32 + j] = __uint_as_float(r1[j]);
           }
 #pragma unroll
-          for (int j = 0; j < 64; ++j) {
-            float b = (col0 + j < p.N) ? __ldg(p.bias + col0 + j) : 0.f;
-            float x = v[j] + b;
-            if constexpr (EPI == EPI_BIAS_GELU_BF16) x = gelu_erf(x);
-            if constexpr (EPI == EPI_BIAS_GELUT_BF16) x = gelu_tanh(x);
-            v[j] = x;
+          for (int j = 0; j < 16; ++j) {
+            const float4 a = *reinterpret_cast<const float4*>(sVec + lcol0 + 4 * j);
+            const float4 b = *reinterpret_cast<const float4*>(sVec + BN + lcol0 + 4 * j);
+            const float av[4] = {a.x, a.y, a.z, a.w};
+            const float bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              float x = fmaf(rstd, v[4 * j + i], fmaf(nmr, av[i], bv[i]));
+              if constexpr (EPI == EPI_BIAS_GELU_BF16) x = gelu_erf(x);
+              if constexpr (EPI == EPI_BIAS_GELUT_BF16) x = gelu_tanh(x);
+              v[4 * j + i] = x;
+            }
           }
           if (lane == 0) tma_store_wait_read<0>();
           __syncwarp();
@@ -264,8 +376,25 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) {
-          if (col0 < p.N && row0 < p.M) tma_store_2d(&tmC, sbuf, col0, row0);
+          if (live) tma_store_2d(&tmC, sbuf, col0, row0);
           tma_store_commit();
+          if constexpr (EPI == EPI_BIAS_RESID_F32) {
+            // next residual chunk into the same buffer once the store has drained it
+            if (c + 1 < kChunks) {
+              tma_store_wait_read<0>();
+              const int ncol0 = col0 + CH;
+              if (ncol0 < p.N && row0 < p.M) {
+                mbar_arrive_expect_tx(&resid_bar[ew], GEMM_STAGING_BYTES);
+                tma_load_2d(sbuf, &tmR, &resid_bar[ew], ncol0, row0);
+              }
+            }
+          }
+        }
+      }
+      if constexpr (EPI == EPI_BIAS_RESID_F32) {
+        if (p.stats_out != nullptr && row < p.M) {
+          float2* so = reinterpret_cast<float2*>(p.stats_out + (size_t)row * p.stats_out_stride);
+          so[2 * n_blk + half] = make_float2(st_s, st_ss);
         }
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }

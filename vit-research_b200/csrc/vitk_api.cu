@@ -140,7 +140,7 @@ int num_sms() {
 
 template <int BN, int EPI>
 int launch_gemm_t(Err& e, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& c,
-                  const GemmParams& p, cudaStream_t st) {
+                  const CUtensorMap& r, const GemmParams& p, cudaStream_t st) {
   auto kern = gemm_bf16_tn_kernel<BN, EPI>;
   static bool attr_set = false;
   if (!attr_set) {
@@ -151,24 +151,34 @@ int launch_gemm_t(Err& e, const CUtensorMap& a, const CUtensorMap& b, const CUte
   const int m_tiles = (p.M + GEMM_BM - 1) / GEMM_BM, n_tiles = (p.N + BN - 1) / BN;
   const int tiles = m_tiles * n_tiles;
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  kern<<<grid, GEMM_THREADS, GemmCfg<BN>::kSmemBytes, st>>>(a, b, c, p);
+  kern<<<grid, GEMM_THREADS, GemmCfg<BN>::kSmemBytes, st>>>(a, b, c, r, p);
   CK(e, cudaGetLastError());
   return 0;
 }
 
+// `r` is the tensor map the residual epilogue loads from (pass `c` when the residual is
+// updated in place or for the epilogues that do not read one).
 int launch_gemm(Err& e, int epi, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& c,
-                const GemmParams& p, cudaStream_t st) {
+                const CUtensorMap& r, const GemmParams& p, cudaStream_t st) {
   if (p.K % GEMM_BK != 0 || p.K <= 0) {
     e.set("gemm: K=%d must be a positive multiple of %d", p.K, GEMM_BK);
     return 1;
   }
+  if (p.stats != nullptr && (p.c1 == nullptr || p.stats_parts < 1)) {
+    e.set("gemm: LayerNorm fold needs c1 and stats_parts >= 1");
+    return 1;
+  }
+  if (epi == EPI_BIAS_RESID_F32 && p.xb != nullptr && (p.N % 32 != 0 || p.xb_ld % 8 != 0)) {
+    e.set("gemm: bf16 residual copy needs N %% 32 == 0 and a 16-byte aligned row pitch");
+    return 1;
+  }
   switch (epi) {
-    case EPI_BIAS_BF16: return launch_gemm_t<256, EPI_BIAS_BF16>(e, a, b, c, p, st);
-    case EPI_BIAS_GELU_BF16: return launch_gemm_t<256, EPI_BIAS_GELU_BF16>(e, a, b, c, p, st);
-    case EPI_BIAS_GELUT_BF16: return launch_gemm_t<256, EPI_BIAS_GELUT_BF16>(e, a, b, c, p, st);
-    case EPI_BIAS_RESID_F32: return launch_gemm_t<256, EPI_BIAS_RESID_F32>(e, a, b, c, p, st);
-    case EPI_TABLE_F32: return launch_gemm_t<256, EPI_TABLE_F32>(e, a, b, c, p, st);
-    case EPI_F32: return launch_gemm_t<256, EPI_F32>(e, a, b, c, p, st);
+    case EPI_BIAS_BF16: return launch_gemm_t<256, EPI_BIAS_BF16>(e, a, b, c, r, p, st);
+    case EPI_BIAS_GELU_BF16: return launch_gemm_t<256, EPI_BIAS_GELU_BF16>(e, a, b, c, r, p, st);
+    case EPI_BIAS_GELUT_BF16: return launch_gemm_t<256, EPI_BIAS_GELUT_BF16>(e, a, b, c, r, p, st);
+    case EPI_BIAS_RESID_F32: return launch_gemm_t<256, EPI_BIAS_RESID_F32>(e, a, b, c, r, p, st);
+    case EPI_TABLE_F32: return launch_gemm_t<256, EPI_TABLE_F32>(e, a, b, c, r, p, st);
+    case EPI_F32: return launch_gemm_t<256, EPI_F32>(e, a, b, c, r, p, st);
   }
   e.set("gemm: unknown epilogue %d", epi);
   return 1;
@@ -207,6 +217,25 @@ int launch_layernorm(Err& e, const float* x, const float* g, const float* b, __n
     layernorm_bf16_kernel<8><<<blocks, 256, 0, st>>>(x, g, b, y, rows, eps);
   else {
     e.set("layernorm: hidden=%d unsupported (768 or 1024)", d);
+    return 1;
+  }
+  CK(e, cudaGetLastError());
+  return 0;
+}
+
+int launch_rowstats(Err& e, const float* x, __nv_bfloat16* xb, float* stats, int rows, int d,
+                    int parts, cudaStream_t st) {
+  if (parts < 1 || parts > 32) {
+    e.set("rowstats: parts=%d outside [1,32]", parts);
+    return 1;
+  }
+  const int blocks = (rows + 7) / 8;
+  if (d == 768)
+    rowstats_cast_kernel<6><<<blocks, 256, 0, st>>>(x, xb, stats, rows, parts);
+  else if (d == 1024)
+    rowstats_cast_kernel<8><<<blocks, 256, 0, st>>>(x, xb, stats, rows, parts);
+  else {
+    e.set("rowstats: hidden=%d unsupported (768 or 1024)", d);
     return 1;
   }
   CK(e, cudaGetLastError());
@@ -255,14 +284,19 @@ uint16_t f32_to_bf16_bits(float f) {
 // handle
 // ------------------------------------------------------------------------------------------
 struct LayerW {
+  // w_qkv / w_fc1 hold the LayerNorm-folded weights gamma∘W (bf16); b_qkv / b_fc1 hold
+  // c2[n] = b[n] + sum_k beta[k] W[n,k]; c1_* hold sum_k bf16(gamma[k] W[n,k]).
   __nv_bfloat16 *w_qkv = nullptr, *w_o = nullptr, *w_fc1 = nullptr, *w_fc2 = nullptr;
   float *b_qkv = nullptr, *b_o = nullptr, *b_fc1 = nullptr, *b_fc2 = nullptr;
-  float *ln1_g = nullptr, *ln1_b = nullptr, *ln2_g = nullptr, *ln2_b = nullptr;
+  float *c1_qkv = nullptr, *c1_fc1 = nullptr;
   CUtensorMap tm_qkv, tm_o, tm_fc1, tm_fc2;
+  // host fp32 copies kept from vitk_set_weight until vitk_finalize_weights folds them
+  std::vector<float> h_wqkv, h_bqkv, h_wfc1, h_bfc1, h_ln1g, h_ln1b, h_ln2g, h_ln2b;
+  bool dirty = true;
 };
 
 struct BatchMaps {  // tensor maps that depend on the number of frames in the call
-  CUtensorMap a_patch, a_act, a_h;          // GEMM A operands
+  CUtensorMap a_patch, a_act, a_h, a_xb;    // GEMM A operands
   CUtensorMap c_resid, c_qkv, c_h;          // GEMM outputs
   CUtensorMap att_q, att_kv, att_o;         // attention
 };
@@ -281,6 +315,9 @@ struct vitk_ctx {
   bool finalized = false;
   // workspace
   __nv_bfloat16 *act = nullptr, *qkv = nullptr, *hbuf = nullptr, *emb_bf16 = nullptr;
+  __nv_bfloat16* xb = nullptr;        // bf16 copy of the residual stream (GEMM A operand)
+  float *stats[2] = {nullptr, nullptr};  // per-row LayerNorm partial sums, ping-pong
+  int stat_parts = 0;                 // 2 * hidden / 256
   float *resid = nullptr, *emb = nullptr;
   uint8_t* pix_stage = nullptr;  // device staging for vitk_embed_host_u8
   std::map<int, BatchMaps> maps;
@@ -334,11 +371,12 @@ void free_ctx(vitk_ctx* c) {
   for (auto& L : c->layers) {
     cudaFree(L.w_qkv); cudaFree(L.w_o); cudaFree(L.w_fc1); cudaFree(L.w_fc2);
     cudaFree(L.b_qkv); cudaFree(L.b_o); cudaFree(L.b_fc1); cudaFree(L.b_fc2);
-    cudaFree(L.ln1_g); cudaFree(L.ln1_b); cudaFree(L.ln2_g); cudaFree(L.ln2_b);
+    cudaFree(L.c1_qkv); cudaFree(L.c1_fc1);
   }
   cudaFree(c->w_patch); cudaFree(c->posb); cudaFree(c->lnf_g); cudaFree(c->lnf_b);
   cudaFree(c->act); cudaFree(c->qkv); cudaFree(c->hbuf); cudaFree(c->emb_bf16);
   cudaFree(c->resid); cudaFree(c->emb); cudaFree(c->pix_stage);
+  cudaFree(c->xb); cudaFree(c->stats[0]); cudaFree(c->stats[1]);
   cudaFree(c->bank); cudaFree(c->bank_sqnorm); cudaFree(c->bank_bf16); cudaFree(c->bank_labels);
   cudaFree(c->res_idx); cudaFree(c->res_label); cudaFree(c->res_counts); cudaFree(c->res_score);
   cudaFree(c->knn_q); cudaFree(c->knn_scores); cudaFree(c->knn_qb); cudaFree(c->knn_cand);
@@ -396,6 +434,7 @@ extern "C" int vitk_create(const vitk_config* cfg, int device, vitk_handle* out)
   c->Kp = cfg->channels * cfg->patch * cfg->patch;
   c->D = cfg->hidden;
   c->F = cfg->mlp;
+  c->stat_parts = 2 * cfg->hidden / 256;
   if (c->S > 256) { e.set("tokens per frame %d > 256 unsupported by the attention kernel", c->S); return fail(c); }
   if (c->Kp % 64) { e.set("channels*patch^2 must be a multiple of 64"); return fail(c); }
   if (cudaSetDevice(device) != cudaSuccess) { e.set("cudaSetDevice failed"); return fail(c); }
@@ -406,8 +445,7 @@ extern "C" int vitk_create(const vitk_config* cfg, int device, vitk_handle* out)
     rc |= dev_alloc(e, &L.w_qkv, 3 * D * D) | dev_alloc(e, &L.w_o, D * D) |
           dev_alloc(e, &L.w_fc1, F * D) | dev_alloc(e, &L.w_fc2, D * F) |
           dev_alloc(e, &L.b_qkv, 3 * D) | dev_alloc(e, &L.b_o, D) | dev_alloc(e, &L.b_fc1, F) |
-          dev_alloc(e, &L.b_fc2, D) | dev_alloc(e, &L.ln1_g, D) | dev_alloc(e, &L.ln1_b, D) |
-          dev_alloc(e, &L.ln2_g, D) | dev_alloc(e, &L.ln2_b, D);
+          dev_alloc(e, &L.b_fc2, D) | dev_alloc(e, &L.c1_qkv, 3 * D) | dev_alloc(e, &L.c1_fc1, F);
     if (rc) return fail(c);
     rc |= tmap_operand(e, &L.tm_qkv, L.w_qkv, 3 * D, D, 256) |
           tmap_operand(e, &L.tm_o, L.w_o, D, D, 256) |
@@ -420,7 +458,10 @@ extern "C" int vitk_create(const vitk_config* cfg, int device, vitk_handle* out)
   rc |= dev_alloc(e, &c->w_patch, D * Kp) | dev_alloc(e, &c->posb, (size_t)c->S * D) |
         dev_alloc(e, &c->lnf_g, D) | dev_alloc(e, &c->lnf_b, D) | dev_alloc(e, &c->act, M * actw) |
         dev_alloc(e, &c->qkv, M * 3 * D) | dev_alloc(e, &c->hbuf, M * F) |
-        dev_alloc(e, &c->resid, M * D) | dev_alloc(e, &c->emb, (size_t)cfg->max_batch * D) |
+        dev_alloc(e, &c->resid, M * D) | dev_alloc(e, &c->xb, M * D) |
+        dev_alloc(e, &c->stats[0], M * 2 * (2 * D / 256)) |
+        dev_alloc(e, &c->stats[1], M * 2 * (2 * D / 256)) |
+        dev_alloc(e, &c->emb, (size_t)cfg->max_batch * D) |
         dev_alloc(e, &c->emb_bf16, (size_t)cfg->max_batch * D) |
         dev_alloc(e, &c->pix_stage,
                   (size_t)cfg->max_batch * cfg->image_h * cfg->image_w * cfg->channels);
@@ -491,13 +532,20 @@ extern "C" int vitk_set_weight(vitk_handle h, const char* name_c, const float* h
     if (li < 0 || li >= (int)h->layers.size()) { e.set("layer index out of range: %s", name.c_str()); return 1; }
     LayerW& L = h->layers[li];
     std::string rest = name.substr(dot + 1);
+    // Tensors that take part in the LayerNorm fold are kept on the host until finalize.
+    auto host_part = [&](std::vector<float>& dst, size_t total, size_t off, size_t cnt) {
+      if (dst.size() != total) dst.assign(total, 0.f);
+      memcpy(dst.data() + off, host, cnt * sizeof(float));
+      L.dirty = true;
+      return 0;
+    };
     auto qkv_part = [&](int part, bool is_w) {
       if (is_w) {
         if (!shape_is(shape, ndim, {D, D})) return bad_shape();
-        return upload_bf16(e, L.w_qkv + (size_t)part * D * D, host, D * D);
+        return host_part(L.h_wqkv, (size_t)3 * D * D, (size_t)part * D * D, (size_t)D * D);
       }
       if (!shape_is(shape, ndim, {D})) return bad_shape();
-      return upload_f32(e, L.b_qkv + (size_t)part * D, host, D);
+      return host_part(L.h_bqkv, (size_t)3 * D, (size_t)part * D, (size_t)D);
     };
     auto mat = [&](__nv_bfloat16* dst, int64_t r, int64_t c) {
       if (!shape_is(shape, ndim, {r, c})) return bad_shape();
@@ -507,6 +555,10 @@ extern "C" int vitk_set_weight(vitk_handle h, const char* name_c, const float* h
       if (!shape_is(shape, ndim, {n})) return bad_shape();
       return upload_f32(e, dst, host, n);
     };
+    auto hvec = [&](std::vector<float>& dst, int64_t n) {
+      if (!shape_is(shape, ndim, {n})) return bad_shape();
+      return host_part(dst, (size_t)n, 0, (size_t)n);
+    };
     if (rest == "attention.attention.query.weight") rc = qkv_part(0, true);
     else if (rest == "attention.attention.query.bias") rc = qkv_part(0, false);
     else if (rest == "attention.attention.key.weight") rc = qkv_part(1, true);
@@ -515,12 +567,14 @@ extern "C" int vitk_set_weight(vitk_handle h, const char* name_c, const float* h
     else if (rest == "attention.attention.value.bias") rc = qkv_part(2, false);
     else if (rest == "attention.output.dense.weight") rc = mat(L.w_o, D, D);
     else if (rest == "attention.output.dense.bias") rc = vec(L.b_o, D);
-    else if (rest == "layernorm_before.weight") rc = vec(L.ln1_g, D);
-    else if (rest == "layernorm_before.bias") rc = vec(L.ln1_b, D);
-    else if (rest == "layernorm_after.weight") rc = vec(L.ln2_g, D);
-    else if (rest == "layernorm_after.bias") rc = vec(L.ln2_b, D);
-    else if (rest == "intermediate.dense.weight") rc = mat(L.w_fc1, F, D);
-    else if (rest == "intermediate.dense.bias") rc = vec(L.b_fc1, F);
+    else if (rest == "layernorm_before.weight") rc = hvec(L.h_ln1g, D);
+    else if (rest == "layernorm_before.bias") rc = hvec(L.h_ln1b, D);
+    else if (rest == "layernorm_after.weight") rc = hvec(L.h_ln2g, D);
+    else if (rest == "layernorm_after.bias") rc = hvec(L.h_ln2b, D);
+    else if (rest == "intermediate.dense.weight") {
+      if (!shape_is(shape, ndim, {F, D})) return bad_shape();
+      rc = host_part(L.h_wfc1, (size_t)F * D, 0, (size_t)F * D);
+    } else if (rest == "intermediate.dense.bias") rc = hvec(L.h_bfc1, F);
     else if (rest == "output.dense.weight") rc = mat(L.w_fc2, D, F);
     else if (rest == "output.dense.bias") rc = vec(L.b_fc2, D);
     else { e.set("vitk_set_weight: unknown key %s", name.c_str()); return 1; }
@@ -552,6 +606,55 @@ extern "C" int vitk_finalize_weights(vitk_handle h) {
       tab[(size_t)t * D + j] =
           h->h_pos[(size_t)t * D + j] + (t == 0 ? h->h_cls[j] : h->h_pbias[j]);
   if (upload_f32(e, h->posb, tab.data(), tab.size())) return 1;
+  // LayerNorm fold (gemm_sm100.cuh): W' = bf16(gamma∘W), c1[n] = sum_k W'[n,k] (from the
+  // rounded values, so a constant row cancels exactly), c2[n] = b[n] + sum_k beta[k] W[n,k].
+  for (size_t li = 0; li < h->layers.size(); ++li) {
+    LayerW& L = h->layers[li];
+    if (!L.dirty) continue;
+    const size_t Dz = (size_t)D, Fz = (size_t)h->F;
+    if (L.h_wqkv.size() != 3 * Dz * Dz || L.h_bqkv.size() != 3 * Dz || L.h_wfc1.size() != Fz * Dz ||
+        L.h_bfc1.size() != Fz || L.h_ln1g.size() != Dz || L.h_ln1b.size() != Dz ||
+        L.h_ln2g.size() != Dz || L.h_ln2b.size() != Dz) {
+      e.set("vitk_finalize_weights: layer %zu changed since the last finalize — re-supply its "
+            "layernorm_before/after, query/key/value and intermediate.dense tensors", li);
+      return 1;
+    }
+    auto fold = [&](const std::vector<float>& W, const std::vector<float>& b,
+                    const std::vector<float>& g, const std::vector<float>& be, size_t rows,
+                    __nv_bfloat16* w_dev, float* c1_dev, float* c2_dev) {
+      std::vector<uint16_t> wq(rows * Dz);
+      std::vector<float> c1(rows), c2(rows);
+      for (size_t n = 0; n < rows; ++n) {
+        double s1 = 0, s2 = 0;
+        const float* wr = W.data() + n * Dz;
+        for (size_t k = 0; k < Dz; ++k) {
+          const uint16_t q = f32_to_bf16_bits(g[k] * wr[k]);
+          wq[n * Dz + k] = q;
+          uint32_t u = (uint32_t)q << 16;
+          float f;
+          memcpy(&f, &u, 4);
+          s1 += f;
+          s2 += (double)be[k] * wr[k];
+        }
+        c1[n] = (float)s1;
+        c2[n] = (float)(s2 + b[n]);
+      }
+      if (cudaMemcpy(w_dev, wq.data(), wq.size() * 2, cudaMemcpyHostToDevice) != cudaSuccess ||
+          cudaMemcpy(c1_dev, c1.data(), rows * 4, cudaMemcpyHostToDevice) != cudaSuccess ||
+          cudaMemcpy(c2_dev, c2.data(), rows * 4, cudaMemcpyHostToDevice) != cudaSuccess) {
+        e.set("vitk_finalize_weights: upload failed: %s", cudaGetErrorString(cudaGetLastError()));
+        return 1;
+      }
+      return 0;
+    };
+    if (fold(L.h_wqkv, L.h_bqkv, L.h_ln1g, L.h_ln1b, 3 * Dz, L.w_qkv, L.c1_qkv, L.b_qkv) ||
+        fold(L.h_wfc1, L.h_bfc1, L.h_ln2g, L.h_ln2b, Fz, L.w_fc1, L.c1_fc1, L.b_fc1))
+      return 1;
+    // the big host copies are only needed for the fold
+    std::vector<float>().swap(L.h_wqkv);
+    std::vector<float>().swap(L.h_wfc1);
+    L.dirty = false;
+  }
   h->finalized = true;
   return 0;
 }
@@ -571,6 +674,7 @@ int get_maps(vitk_ctx* c, int n, BatchMaps** out) {
   int rc = tmap_operand(e, &m.a_patch, c->act, M, c->Kp, GEMM_BM) |
            tmap_operand(e, &m.a_act, c->act, M, D, GEMM_BM) |
            tmap_operand(e, &m.a_h, c->hbuf, M, F, GEMM_BM) |
+           tmap_operand(e, &m.a_xb, c->xb, M, D, GEMM_BM) |
            tmap_output(e, &m.c_resid, c->resid, M, D, false) |
            tmap_output(e, &m.c_qkv, c->qkv, M, 3 * D, true) |
            tmap_output(e, &m.c_h, c->hbuf, M, F, true) |
@@ -596,28 +700,45 @@ int forward_chunk(vitk_ctx* c, const void* pix, int fmt, int n, float* emb_f32,
   GemmParams gp{};
   gp.M = M; gp.N = D; gp.K = c->Kp;
   gp.table = c->posb; gp.table_rows = c->S;
-  if (launch_gemm(e, EPI_TABLE_F32, mp->a_patch, c->tm_patch, mp->c_resid, gp, st)) return 1;
-  c->launches += 2;
+  if (launch_gemm(e, EPI_TABLE_F32, mp->a_patch, c->tm_patch, mp->c_resid, mp->c_resid, gp, st))
+    return 1;
+  // bf16 copy + row statistics of the embedded tokens: inputs of layer 0's folded LayerNorm
+  const int parts = c->stat_parts;
+  const long long sstride = 2LL * parts;
+  if (launch_rowstats(e, c->resid, c->xb, c->stats[0], M, D, parts, st)) return 1;
+  c->launches += 3;
   const int epi_fc1 = cfg.gelu_tanh ? EPI_BIAS_GELUT_BF16 : EPI_BIAS_GELU_BF16;
-  for (auto& L : c->layers) {
-    // (a5.1) LN1 -> (a5.2) fused QKV GEMM -> (a5.3) attention -> (a5.4) out-proj + residual
-    if (launch_layernorm(e, c->resid, L.ln1_g, L.ln1_b, c->act, M, D, cfg.ln_eps, st)) return 1;
+  const size_t nl = c->layers.size();
+  for (size_t li = 0; li < nl; ++li) {
+    LayerW& L = c->layers[li];
+    // (a5.1+a5.2) LN1 folded into the fused QKV GEMM: A = raw residual (bf16), stats[0]
     GemmParams q{};
-    q.M = M; q.N = 3 * D; q.K = D; q.bias = L.b_qkv;
-    if (launch_gemm(e, EPI_BIAS_BF16, mp->a_act, L.tm_qkv, mp->c_qkv, q, st)) return 1;
+    q.M = M; q.N = 3 * D; q.K = D; q.bias = L.b_qkv; q.c1 = L.c1_qkv;
+    q.stats = c->stats[0]; q.stats_parts = parts; q.stats_stride = sstride;
+    q.inv_d = 1.0f / D; q.eps = cfg.ln_eps;
+    if (launch_gemm(e, EPI_BIAS_BF16, mp->a_xb, L.tm_qkv, mp->c_qkv, mp->c_qkv, q, st)) return 1;
+    // (a5.3) attention
     if (launch_attention(e, mp->att_q, mp->att_kv, mp->att_o, n, c->S, cfg.heads, st)) return 1;
+    // (a5.4) out-proj + residual; epilogue also emits the bf16 copy and LN2's row sums
     GemmParams o{};
-    o.M = M; o.N = D; o.K = D; o.bias = L.b_o; o.resid = c->resid; o.ldr = D;
-    if (launch_gemm(e, EPI_BIAS_RESID_F32, mp->a_act, L.tm_o, mp->c_resid, o, st)) return 1;
-    // (a5.1) LN2 -> (a5.5) fc1 + GELU -> fc2 + residual
-    if (launch_layernorm(e, c->resid, L.ln2_g, L.ln2_b, c->act, M, D, cfg.ln_eps, st)) return 1;
+    o.M = M; o.N = D; o.K = D; o.bias = L.b_o;
+    o.xb = c->xb; o.xb_ld = D; o.stats_out = c->stats[1]; o.stats_out_stride = sstride;
+    if (launch_gemm(e, EPI_BIAS_RESID_F32, mp->a_act, L.tm_o, mp->c_resid, mp->c_resid, o, st))
+      return 1;
+    // (a5.1+a5.5) LN2 folded into fc1 + GELU, then fc2 + residual (+ next layer's LN1 inputs)
     GemmParams f1{};
-    f1.M = M; f1.N = F; f1.K = D; f1.bias = L.b_fc1;
-    if (launch_gemm(e, epi_fc1, mp->a_act, L.tm_fc1, mp->c_h, f1, st)) return 1;
+    f1.M = M; f1.N = F; f1.K = D; f1.bias = L.b_fc1; f1.c1 = L.c1_fc1;
+    f1.stats = c->stats[1]; f1.stats_parts = parts; f1.stats_stride = sstride;
+    f1.inv_d = 1.0f / D; f1.eps = cfg.ln_eps;
+    if (launch_gemm(e, epi_fc1, mp->a_xb, L.tm_fc1, mp->c_h, mp->c_h, f1, st)) return 1;
     GemmParams f2{};
-    f2.M = M; f2.N = D; f2.K = F; f2.bias = L.b_fc2; f2.resid = c->resid; f2.ldr = D;
-    if (launch_gemm(e, EPI_BIAS_RESID_F32, mp->a_h, L.tm_fc2, mp->c_resid, f2, st)) return 1;
-    c->launches += 7;
+    f2.M = M; f2.N = D; f2.K = F; f2.bias = L.b_fc2;
+    if (li + 1 < nl) {  // nobody reads the copy / sums after the last layer
+      f2.xb = c->xb; f2.xb_ld = D; f2.stats_out = c->stats[0]; f2.stats_out_stride = sstride;
+    }
+    if (launch_gemm(e, EPI_BIAS_RESID_F32, mp->a_h, L.tm_fc2, mp->c_resid, mp->c_resid, f2, st))
+      return 1;
+    c->launches += 5;
   }
   // (a6) final LN on the CLS rows only, (a7) row normalisation
   const int blocks = (n + 3) / 4;
@@ -792,7 +913,7 @@ extern "C" int vitk_knn_vote(vitk_handle h, const float* q_dev, int n, int k, in
     return 1;
   GemmParams gp{};
   gp.M = n; gp.N = m; gp.K = d;
-  if (launch_gemm(e, EPI_F32, ta, h->tm_bank, tc, gp, st)) return 1;
+  if (launch_gemm(e, EPI_F32, ta, h->tm_bank, tc, tc, gp, st)) return 1;
   knn_candidates_kernel<<<(n + 3) / 4, 128, 0, st>>>(h->knn_scores, ld, h->bank_sqnorm, n, m, kc,
                                                      metric, h->knn_cand);
   CK(e, cudaGetLastError());
@@ -811,25 +932,68 @@ namespace {
 thread_local Err g_op_err;
 }
 
+namespace {
+int op_gemm_common(const void* a, const void* w, void* out, int M, int N, int K, int epi,
+                   const float* bias, const float* c1, const float* stats, int stats_parts,
+                   float ln_eps, const float* resid, void* xb_out, float* stats_out,
+                   const float* table, int table_rows, void* stream) {
+  Err& e = g_op_err;
+  auto fail = [&]() { g_create_error = e.msg; return 1; };
+  if (K < GEMM_BK || K % GEMM_BK) {
+    e.set("vitk_op_gemm: K=%d must be a positive multiple of %d", K, GEMM_BK);
+    return fail();
+  }
+  if (M < 1 || N < 4 || N % 4) { e.set("vitk_op_gemm: bad shape M=%d N=%d", M, N); return fail(); }
+  const bool bf16_out = epi == EPI_BIAS_BF16 || epi == EPI_BIAS_GELU_BF16 || epi == EPI_BIAS_GELUT_BF16;
+  if (bf16_out && N % 8) { e.set("vitk_op_gemm: bf16 output needs N %% 8 == 0"); return fail(); }
+  if ((bf16_out || epi == EPI_BIAS_RESID_F32) && !bias) { e.set("vitk_op_gemm: bias required"); return fail(); }
+  if (epi == EPI_BIAS_RESID_F32 && !resid) { e.set("vitk_op_gemm: resid required"); return fail(); }
+  CUtensorMap ta, tb, tc, tr;
+  GemmParams p{};
+  p.M = M; p.N = N; p.K = K; p.bias = bias; p.table = table;
+  p.table_rows = table_rows > 0 ? table_rows : 1;
+  if (stats) {
+    p.c1 = c1; p.stats = stats; p.stats_parts = stats_parts; p.stats_stride = 2LL * stats_parts;
+    p.inv_d = 1.0f / K; p.eps = ln_eps;
+  }
+  if (epi == EPI_BIAS_RESID_F32) {
+    p.xb = reinterpret_cast<__nv_bfloat16*>(xb_out); p.xb_ld = N;
+    p.stats_out = stats_out; p.stats_out_stride = 2LL * (2 * ((N + 255) / 256));
+  }
+  int rc = tmap_operand(e, &ta, a, M, K, GEMM_BM) || tmap_operand(e, &tb, w, N, K, 256) ||
+           tmap_output(e, &tc, out, M, N, bf16_out);
+  if (!rc) {
+    if (epi == EPI_BIAS_RESID_F32 && resid != out)
+      rc = tmap_output(e, &tr, const_cast<float*>(resid), M, N, false);
+    else
+      tr = tc;
+  }
+  rc = rc || launch_gemm(e, epi, ta, tb, tc, tr, p, reinterpret_cast<cudaStream_t>(stream));
+  if (rc) return fail();
+  return 0;
+}
+}  // namespace
+
 extern "C" int vitk_op_gemm(const void* a, const void* w, void* out, int M, int N, int K, int epi,
                             const float* bias, const float* resid, const float* table,
                             int table_rows, void* stream) {
+  return op_gemm_common(a, w, out, M, N, K, epi, bias, nullptr, nullptr, 0, 0.f, resid, nullptr,
+                        nullptr, table, table_rows, stream);
+}
+
+extern "C" int vitk_op_gemm_fused(const void* a, const void* w, void* out, int M, int N, int K,
+                                  int epi, const float* bias, const float* c1, const float* stats,
+                                  int stats_parts, float ln_eps, const float* resid, void* xb_out,
+                                  float* stats_out, void* stream) {
+  return op_gemm_common(a, w, out, M, N, K, epi, bias, c1, stats, stats_parts, ln_eps, resid, xb_out,
+                        stats_out, nullptr, 1, stream);
+}
+
+extern "C" int vitk_op_rowstats(const float* x, void* xb, float* stats, int rows, int d, int parts,
+                                void* stream) {
   Err& e = g_op_err;
-  if (K < GEMM_BK || K % GEMM_BK) {
-    e.set("vitk_op_gemm: K=%d must be a positive multiple of %d", K, GEMM_BK);
-    g_create_error = e.msg;
-    return 1;
-  }
-  if (M < 1 || N < 4 || N % 4) { e.set("vitk_op_gemm: bad shape M=%d N=%d", M, N); g_create_error = e.msg; return 1; }
-  const bool bf16_out = epi == EPI_BIAS_BF16 || epi == EPI_BIAS_GELU_BF16 || epi == EPI_BIAS_GELUT_BF16;
-  if (bf16_out && N % 8) { e.set("vitk_op_gemm: bf16 output needs N %% 8 == 0"); g_create_error = e.msg; return 1; }
-  CUtensorMap ta, tb, tc;
-  GemmParams p{};
-  p.M = M; p.N = N; p.K = K; p.bias = bias; p.resid = resid; p.ldr = N; p.table = table;
-  p.table_rows = table_rows > 0 ? table_rows : 1;
-  int rc = tmap_operand(e, &ta, a, M, K, GEMM_BM) || tmap_operand(e, &tb, w, N, K, 256) ||
-           tmap_output(e, &tc, out, M, N, bf16_out) ||
-           launch_gemm(e, epi, ta, tb, tc, p, reinterpret_cast<cudaStream_t>(stream));
+  int rc = launch_rowstats(e, x, reinterpret_cast<__nv_bfloat16*>(xb), stats, rows, d, parts,
+                           reinterpret_cast<cudaStream_t>(stream));
   if (rc) g_create_error = e.msg;
   return rc;
 }
