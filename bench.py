@@ -151,7 +151,7 @@ def run_reference(args, rank):
 # ---------------------------------------------------------------------------------------------
 # our arm
 # ---------------------------------------------------------------------------------------------
-def time_kernels(v, lib, torch, n_frames):
+def time_kernels(v, lib, torch, n_frames, warm=3, reps=10):
     """Per-kernel device times at the workload's shapes (CUDA events, launches back to back on
     the current stream after warm-up; operands >> L2)."""
     from vit_research_b200._lib import ptr, stream_ptr
@@ -190,9 +190,8 @@ def time_kernels(v, lib, torch, n_frames):
     }
     res = {}
     for name, (fn, flops) in ops.items():
-        for _ in range(3):
+        for _ in range(warm):
             assert fn() == 0, lib.vitk_last_error(None)
-        reps = 10
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         torch.cuda.synchronize()
         e0.record()

@@ -7,4 +7,5 @@ import bench
 
 lib = v.load()
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 256
-print(json.dumps(bench.time_kernels(v, lib, torch, n), indent=1))
+warm = int(os.environ.get("KB_WARM", "3")); reps = int(os.environ.get("KB_REPS", "10"))
+print(json.dumps(bench.time_kernels(v, lib, torch, n, warm, reps), indent=1))

@@ -64,15 +64,22 @@ constexpr int GEMM_EPI_WARPS = 8;
 constexpr int GEMM_STAGING_BYTES = 4096;  // 32 rows x 128 B per buffer
 constexpr int GEMM_MAX_SMEM = 232448;     // 227 KB opt-in limit per CTA
 
-template <int BN>
+// CG = CTAs cooperating on one tcgen05.mma (cta_group): 1, or 2 = a CTA pair computing a
+// 256 x BN tile — each CTA stages its own 128 rows of A and only HALF of the W tile, which
+// halves the shared-memory fill + operand-read traffic per FLOP (the 1-CTA kernel is bound by
+// it: 16 KB A + 32 KB W filled and 12 KB read per 128 MMA cycles > 128 B/clk/SM).
+template <int BN, int CG>
 struct GemmCfg {
-  static constexpr int kStages = (BN == 256) ? 4 : 6;
+  static constexpr int kStages = (CG == 2) ? 5 : ((BN == 256) ? 4 : 6);
   static constexpr int kABytes = GEMM_BM * GEMM_BK * 2;  // 16 KB
-  static constexpr int kBBytes = BN * GEMM_BK * 2;
+  static constexpr int kBRows = BN / CG;                 // W rows this CTA stages
+  static constexpr int kBBytes = kBRows * GEMM_BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStagingBytes = GEMM_EPI_WARPS * GEMM_STAGING_BYTES;  // 32 KB
+  // the CTA pair's smaller W stage leaves room to double-buffer the epilogue staging tiles
+  static constexpr int kStagingBufs = (CG == 2) ? 2 : 1;
+  static constexpr int kStagingBytes = GEMM_EPI_WARPS * kStagingBufs * GEMM_STAGING_BYTES;
   static constexpr int kVecBytes = 2 * BN * 4;   // c1 | c2 (bias) of the current N tile
-  static constexpr int kBarBytes = 256;          // 2*kStages + 4 + 8 mbarriers + TMEM slot
+  static constexpr int kBarBytes = 256;          // 2*kStages + 4 + 16 mbarriers + TMEM slot
   static constexpr int kCarveBytes = kStages * kStageBytes + kStagingBytes + kVecBytes + kBarBytes;
   // the carve-up starts at the first 1024-B boundary of the dynamic window; ask for as much
   // alignment slack as the 227 KB limit leaves (the kernel traps if it is ever insufficient)
@@ -96,12 +103,12 @@ __device__ __forceinline__ uint32_t dynamic_smem_size() {
   return v;
 }
 
-template <int BN, int EPI>
+template <int BN, int EPI, int CG>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmR,
                     const GemmParams p) {
-  using Cfg = GemmCfg<BN>;
+  using Cfg = GemmCfg<BN, CG>;
   constexpr int kStages = Cfg::kStages;
   constexpr int CH = EpiTraits<EPI>::kChunkCols;
 
@@ -123,15 +130,20 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint64_t* empty_bar = bars + kStages;
   uint64_t* tfull_bar = bars + 2 * kStages;
   uint64_t* tempty_bar = bars + 2 * kStages + 2;
-  uint64_t* resid_bar = bars + 2 * kStages + 4;  // [GEMM_EPI_WARPS]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4 + GEMM_EPI_WARPS);
+  uint64_t* resid_bar = bars + 2 * kStages + 4;  // [GEMM_EPI_WARPS][2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4 + 2 * GEMM_EPI_WARPS);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
+  // work unit = one (CG*128) x BN output tile; CTA `rank` of the pair owns its 128-row half
+  const uint32_t rank = (CG == 2) ? cluster_ctarank() : 0u;
+  const int first_unit = blockIdx.x / CG;
+  const int unit_stride = gridDim.x / CG;
   const int m_tiles = (p.M + GEMM_BM - 1) / GEMM_BM;
+  const int m_units = (m_tiles + CG - 1) / CG;
   const int n_tiles = (p.N + BN - 1) / BN;
-  const int num_tiles = m_tiles * n_tiles;
+  const int num_tiles = m_units * n_tiles;
   const int num_kb = p.K / GEMM_BK;
 
   if (warp == 0 && lane == 0) {
@@ -147,14 +159,18 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull_bar[i], 1);
-      mbar_init(&tempty_bar[i], GEMM_EPI_WARPS);
+      mbar_init(&tempty_bar[i], GEMM_EPI_WARPS * CG);  // the leader also waits for its peer
     }
-    for (int i = 0; i < GEMM_EPI_WARPS; ++i) mbar_init(&resid_bar[i], 1);
+    for (int i = 0; i < 2 * GEMM_EPI_WARPS; ++i) mbar_init(&resid_bar[i], 1);
     fence_mbar_init();
   }
-  if (warp == 2) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+  if (warp == 2) {
+    if constexpr (CG == 2) tmem_alloc_cg2<Cfg::kTmemCols>(tmem_slot);
+    else tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+  }
   tc_fence_before_sync();
-  __syncthreads();
+  if constexpr (CG == 2) cluster_sync_all();  // peer barriers initialised before anyone signals
+  else __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -163,27 +179,40 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
+      for (int tile = first_unit; tile < num_tiles; tile += unit_stride) {
+        const int m_blk = (tile / n_tiles) * CG + (int)rank, n_blk = tile % n_tiles;
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1u);
-          mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
-          tma_load_2d(sA + stage * Cfg::kABytes, &tmA, &full_bar[stage], kb * GEMM_BK,
-                      m_blk * GEMM_BM);
-          tma_load_2d(sB + stage * Cfg::kBBytes, &tmB, &full_bar[stage], kb * GEMM_BK, n_blk * BN);
+          uint8_t* a_dst = sA + stage * Cfg::kABytes;
+          uint8_t* b_dst = sB + stage * Cfg::kBBytes;
+          if constexpr (CG == 2) {
+            // both CTAs' bytes complete on the leader's barrier; the W tile is split by rows
+            if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::kStageBytes);
+            tma_load_2d_cg2(a_dst, &tmA, &full_bar[stage], kb * GEMM_BK, m_blk * GEMM_BM);
+            tma_load_2d_cg2(b_dst, &tmB, &full_bar[stage], kb * GEMM_BK,
+                            n_blk * BN + (int)rank * Cfg::kBRows);
+          } else {
+            mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+            tma_load_2d(a_dst, &tmA, &full_bar[stage], kb * GEMM_BK, m_blk * GEMM_BM);
+            // the W tensor maps carry 128-row boxes (shared with the CTA-pair kernel)
+#pragma unroll
+            for (int h = 0; h < BN / 128; ++h)
+              tma_load_2d(b_dst + h * 128 * GEMM_BK * 2, &tmB, &full_bar[stage], kb * GEMM_BK,
+                          n_blk * BN + h * 128);
+          }
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
       }
     }
   } else if (warp == 1) {
     // ------------------------------ MMA issuer ------------------------------
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16_f32(GEMM_BM, BN, false, false);
+    if (lane == 0 && rank == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16_f32(GEMM_BM * CG, BN, false, false);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int tile = first_unit; tile < num_tiles; tile += unit_stride) {
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1u);
         tc_fence_after_sync();
         const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BN);
@@ -195,13 +224,21 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
           for (int k = 0; k < GEMM_BK / 16; ++k) {
             // advance 16 bf16 = 32 B along K inside the 128 B swizzle atom: +2 in the >>4 field
-            umma_bf16_ss(d_tmem, da + static_cast<uint64_t>(2 * k), db + static_cast<uint64_t>(2 * k),
-                         idesc, (kb | k) != 0 ? 1u : 0u);
+            if constexpr (CG == 2)
+              umma_bf16_ss_cg2(d_tmem, da + static_cast<uint64_t>(2 * k),
+                               db + static_cast<uint64_t>(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+            else
+              umma_bf16_ss(d_tmem, da + static_cast<uint64_t>(2 * k),
+                           db + static_cast<uint64_t>(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
           }
-          umma_commit(&empty_bar[stage]);  // smem stage reusable once these MMAs retire
+          // smem stage reusable (in both CTAs of a pair) once these MMAs retire
+          if constexpr (CG == 2) umma_commit_cg2(&empty_bar[stage]);
+          else umma_commit(&empty_bar[stage]);
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
-        umma_commit(&tfull_bar[acc]);  // accumulator complete
+        // accumulator complete (each CTA of a pair holds its own 128 rows)
+        if constexpr (CG == 2) umma_commit_cg2(&tfull_bar[acc]);
+        else umma_commit(&tfull_bar[acc]);
         if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
       }
     }
@@ -213,12 +250,28 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int et = threadIdx.x - 128;   // 0..255 among the epilogue threads
     constexpr int kColsPerWarp = BN / 2;
     constexpr int kChunks = kColsPerWarp / CH;
-    uint8_t* sbuf = sStage + ew * GEMM_STAGING_BYTES;
+    constexpr int NBUF = Cfg::kStagingBufs;  // staging tiles per warp (2: stores/loads overlap math)
+    uint8_t* swarp = sStage + ew * NBUF * GEMM_STAGING_BYTES;
+    uint64_t* rbar = resid_bar + ew * 2;
     int acc = 0;
     uint32_t acc_phase = 0;
-    uint32_t resid_phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
+    uint32_t cc = 0;      // chunks processed by this warp: staging buffer = cc % NBUF
+    uint32_t rphase = 0;  // bit b: phase of rbar[b]
+    // EPI_BIAS_RESID_F32: lane 0 asks TMA for the residual chunk (tile_, c_) into buffer b_
+    auto resid_request = [&](int tile_, int c_, uint32_t b_) {
+      if (tile_ >= num_tiles) return;
+      const int r0_ = ((tile_ / n_tiles) * CG + (int)rank) * GEMM_BM + q * 32;
+      const int c0_ = (tile_ % n_tiles) * BN + half * kColsPerWarp + c_ * CH;
+      if (c0_ < p.N && r0_ < p.M) {
+        mbar_arrive_expect_tx(&rbar[b_], GEMM_STAGING_BYTES);
+        tma_load_2d(swarp + b_ * GEMM_STAGING_BYTES, &tmR, &rbar[b_], c0_, r0_);
+      }
+    };
+    if constexpr (EPI == EPI_BIAS_RESID_F32) {
+      if (lane == 0) resid_request(first_unit, 0, 0);
+    }
+    for (int tile = first_unit; tile < num_tiles; tile += unit_stride) {
+      const int m_blk = (tile / n_tiles) * CG + (int)rank, n_blk = tile % n_tiles;
       const int row0 = m_blk * GEMM_BM + q * 32;
       const int row = row0 + lane;
       if constexpr (EpiTraits<EPI>::kUsesVec) {
@@ -249,27 +302,27 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
       const float nmr = -mean * rstd;  // y = rstd*acc + nmr*c1 + c2
       float st_s = 0.f, st_ss = 0.f;   // EPI_BIAS_RESID_F32: this warp's partial row statistics
-      if constexpr (EPI == EPI_BIAS_RESID_F32) {
-        // residual chunk 0 -> staging while the accumulator is still being produced
-        if (lane == 0) {
-          tma_store_wait_read<0>();
-          const int col0 = n_blk * BN + half * kColsPerWarp;
-          if (col0 < p.N && row0 < p.M) {
-            mbar_arrive_expect_tx(&resid_bar[ew], GEMM_STAGING_BYTES);
-            tma_load_2d(sbuf, &tmR, &resid_bar[ew], col0, row0);
-          }
-        }
-      }
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after_sync();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
                              static_cast<uint32_t>(acc * BN + half * kColsPerWarp);
 #pragma unroll 1
-      for (int c = 0; c < kChunks; ++c) {
+      for (int c = 0; c < kChunks; ++c, ++cc) {
+        const uint32_t b = cc & (NBUF - 1);
+        uint8_t* sbuf = swarp + b * GEMM_STAGING_BYTES;
         const int lcol0 = half * kColsPerWarp + c * CH;  // column inside the N tile
         const int col0 = n_blk * BN + lcol0;
         const bool live = col0 < p.N && row0 < p.M;      // warp-uniform
         if constexpr (CH == 32) {
+          if constexpr (EPI == EPI_BIAS_RESID_F32 && NBUF == 2) {
+            // prefetch the NEXT chunk's residual into the other buffer: its previous occupant
+            // (the store committed one chunk ago) must have been read out of smem first
+            if (lane == 0) {
+              tma_store_wait_read<0>();
+              if (c + 1 < kChunks) resid_request(tile, c + 1, b ^ 1u);
+              else resid_request(tile + unit_stride, 0, b ^ 1u);
+            }
+          }
           uint32_t r[32];
           tmem_ld_32x32b_x32(t_row + c * CH, r);
           tmem_ld_wait();
@@ -278,16 +331,16 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
           if constexpr (EPI == EPI_BIAS_RESID_F32) {
             if (live) {
-              mbar_wait(&resid_bar[ew], resid_phase);
-              resid_phase ^= 1u;
+              mbar_wait(&rbar[b], (rphase >> b) & 1u);
+              rphase ^= 1u << b;
             }
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-              const float4 b = *reinterpret_cast<const float4*>(sVec + BN + lcol0 + 4 * j);
+              const float4 bb = *reinterpret_cast<const float4*>(sVec + BN + lcol0 + 4 * j);
               float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
               if (live) x = *reinterpret_cast<const float4*>(sbuf + lane * 128 + ((j ^ (lane & 7)) << 4));
-              v[4 * j + 0] += x.x + b.x; v[4 * j + 1] += x.y + b.y;
-              v[4 * j + 2] += x.z + b.z; v[4 * j + 3] += x.w + b.w;
+              v[4 * j + 0] += x.x + bb.x; v[4 * j + 1] += x.y + bb.y;
+              v[4 * j + 2] += x.z + bb.z; v[4 * j + 3] += x.w + bb.w;
             }
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
@@ -319,10 +372,10 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               }
             }
           }
-          // the TMA store that last read the staging tile must have finished reading it
-          // (the residual epilogue already waited before loading the residual into it)
+          // the TMA store that last read this staging tile must have finished reading it (the
+          // residual epilogue already waited before the residual was loaded into it)
           if constexpr (EPI != EPI_BIAS_RESID_F32) {
-            if (lane == 0) tma_store_wait_read<0>();
+            if (lane == 0) tma_store_wait_read<NBUF - 1>();
             __syncwarp();
           }
 #pragma unroll
@@ -344,9 +397,9 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
             const float4 a = *reinterpret_cast<const float4*>(sVec + lcol0 + 4 * j);
-            const float4 b = *reinterpret_cast<const float4*>(sVec + BN + lcol0 + 4 * j);
+            const float4 bb = *reinterpret_cast<const float4*>(sVec + BN + lcol0 + 4 * j);
             const float av[4] = {a.x, a.y, a.z, a.w};
-            const float bv[4] = {b.x, b.y, b.z, b.w};
+            const float bv[4] = {bb.x, bb.y, bb.z, bb.w};
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
               float x = fmaf(rstd, v[4 * j + i], fmaf(nmr, av[i], bv[i]));
@@ -355,7 +408,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               v[4 * j + i] = x;
             }
           }
-          if (lane == 0) tma_store_wait_read<0>();
+          if (lane == 0) tma_store_wait_read<NBUF - 1>();
           __syncwarp();
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
@@ -371,23 +424,22 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           // all TMEM reads of this accumulator stage are done: hand it back to the MMA warp
           tc_fence_before_sync();
           __syncwarp();
-          if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+          if (lane == 0) {
+            if constexpr (CG == 2) mbar_arrive_cluster(&tempty_bar[acc], 0);
+            else mbar_arrive(&tempty_bar[acc]);
+          }
         }
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) {
           if (live) tma_store_2d(&tmC, sbuf, col0, row0);
           tma_store_commit();
-          if constexpr (EPI == EPI_BIAS_RESID_F32) {
-            // next residual chunk into the same buffer once the store has drained it
-            if (c + 1 < kChunks) {
-              tma_store_wait_read<0>();
-              const int ncol0 = col0 + CH;
-              if (ncol0 < p.N && row0 < p.M) {
-                mbar_arrive_expect_tx(&resid_bar[ew], GEMM_STAGING_BYTES);
-                tma_load_2d(sbuf, &tmR, &resid_bar[ew], ncol0, row0);
-              }
-            }
+          if constexpr (EPI == EPI_BIAS_RESID_F32 && NBUF == 1) {
+            // single staging tile: the next residual chunk can only be requested once this
+            // store has drained it
+            tma_store_wait_read<0>();
+            if (c + 1 < kChunks) resid_request(tile, c + 1, 0);
+            else resid_request(tile + unit_stride, 0, 0);
           }
         }
       }
@@ -403,10 +455,12 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   }
 
   tc_fence_before_sync();
-  __syncthreads();
+  if constexpr (CG == 2) cluster_sync_all();  // no CTA of the pair exits while its peer may signal it
+  else __syncthreads();
   if (warp == 2) {
     tc_fence_after_sync();
-    tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+    if constexpr (CG == 2) tmem_dealloc_cg2<Cfg::kTmemCols>(tmem_base);
+    else tmem_dealloc<Cfg::kTmemCols>(tmem_base);
   }
 }
 

@@ -7,6 +7,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <set>
@@ -138,22 +139,54 @@ int num_sms() {
   return g_num_sms;
 }
 
-template <int BN, int EPI>
+template <int BN, int EPI, int CG>
 int launch_gemm_t(Err& e, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& c,
                   const CUtensorMap& r, const GemmParams& p, cudaStream_t st) {
-  auto kern = gemm_bf16_tn_kernel<BN, EPI>;
+  auto kern = gemm_bf16_tn_kernel<BN, EPI, CG>;
+  using Cfg = GemmCfg<BN, CG>;
   static bool attr_set = false;
   if (!attr_set) {
-    CK(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               GemmCfg<BN>::kSmemBytes));
+    CK(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
     attr_set = true;
   }
   const int m_tiles = (p.M + GEMM_BM - 1) / GEMM_BM, n_tiles = (p.N + BN - 1) / BN;
-  const int tiles = m_tiles * n_tiles;
-  const int grid = tiles < num_sms() ? tiles : num_sms();
-  kern<<<grid, GEMM_THREADS, GemmCfg<BN>::kSmemBytes, st>>>(a, b, c, r, p);
-  CK(e, cudaGetLastError());
+  const int units = ((m_tiles + CG - 1) / CG) * n_tiles;
+  const int slots = num_sms() / CG;  // CTA pairs occupy the two SMs of a TPC
+  const int grid = CG * (units < slots ? units : slots);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid, 1, 1);
+  cfg.blockDim = dim3(GEMM_THREADS, 1, 1);
+  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CG;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  CK(e, cudaLaunchKernelEx(&cfg, kern, a, b, c, r, p));
   return 0;
+}
+
+// 0 = choose (CTA pair whenever there are at least two 128-row blocks), 1 / 2 = forced
+// (VITK_GEMM_CG environment variable; the parity tests run both).
+int gemm_cta_group(int M) {
+  static int forced = -1;
+  if (forced < 0) {
+    const char* v = getenv("VITK_GEMM_CG");
+    forced = v ? atoi(v) : 0;
+    if (forced != 1 && forced != 2) forced = 0;
+  }
+  if (forced) return forced;
+  return M > GEMM_BM ? 2 : 1;
+}
+
+template <int EPI>
+int launch_gemm_e(Err& e, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& c,
+                  const CUtensorMap& r, const GemmParams& p, cudaStream_t st) {
+  return gemm_cta_group(p.M) == 2 ? launch_gemm_t<256, EPI, 2>(e, a, b, c, r, p, st)
+                                  : launch_gemm_t<256, EPI, 1>(e, a, b, c, r, p, st);
 }
 
 // `r` is the tensor map the residual epilogue loads from (pass `c` when the residual is
@@ -173,12 +206,12 @@ int launch_gemm(Err& e, int epi, const CUtensorMap& a, const CUtensorMap& b, con
     return 1;
   }
   switch (epi) {
-    case EPI_BIAS_BF16: return launch_gemm_t<256, EPI_BIAS_BF16>(e, a, b, c, r, p, st);
-    case EPI_BIAS_GELU_BF16: return launch_gemm_t<256, EPI_BIAS_GELU_BF16>(e, a, b, c, r, p, st);
-    case EPI_BIAS_GELUT_BF16: return launch_gemm_t<256, EPI_BIAS_GELUT_BF16>(e, a, b, c, r, p, st);
-    case EPI_BIAS_RESID_F32: return launch_gemm_t<256, EPI_BIAS_RESID_F32>(e, a, b, c, r, p, st);
-    case EPI_TABLE_F32: return launch_gemm_t<256, EPI_TABLE_F32>(e, a, b, c, r, p, st);
-    case EPI_F32: return launch_gemm_t<256, EPI_F32>(e, a, b, c, r, p, st);
+    case EPI_BIAS_BF16: return launch_gemm_e<EPI_BIAS_BF16>(e, a, b, c, r, p, st);
+    case EPI_BIAS_GELU_BF16: return launch_gemm_e<EPI_BIAS_GELU_BF16>(e, a, b, c, r, p, st);
+    case EPI_BIAS_GELUT_BF16: return launch_gemm_e<EPI_BIAS_GELUT_BF16>(e, a, b, c, r, p, st);
+    case EPI_BIAS_RESID_F32: return launch_gemm_e<EPI_BIAS_RESID_F32>(e, a, b, c, r, p, st);
+    case EPI_TABLE_F32: return launch_gemm_e<EPI_TABLE_F32>(e, a, b, c, r, p, st);
+    case EPI_F32: return launch_gemm_e<EPI_F32>(e, a, b, c, r, p, st);
   }
   e.set("gemm: unknown epilogue %d", epi);
   return 1;
@@ -447,10 +480,10 @@ extern "C" int vitk_create(const vitk_config* cfg, int device, vitk_handle* out)
           dev_alloc(e, &L.b_qkv, 3 * D) | dev_alloc(e, &L.b_o, D) | dev_alloc(e, &L.b_fc1, F) |
           dev_alloc(e, &L.b_fc2, D) | dev_alloc(e, &L.c1_qkv, 3 * D) | dev_alloc(e, &L.c1_fc1, F);
     if (rc) return fail(c);
-    rc |= tmap_operand(e, &L.tm_qkv, L.w_qkv, 3 * D, D, 256) |
-          tmap_operand(e, &L.tm_o, L.w_o, D, D, 256) |
-          tmap_operand(e, &L.tm_fc1, L.w_fc1, F, D, 256) |
-          tmap_operand(e, &L.tm_fc2, L.w_fc2, D, F, 256);
+    rc |= tmap_operand(e, &L.tm_qkv, L.w_qkv, 3 * D, D, 128) |
+          tmap_operand(e, &L.tm_o, L.w_o, D, D, 128) |
+          tmap_operand(e, &L.tm_fc1, L.w_fc1, F, D, 128) |
+          tmap_operand(e, &L.tm_fc2, L.w_fc2, D, F, 128);
     if (rc) return fail(c);
   }
   const size_t M = (size_t)cfg->max_batch * c->S;
@@ -471,7 +504,7 @@ extern "C" int vitk_create(const vitk_config* cfg, int device, vitk_handle* out)
         dev_alloc(e, &c->res_label, (size_t)cfg->max_batch) |
         dev_alloc(e, &c->res_counts, (size_t)cfg->max_batch * KNN_MAX_CLASSES);
   if (rc) return fail(c);
-  if (tmap_operand(e, &c->tm_patch, c->w_patch, D, Kp, 256)) return fail(c);
+  if (tmap_operand(e, &c->tm_patch, c->w_patch, D, Kp, 128)) return fail(c);
   if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess) {
     e.set("cudaStreamCreate failed");
     return fail(c);
@@ -856,7 +889,7 @@ extern "C" int vitk_bank_set(vitk_handle h, const float* rows_host, int m, int d
     }
   }
   CK(e, cudaMemcpy(h->bank_labels, lab.data(), (size_t)m * 4, cudaMemcpyHostToDevice));
-  if (tmap_operand(e, &h->tm_bank, h->bank_bf16, m, d, 256)) return 1;
+  if (tmap_operand(e, &h->tm_bank, h->bank_bf16, m, d, 128)) return 1;
   h->bank_m = m;
   h->bank_d = d;
   h->bank_classes = labels_host ? n_classes : 0;
@@ -960,7 +993,7 @@ int op_gemm_common(const void* a, const void* w, void* out, int M, int N, int K,
     p.xb = reinterpret_cast<__nv_bfloat16*>(xb_out); p.xb_ld = N;
     p.stats_out = stats_out; p.stats_out_stride = 2LL * (2 * ((N + 255) / 256));
   }
-  int rc = tmap_operand(e, &ta, a, M, K, GEMM_BM) || tmap_operand(e, &tb, w, N, K, 256) ||
+  int rc = tmap_operand(e, &ta, a, M, K, GEMM_BM) || tmap_operand(e, &tb, w, N, K, 128) ||
            tmap_output(e, &tc, out, M, N, bf16_out);
   if (!rc) {
     if (epi == EPI_BIAS_RESID_F32 && resid != out)
