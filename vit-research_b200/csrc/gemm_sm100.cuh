@@ -63,6 +63,7 @@ constexpr int GEMM_THREADS = 384;
 constexpr int GEMM_EPI_WARPS = 8;
 constexpr int GEMM_STAGING_BYTES = 4096;  // 32 rows x 128 B per buffer
 constexpr int GEMM_MAX_SMEM = 232448;     // 227 KB opt-in limit per CTA
+constexpr int GEMM_MAX_STAT_PARTS = 8;    // LN-fold partial (sum, sumsq) pairs per row: even, <= 8
 
 // CG = CTAs cooperating on one tcgen05.mma (cta_group): 1, or 2 = a CTA pair computing a
 // 256 x BN tile — each CTA stages its own 128 rows of A and only HALF of the W tile, which
@@ -288,16 +289,42 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       float mean = 0.f, rstd = 1.f;
       if constexpr (EpiTraits<EPI>::kOutBf16) {
         if (p.stats != nullptr && row < p.M) {
-          const float2* sp = reinterpret_cast<const float2*>(p.stats + (size_t)row * p.stats_stride);
+          // all partial pairs in flight at once (a dependent add per load would serialise
+          // stats_parts L2 round trips on the in-order issue path)
+          const float4* sp = reinterpret_cast<const float4*>(p.stats + (size_t)row * p.stats_stride);
+          float4 t[GEMM_MAX_STAT_PARTS / 2];
+#pragma unroll
+          for (int i = 0; i < GEMM_MAX_STAT_PARTS / 2; ++i)
+            t[i] = (2 * i < p.stats_parts) ? __ldg(sp + i) : make_float4(0.f, 0.f, 0.f, 0.f);
           float s = 0.f, ss = 0.f;
-          for (int i = 0; i < p.stats_parts; ++i) {
-            const float2 t = __ldg(sp + i);
-            s += t.x;
-            ss += t.y;
+#pragma unroll
+          for (int i = 0; i < GEMM_MAX_STAT_PARTS / 2; ++i) {
+            s += t[i].x + t[i].z;
+            ss += t[i].y + t[i].w;
           }
           mean = s * p.inv_d;
           const float var = fmaxf(fmaf(-mean, mean, ss * p.inv_d), 0.f);
           rstd = rsqrtf(var + p.eps);
+        }
+      }
+      // pull the NEXT tile's per-row sums and per-column vectors towards L1 while this tile is
+      // processed (their L2 latency otherwise sits on the epilogue's critical path every tile)
+      if constexpr (EpiTraits<EPI>::kUsesVec) {
+        const int nt = tile + unit_stride;
+        if (nt < num_tiles) {
+          const int nn = (nt % n_tiles) * BN + et;
+          if (nn < p.N) {
+            prefetch_l1(p.bias + nn);
+            if (p.stats != nullptr) prefetch_l1(p.c1 + nn);
+          }
+          if constexpr (EpiTraits<EPI>::kOutBf16) {
+            const int nrow = ((nt / n_tiles) * CG + (int)rank) * GEMM_BM + q * 32 + lane;
+            if (p.stats != nullptr && nrow < p.M) {
+              const float* np_ = p.stats + (size_t)nrow * p.stats_stride;
+              prefetch_l1(np_);
+              prefetch_l1(np_ + 2 * p.stats_parts - 1);
+            }
+          }
         }
       }
       const float nmr = -mean * rstd;  // y = rstd*acc + nmr*c1 + c2

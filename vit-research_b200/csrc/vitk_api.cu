@@ -197,8 +197,10 @@ int launch_gemm(Err& e, int epi, const CUtensorMap& a, const CUtensorMap& b, con
     e.set("gemm: K=%d must be a positive multiple of %d", p.K, GEMM_BK);
     return 1;
   }
-  if (p.stats != nullptr && (p.c1 == nullptr || p.stats_parts < 1)) {
-    e.set("gemm: LayerNorm fold needs c1 and stats_parts >= 1");
+  if (p.stats != nullptr && (p.c1 == nullptr || p.stats_parts < 2 || p.stats_parts % 2 ||
+                             p.stats_parts > GEMM_MAX_STAT_PARTS || p.stats_stride % 4)) {
+    e.set("gemm: LayerNorm fold needs c1, an even stats_parts in [2,%d] and 16-byte aligned rows",
+          GEMM_MAX_STAT_PARTS);
     return 1;
   }
   if (epi == EPI_BIAS_RESID_F32 && p.xb != nullptr && (p.N % 32 != 0 || p.xb_ld % 8 != 0)) {
