@@ -49,7 +49,8 @@ struct AttnParams {
   int S;        // tokens per frame
   int heads;
   int frames;
-  int nblk;     // query blocks per (frame, head): 1 if S <= 128 else 2
+  int q_rows;   // queries per frame that are needed (== S, or fewer: last-layer CLS shortcut)
+  int nblk;     // query blocks per (frame, head): 1 if q_rows <= 128 else 2
   float scale_log2e;  // (1/sqrt(d)) * log2(e)
 };
 
@@ -78,7 +79,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   const int head = fh % p.heads;
   const int D = p.heads * ATT_D;
   const int S = p.S, SK = L.sk;
-  const int rows_valid = min(128, S - blk * 128);   // query rows of this block that exist
+  const int rows_valid = min(128, p.q_rows - blk * 128);  // query rows of this block needed
   const bool warp_active = warp * 32 < rows_valid;  // warps whose 32 rows are all padding idle
 
   if (tid == 0) {

@@ -55,12 +55,76 @@ __device__ __forceinline__ void warp_argbest(float& k, int& i) {
   }
 }
 
-// Candidate selection on the bf16-GEMM scores.  One warp per query; lane l owns bank rows
+// Order-preserving map float -> uint32 (larger float <=> larger integer); 0 is below every
+// real value and marks "no row".
+__device__ __forceinline__ uint32_t float_order_bits(float f) {
+  const uint32_t u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+// Candidate selection, register-resident fast path (m <= 32*KPL): one warp per query, lane l
+// holds the keys of bank rows l, l+32, ... in registers.  The kc-th largest key is found by a
+// 32-step bitwise binary search (count(key >= t) via compare + warp reduce_add: no memory
+// traffic, no dependent rescans), then every row above the threshold — and rows equal to it in
+// ascending index order until kc are taken — is compacted out with ballots.  The candidate SET
+// equals the first kc rows of the (key desc, index asc) order; their order is irrelevant (the
+// re-rank sorts them).
+template <int KPL>
+__global__ void __launch_bounds__(128)
+knn_candidates_reg_kernel(const float* __restrict__ scores, int ld,
+                          const float* __restrict__ bank_sqnorm, int nq, int m, int kc, int metric,
+                          int32_t* __restrict__ cand) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp >= nq) return;
+  const float* row = scores + (size_t)warp * ld;
+  uint32_t key[KPL];
+#pragma unroll
+  for (int j = 0; j < KPL; ++j) {
+    const int i = lane + 32 * j;
+    float s = -INFINITY;
+    if (i < m) {
+      s = row[i];
+      if (metric == METRIC_L2) s = 2.0f * s - __ldg(bank_sqnorm + i);
+    }
+    key[j] = i < m ? float_order_bits(s) : 0u;
+  }
+  uint32_t t = 0;
+#pragma unroll 1
+  for (int bit = 31; bit >= 0; --bit) {
+    const uint32_t tt = t | (1u << bit);
+    int c = 0;
+#pragma unroll
+    for (int j = 0; j < KPL; ++j) c += key[j] >= tt ? 1 : 0;
+    c = __reduce_add_sync(0xffffffffu, c);
+    if (c >= kc) t = tt;
+  }
+  int32_t* out = cand + (size_t)warp * kc;
+  const uint32_t lt_mask = (1u << lane) - 1u;
+  int base = 0;
+#pragma unroll
+  for (int j = 0; j < KPL; ++j) {
+    const bool pr = key[j] > t;
+    const uint32_t b = __ballot_sync(0xffffffffu, pr);
+    if (pr) out[base + __popc(b & lt_mask)] = lane + 32 * j;
+    base += __popc(b);
+  }
+#pragma unroll
+  for (int j = 0; j < KPL; ++j) {
+    const bool pr = key[j] == t && t != 0u;
+    const uint32_t b = __ballot_sync(0xffffffffu, pr);
+    const int pos = base + __popc(b & lt_mask);
+    if (pr && pos < kc) out[pos] = lane + 32 * j;
+    base += __popc(b);
+  }
+}
+
+// Candidate selection, general path (any m).  One warp per query; lane l owns bank rows
 // l, l+32, ...  Each round every lane offers its best not-yet-taken row; the warp-shuffle
 // argmax picks the winner; only the winning lane rescans its rows for its next-best.
 // key = score (cosine) or 2*score - ||b||^2 (L2: larger == closer).
 __global__ void __launch_bounds__(128)
-knn_candidates_kernel(const float* __restrict__ scores, int ld, const float* __restrict__ bank_sqnorm,
+knn_candidates_scan_kernel(const float* __restrict__ scores, int ld, const float* __restrict__ bank_sqnorm,
                       int nq, int m, int kc, int metric, int32_t* __restrict__ cand) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
@@ -110,39 +174,48 @@ knn_rerank_vote_kernel(const float* __restrict__ q, const float* __restrict__ ba
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (warp >= nq) return;
-  const float* qr = q + (size_t)warp * d;
+  // Each lane owns candidate slots lane, lane+32, ... and computes their full fp32 dot /
+  // squared distance itself: no shuffles, (KNN_MAX_CAND/32) x 4 independent loads in flight per
+  // lane, and the keys land exactly where the selection below expects them.  The query row is
+  // staged in shared memory (broadcast reads).
+  extern __shared__ float knn_q_smem[];
+  float* qs = knn_q_smem + (threadIdx.x >> 5) * d;
+  for (int i = lane * 4; i < d; i += 128)
+    *reinterpret_cast<float4*>(qs + i) = *reinterpret_cast<const float4*>(q + (size_t)warp * d + i);
+  __syncwarp();
   float ck[KNN_MAX_CAND / 32];   // key (larger == better) of candidate slot lane + 32*s
   int ci[KNN_MAX_CAND / 32];
+  const float* br[KNN_MAX_CAND / 32];
+  float acc[KNN_MAX_CAND / 32];
 #pragma unroll
-  for (int s = 0; s < KNN_MAX_CAND / 32; ++s) { ck[s] = -INFINITY; ci[s] = 0x7fffffff; }
-  for (int c = 0; c < kc; ++c) {
-    const int bi = cand[(size_t)warp * kc + c];
-    float acc = 0.f;
-    if (bi >= 0 && bi < m) {
-      const float* br = bank + (size_t)bi * d;
-      if (metric == METRIC_L2) {
-        for (int i = lane * 4; i < d; i += 128) {
-          float4 a = *reinterpret_cast<const float4*>(qr + i);
-          float4 b = __ldg(reinterpret_cast<const float4*>(br + i));
-          float dx = a.x - b.x, dy = a.y - b.y, dz = a.z - b.z, dw = a.w - b.w;
-          acc += (dx * dx + dy * dy) + (dz * dz + dw * dw);
-        }
-      } else {
-        for (int i = lane * 4; i < d; i += 128) {
-          float4 a = *reinterpret_cast<const float4*>(qr + i);
-          float4 b = __ldg(reinterpret_cast<const float4*>(br + i));
-          acc += (a.x * b.x + a.y * b.y) + (a.z * b.z + a.w * b.w);
-        }
-      }
-      acc = warp_sum(acc);
-      const float key = metric == METRIC_L2 ? -acc : acc;
-      if ((c & 31) == lane) {
+  for (int s = 0; s < KNN_MAX_CAND / 32; ++s) {
+    const int c = lane + 32 * s;
+    int bi = c < kc ? cand[(size_t)warp * kc + c] : -1;
+    if (bi < 0 || bi >= m) bi = -1;
+    ci[s] = bi < 0 ? 0x7fffffff : bi;
+    br[s] = bank + (size_t)(bi < 0 ? 0 : bi) * d;
+    acc[s] = 0.f;
+  }
+  const int nslots = (kc + 31) >> 5;  // warp-uniform
+#pragma unroll 2
+  for (int i = 0; i < d; i += 4) {
+    const float4 a = *reinterpret_cast<const float4*>(qs + i);
 #pragma unroll
-        for (int s = 0; s < KNN_MAX_CAND / 32; ++s)
-          if (s == (c >> 5)) { ck[s] = key; ci[s] = bi; }
+    for (int s = 0; s < KNN_MAX_CAND / 32; ++s) {
+      if (s < nslots) {
+        const float4 b = __ldg(reinterpret_cast<const float4*>(br[s] + i));
+        if (metric == METRIC_L2) {
+          const float dx = a.x - b.x, dy = a.y - b.y, dz = a.z - b.z, dw = a.w - b.w;
+          acc[s] += (dx * dx + dy * dy) + (dz * dz + dw * dw);
+        } else {
+          acc[s] += (a.x * b.x + a.y * b.y) + (a.z * b.z + a.w * b.w);
+        }
       }
     }
   }
+#pragma unroll
+  for (int s = 0; s < KNN_MAX_CAND / 32; ++s)
+    ck[s] = ci[s] == 0x7fffffff ? -INFINITY : (metric == METRIC_L2 ? -acc[s] : acc[s]);
   int cnt[KNN_MAX_CLASSES];
 #pragma unroll
   for (int j = 0; j < KNN_MAX_CLASSES; ++j) cnt[j] = 0;

@@ -100,17 +100,19 @@ int make_tmap(Err& e, CUtensorMap* m, CUtensorMapDataType dt, int rank, void* ba
 }
 
 // [rows, cols] bf16 row-major operand (A or W): box {64, box_rows}
-int tmap_operand(Err& e, CUtensorMap* m, const void* base, int rows, int cols, int box_rows) {
+int tmap_operand(Err& e, CUtensorMap* m, const void* base, int rows, int cols, int box_rows,
+                 long long pitch_elems = 0) {
   uint64_t dims[2] = {(uint64_t)cols, (uint64_t)rows};
-  uint64_t str[1] = {(uint64_t)cols * 2};
+  uint64_t str[1] = {(uint64_t)(pitch_elems ? pitch_elems : cols) * 2};
   uint32_t box[2] = {64u, (uint32_t)box_rows};
   return make_tmap(e, m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, str,
                    box);
 }
 // [rows, cols] output: 32-row boxes, 128 B wide (64 bf16 / 32 f32)
-int tmap_output(Err& e, CUtensorMap* m, void* base, int rows, int cols, bool bf16) {
+int tmap_output(Err& e, CUtensorMap* m, void* base, int rows, int cols, bool bf16,
+                long long pitch_elems = 0) {
   uint64_t dims[2] = {(uint64_t)cols, (uint64_t)rows};
-  uint64_t str[1] = {(uint64_t)cols * (bf16 ? 2u : 4u)};
+  uint64_t str[1] = {(uint64_t)(pitch_elems ? pitch_elems : cols) * (bf16 ? 2u : 4u)};
   uint32_t box[2] = {bf16 ? 64u : 32u, 32u};
   return make_tmap(e, m, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32,
                    2, base, dims, str, box);
@@ -219,8 +221,9 @@ int launch_gemm(Err& e, int epi, const CUtensorMap& a, const CUtensorMap& b, con
   return 1;
 }
 
+// q_rows > 0: only the first q_rows queries of every frame are needed (last layer: the CLS row)
 int launch_attention(Err& e, const CUtensorMap& tq, const CUtensorMap& tkv, const CUtensorMap& to,
-                     int frames, int S, int heads, cudaStream_t st) {
+                     int frames, int S, int heads, cudaStream_t st, int q_rows = 0) {
   if (S < 1 || S > 256) {
     e.set("attention: S=%d unsupported (1..256)", S);
     return 1;
@@ -236,7 +239,8 @@ int launch_attention(Err& e, const CUtensorMap& tq, const CUtensorMap& tkv, cons
   p.S = S;
   p.heads = heads;
   p.frames = frames;
-  p.nblk = S > 128 ? 2 : 1;
+  p.q_rows = q_rows > 0 && q_rows < S ? q_rows : S;
+  p.nblk = p.q_rows > 128 ? 2 : 1;
   p.scale_log2e = 0.125f * 1.4426950408889634f;  // head dim 64 -> 1/sqrt(64)
   attention_kernel<<<frames * heads * p.nblk, ATT_THREADS, L.total, st>>>(tq, tkv, to, p);
   CK(e, cudaGetLastError());
@@ -334,6 +338,8 @@ struct BatchMaps {  // tensor maps that depend on the number of frames in the ca
   CUtensorMap a_patch, a_act, a_h, a_xb;    // GEMM A operands
   CUtensorMap c_resid, c_qkv, c_h;          // GEMM outputs
   CUtensorMap att_q, att_kv, att_o;         // attention
+  // last layer, CLS rows only (row f of these maps = token 0 of frame f: pitch S*D)
+  CUtensorMap a_act_cls, a_xb_cls, a_h_cls, c_resid_cls, c_h_cls;
 };
 
 struct vitk_ctx {
@@ -353,6 +359,7 @@ struct vitk_ctx {
   __nv_bfloat16* xb = nullptr;        // bf16 copy of the residual stream (GEMM A operand)
   float *stats[2] = {nullptr, nullptr};  // per-row LayerNorm partial sums, ping-pong
   int stat_parts = 0;                 // 2 * hidden / 256
+  bool cls_only_last = true;          // VITK_FULL_LAST_LAYER=1 computes all tokens in the last layer
   float *resid = nullptr, *emb = nullptr;
   uint8_t* pix_stage = nullptr;  // device staging for vitk_embed_host_u8
   std::map<int, BatchMaps> maps;
@@ -470,6 +477,10 @@ extern "C" int vitk_create(const vitk_config* cfg, int device, vitk_handle* out)
   c->D = cfg->hidden;
   c->F = cfg->mlp;
   c->stat_parts = 2 * cfg->hidden / 256;
+  {
+    const char* v = getenv("VITK_FULL_LAST_LAYER");
+    c->cls_only_last = !(v && atoi(v) == 1);
+  }
   if (c->S > 256) { e.set("tokens per frame %d > 256 unsupported by the attention kernel", c->S); return fail(c); }
   if (c->Kp % 64) { e.set("channels*patch^2 must be a multiple of 64"); return fail(c); }
   if (cudaSetDevice(device) != cudaSuccess) { e.set("cudaSetDevice failed"); return fail(c); }
@@ -715,7 +726,12 @@ int get_maps(vitk_ctx* c, int n, BatchMaps** out) {
            tmap_output(e, &m.c_h, c->hbuf, M, F, true) |
            tmap_tokens(e, &m.att_q, c->qkv, n, c->S, 3 * D, 128) |
            tmap_tokens(e, &m.att_kv, c->qkv, n, c->S, 3 * D, sk) |
-           tmap_tokens(e, &m.att_o, c->act, n, c->S, D, 128);
+           tmap_tokens(e, &m.att_o, c->act, n, c->S, D, 128) |
+           tmap_operand(e, &m.a_act_cls, c->act, n, D, GEMM_BM, (long long)c->S * D) |
+           tmap_operand(e, &m.a_xb_cls, c->xb, n, D, GEMM_BM, (long long)c->S * D) |
+           tmap_operand(e, &m.a_h_cls, c->hbuf, n, F, GEMM_BM) |
+           tmap_output(e, &m.c_resid_cls, c->resid, n, D, false, (long long)c->S * D) |
+           tmap_output(e, &m.c_h_cls, c->hbuf, n, F, true);
   if (rc) return 1;
   *out = &c->maps.emplace(n, m).first->second;
   return 0;
@@ -752,8 +768,33 @@ int forward_chunk(vitk_ctx* c, const void* pix, int fmt, int n, float* emb_f32,
     q.stats = c->stats[0]; q.stats_parts = parts; q.stats_stride = sstride;
     q.inv_d = 1.0f / D; q.eps = cfg.ln_eps;
     if (launch_gemm(e, EPI_BIAS_BF16, mp->a_xb, L.tm_qkv, mp->c_qkv, mp->c_qkv, q, st)) return 1;
+    // Last layer: the reference reads only last_hidden_state[:,0,:] (ratt_write_clips_to_ragdb.py
+    // :148), and after the attention every remaining op is row-wise, so only the CLS query and
+    // the CLS rows of proj / MLP are computed (bit-identical for those rows).
+    const bool cls_only = (li + 1 == nl) && c->cls_only_last && c->S > 1;
     // (a5.3) attention
-    if (launch_attention(e, mp->att_q, mp->att_kv, mp->att_o, n, c->S, cfg.heads, st)) return 1;
+    if (launch_attention(e, mp->att_q, mp->att_kv, mp->att_o, n, c->S, cfg.heads, st,
+                         cls_only ? 1 : 0))
+      return 1;
+    if (cls_only) {
+      const long long pitch = (long long)c->S;
+      GemmParams o{};
+      o.M = n; o.N = D; o.K = D; o.bias = L.b_o;
+      o.xb = c->xb; o.xb_ld = pitch * D; o.stats_out = c->stats[1]; o.stats_out_stride = pitch * sstride;
+      if (launch_gemm(e, EPI_BIAS_RESID_F32, mp->a_act_cls, L.tm_o, mp->c_resid_cls, mp->c_resid_cls, o, st))
+        return 1;
+      GemmParams f1{};
+      f1.M = n; f1.N = F; f1.K = D; f1.bias = L.b_fc1; f1.c1 = L.c1_fc1;
+      f1.stats = c->stats[1]; f1.stats_parts = parts; f1.stats_stride = pitch * sstride;
+      f1.inv_d = 1.0f / D; f1.eps = cfg.ln_eps;
+      if (launch_gemm(e, epi_fc1, mp->a_xb_cls, L.tm_fc1, mp->c_h_cls, mp->c_h_cls, f1, st)) return 1;
+      GemmParams f2{};
+      f2.M = n; f2.N = D; f2.K = F; f2.bias = L.b_fc2;
+      if (launch_gemm(e, EPI_BIAS_RESID_F32, mp->a_h_cls, L.tm_fc2, mp->c_resid_cls, mp->c_resid_cls, f2, st))
+        return 1;
+      c->launches += 5;
+      continue;
+    }
     // (a5.4) out-proj + residual; epilogue also emits the bf16 copy and LN2's row sums
     GemmParams o{};
     o.M = M; o.N = D; o.K = D; o.bias = L.b_o;
@@ -949,10 +990,24 @@ extern "C" int vitk_knn_vote(vitk_handle h, const float* q_dev, int n, int k, in
   GemmParams gp{};
   gp.M = n; gp.N = m; gp.K = d;
   if (launch_gemm(e, EPI_F32, ta, h->tm_bank, tc, tc, gp, st)) return 1;
-  knn_candidates_kernel<<<(n + 3) / 4, 128, 0, st>>>(h->knn_scores, ld, h->bank_sqnorm, n, m, kc,
-                                                     metric, h->knn_cand);
+  {
+    const int blocks = (n + 3) / 4;
+    const float* sc = h->knn_scores;
+    const float* sq = h->bank_sqnorm;
+    int32_t* cd = h->knn_cand;
+    if (m <= 256) knn_candidates_reg_kernel<8><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd);
+    else if (m <= 512) knn_candidates_reg_kernel<16><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd);
+    else if (m <= 1024) knn_candidates_reg_kernel<32><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd);
+    else if (m <= 1536) knn_candidates_reg_kernel<48><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd);
+    else if (m <= 2048) knn_candidates_reg_kernel<64><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd);
+    else knn_candidates_scan_kernel<<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd);
+  }
   CK(e, cudaGetLastError());
-  knn_rerank_vote_kernel<<<(n + 3) / 4, 128, 0, st>>>(
+  if (d % 4 != 0 || (size_t)4 * d * sizeof(float) > 48 * 1024) {
+    e.set("vitk_knn_vote: d=%d must be a multiple of 4 and at most 3072", d);
+    return 1;
+  }
+  knn_rerank_vote_kernel<<<(n + 3) / 4, 128, (size_t)4 * d * sizeof(float), st>>>(
       h->knn_q, h->bank, h->bank_classes ? h->bank_labels : nullptr, h->knn_cand, n, m, d, kc, k,
       metric, h->bank_classes, idx_out, score_out, label_out, counts_out);
   CK(e, cudaGetLastError());
