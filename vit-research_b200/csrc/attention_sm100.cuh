@@ -58,7 +58,7 @@ struct AttnParams {
 // tmKV: same tensor,                          box {64, sk, 1}      (K and V)
 // tmO : 3-D map over out [frames, S, D] bf16, box {64, 128, 1}
 __global__ void __launch_bounds__(ATT_THREADS, 2)
-attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
+attention_v2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
                  const __grid_constant__ CUtensorMap tmO, const AttnParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -248,6 +248,292 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   if (warp == 1) {
     tc_fence_after_sync();
     tmem_dealloc<ATT_TMEM_COLS>(tmem_base);
+  }
+}
+
+// =============================================================================================
+// v3: persistent, warp-specialised.  One CTA per SM loops over (frame, head) units; both query
+// blocks of a unit share ONE K/V load.  Roles (384 threads):
+//   warp 0        TMA loader: Q0 | Q1 | K on kv_full[stage], V on v_full[stage]; 2 stages of 84 KB
+//   warp 1        MMA issuer: two independent per-TMEM-slot state machines, advanced by polling
+//                 (S = Q K^T when the slot is free, O = P V when that slot's P is ready)
+//   warp 2        TMEM allocator (2 slots x 256 columns: S f32 | P bf16 aliasing S | O f32)
+//   warps 4-7     softmax + epilogue of slot 0      warps 8-11  softmax + epilogue of slot 1
+// Query block b of unit j uses slot b ^ (j & 1), so the 128-row and the 69-row block alternate
+// between the two softmax warpgroups; while one group is in its exp2 loop the other group's
+// MMAs, loads and stores proceed.  v2 ran 2 independent CTAs/SM with every phase serialised
+// inside a CTA and K/V loaded twice (127 us/layer at 256 frames).
+// =============================================================================================
+constexpr int ATT3_THREADS = 384;
+constexpr int ATT3_STAGES = 2;
+
+struct Attn3SmemLayout {
+  int sk, kv_bytes, stage_bytes, off_bar, total;
+};
+__host__ __device__ inline Attn3SmemLayout attn3_smem_layout(int S) {
+  Attn3SmemLayout L;
+  L.sk = (S + 15) & ~15;
+  L.kv_bytes = ((L.sk * 128) + 1023) & ~1023;
+  L.stage_bytes = 2 * 16384 + 2 * L.kv_bytes;  // Q0 | Q1 | K | V
+  L.off_bar = ATT3_STAGES * L.stage_bytes;
+  L.total = L.off_bar + 256 + 1024;
+  return L;
+}
+
+__global__ void __launch_bounds__(ATT3_THREADS, 1)
+attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
+                 const __grid_constant__ CUtensorMap tmO, const AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  const Attn3SmemLayout L = attn3_smem_layout(p.S);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.off_bar);
+  uint64_t* kv_full = bars + 0;      // [2] stage
+  uint64_t* v_full = bars + 2;       // [2] stage
+  uint64_t* stage_empty = bars + 4;  // [2] stage, count 2 (one per softmax warpgroup)
+  uint64_t* s_full = bars + 6;       // [2] slot
+  uint64_t* p_full = bars + 8;       // [2] slot, count 4 (one per warp)
+  uint64_t* o_full = bars + 10;      // [2] slot
+  uint64_t* slot_free = bars + 12;   // [2] slot, count 4
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14);
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31;
+  const int D = p.heads * ATT_D;
+  const int S = p.S, SK = L.sk;
+  const int units = p.frames * p.heads;
+  const int nblk = p.nblk;
+
+  if (tid == 0) {
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmKV);
+    tma_prefetch_desc(&tmO);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&kv_full[i], 1);
+      mbar_init(&v_full[i], 1);
+      mbar_init(&stage_empty[i], 2);
+      mbar_init(&s_full[i], 1);
+      mbar_init(&p_full[i], 4);
+      mbar_init(&o_full[i], 1);
+      mbar_init(&slot_free[i], 4);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc<512>(tmem_slot);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------ loader ------------------------------
+    if (lane == 0) {
+      int j = 0;
+      for (int u = blockIdx.x; u < units; u += gridDim.x, ++j) {
+        const int st = j & 1;
+        const uint32_t ph = (j >> 1) & 1;
+        const int frame = u / p.heads, head = u % p.heads;
+        uint8_t* sb = smem + st * L.stage_bytes;
+        mbar_wait(&stage_empty[st], ph ^ 1u);
+        mbar_arrive_expect_tx(&kv_full[st], 16384 * nblk + SK * 128);
+        tma_load_3d(sb, &tmQ, &kv_full[st], head * ATT_D, 0, frame);
+        if (nblk == 2) tma_load_3d(sb + 16384, &tmQ, &kv_full[st], head * ATT_D, 128, frame);
+        tma_load_3d(sb + 32768, &tmKV, &kv_full[st], D + head * ATT_D, 0, frame);
+        mbar_arrive_expect_tx(&v_full[st], SK * 128);
+        tma_load_3d(sb + 32768 + L.kv_bytes, &tmKV, &v_full[st], 2 * D + head * ATT_D, 0, frame);
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------ MMA issuer ------------------------------
+    if (lane == 0) {
+      const int my_units = (units - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+      const uint32_t idesc_s = make_idesc_bf16_f32(128, (uint32_t)SK, false, false);
+      const uint32_t idesc_o = make_idesc_bf16_f32(128, ATT_D, false, true);
+      int uj[2] = {0, 0};   // unit each slot's state machine is working on
+      int phs[2] = {0, 0};  // 0: S = Q K^T is next, 1: O = P V is next
+      long long t0 = clock64();
+      while (uj[0] < my_units || uj[1] < my_units) {
+        bool progressed = false;
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+          const int j = uj[s];
+          if (j >= my_units) continue;
+          const int st = j & 1;
+          const uint32_t sph = (j >> 1) & 1, uph = j & 1;
+          const int b = s ^ (j & 1);  // query block this slot holds in unit j
+          uint8_t* sb = smem + st * L.stage_bytes;
+          const uint32_t t_slot = tmem_base + s * 256;
+          if (phs[s] == 0) {
+            if (!mbar_try_wait(&kv_full[st], sph) || !mbar_try_wait(&slot_free[s], uph ^ 1u)) continue;
+            tc_fence_after_sync();
+            if (b < nblk) {
+              const uint64_t dq = make_smem_desc_sw128(smem_u32(sb + b * 16384), 1024, 0);
+              const uint64_t dk = make_smem_desc_sw128(smem_u32(sb + 32768), 1024, 0);
+#pragma unroll
+              for (int k = 0; k < ATT_D / 16; ++k)
+                umma_bf16_ss(t_slot, dq + 2 * k, dk + 2 * k, idesc_s, k != 0 ? 1u : 0u);
+            }
+            umma_commit(&s_full[s]);
+            phs[s] = 1;
+          } else {
+            if (!mbar_try_wait(&p_full[s], uph) || !mbar_try_wait(&v_full[st], sph)) continue;
+            tc_fence_after_sync();
+            if (b < nblk) {
+              const uint32_t sv = smem_u32(sb + 32768 + L.kv_bytes);
+              for (int kk = 0; kk < SK / 16; ++kk) {
+                const uint64_t dv = make_smem_desc_sw128(sv + kk * 16 * 128, 1024, 1024);
+                umma_bf16_ts(t_slot + SK / 2, t_slot + kk * 8, dv, idesc_o, kk != 0 ? 1u : 0u);
+              }
+            }
+            umma_commit(&o_full[s]);
+            phs[s] = 0;
+            uj[s] = j + 1;
+          }
+          progressed = true;
+        }
+        if (progressed) t0 = clock64();
+        else if (clock64() - t0 > 4000000000LL) {
+          printf("vitk: attention MMA poll timeout block %d\n", (int)blockIdx.x);
+          __trap();
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ------------------------------ softmax + epilogue ------------------------------
+    const int g = (warp - 4) >> 2;  // warpgroup == TMEM slot
+    const int wq = warp & 3;        // TMEM lane quarter
+    const int r = wq * 32 + lane;   // row within the query block == TMEM lane
+    const uint32_t lane_off = static_cast<uint32_t>(wq * 32) << 16;
+    const uint32_t t_slot = tmem_base + g * 256 + lane_off;
+    const uint32_t t_o = t_slot + static_cast<uint32_t>(SK / 2);
+    int j = 0;
+    for (int u = blockIdx.x; u < units; u += gridDim.x, ++j) {
+      const int st = j & 1;
+      const uint32_t uph = j & 1;
+      const int b = g ^ (j & 1);
+      const int frame = u / p.heads, head = u % p.heads;
+      const bool blk_active = b < nblk;
+      const int rows_valid = blk_active ? min(128, p.q_rows - b * 128) : 0;
+      const bool warp_active = wq * 32 < rows_valid;
+      uint8_t* sO = smem + st * L.stage_bytes + b * 16384;  // Q_b's tile, dead after S = Q K^T
+
+      mbar_wait(&s_full[g], uph);
+      tc_fence_after_sync();
+      float sum = 0.f;
+      if (warp_active) {
+        // pass 1: row max over the S valid key columns
+        float mx = -INFINITY;
+        int c0 = 0;
+        for (; c0 + 32 <= SK; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld_32x32b_x32(t_slot + c0, v);
+          tmem_ld_wait();
+          if (c0 + 32 <= S) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if (c0 + i < S) mx = fmaxf(mx, __uint_as_float(v[i]));
+          }
+        }
+        if (c0 < SK) {
+          uint32_t v[16];
+          tmem_ld_32x32b_x16(t_slot + c0, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 16; ++i)
+            if (c0 + i < S) mx = fmaxf(mx, __uint_as_float(v[i]));
+        }
+        const float mxs = mx * p.scale_log2e;
+        // pass 2: p = exp2(s*scale - max*scale) -> bf16 pairs written over the consumed S cells
+        for (c0 = 0; c0 + 32 <= SK; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld_32x32b_x32(t_slot + c0, v);
+          tmem_ld_wait();
+          uint32_t pk[16];
+          const bool full = c0 + 32 <= S;
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            float e0 = ex2_approx(fmaf(__uint_as_float(v[2 * i]), p.scale_log2e, -mxs));
+            float e1 = ex2_approx(fmaf(__uint_as_float(v[2 * i + 1]), p.scale_log2e, -mxs));
+            if (!full) {
+              e0 = (c0 + 2 * i < S) ? e0 : 0.f;
+              e1 = (c0 + 2 * i + 1 < S) ? e1 : 0.f;
+            }
+            sum += e0 + e1;
+            pk[i] = pack_bf16x2(e0, e1);
+          }
+          tmem_st_32x32b_x16(t_slot + (c0 >> 1), pk);
+        }
+        if (c0 < SK) {
+          uint32_t v[16];
+          tmem_ld_32x32b_x16(t_slot + c0, v);
+          tmem_ld_wait();
+          uint32_t pk[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            float e0 = ex2_approx(fmaf(__uint_as_float(v[2 * i]), p.scale_log2e, -mxs));
+            float e1 = ex2_approx(fmaf(__uint_as_float(v[2 * i + 1]), p.scale_log2e, -mxs));
+            e0 = (c0 + 2 * i < S) ? e0 : 0.f;
+            e1 = (c0 + 2 * i + 1 < S) ? e1 : 0.f;
+            sum += e0 + e1;
+            pk[i] = pack_bf16x2(e0, e1);
+          }
+          tmem_st_32x32b_x8(t_slot + (c0 >> 1), pk);
+        }
+        tmem_st_wait();
+      }
+      tc_fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&p_full[g]);
+
+      mbar_wait(&o_full[g], uph);
+      tc_fence_after_sync();
+      if (warp_active) {
+        const float inv = 1.0f / sum;
+        uint32_t v0[32], v1[32];
+        tmem_ld_32x32b_x32(t_o, v0);
+        tmem_ld_32x32b_x32(t_o + 32, v1);
+        tmem_ld_wait();
+        tc_fence_before_sync();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&slot_free[g]);  // O is in registers: the slot can be refilled
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const uint32_t* src = i < 4 ? v0 + 8 * i : v1 + 8 * (i - 4);
+          uint4 o;
+          o.x = pack_bf16x2(__uint_as_float(src[0]) * inv, __uint_as_float(src[1]) * inv);
+          o.y = pack_bf16x2(__uint_as_float(src[2]) * inv, __uint_as_float(src[3]) * inv);
+          o.z = pack_bf16x2(__uint_as_float(src[4]) * inv, __uint_as_float(src[5]) * inv);
+          o.w = pack_bf16x2(__uint_as_float(src[6]) * inv, __uint_as_float(src[7]) * inv);
+          *reinterpret_cast<uint4*>(sO + r * 128 + ((i ^ (r & 7)) << 4)) = o;
+        }
+        fence_proxy_async_smem();
+      } else {
+        tc_fence_before_sync();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&slot_free[g]);
+      }
+      named_bar_sync(2 + g, 128);
+      if (wq == 0 && lane == 0) {
+        if (blk_active) {
+          // rows of idle warps hold stale Q bytes: tokens >= S are clipped by the 3-D map, and
+          // with q_rows < S (last-layer CLS shortcut) the extra rows are never read
+          tma_store_3d(&tmO, sO, head * ATT_D, b * 128, frame);
+          tma_store_commit();
+          tma_store_wait_read<0>();
+        }
+        mbar_arrive(&stage_empty[st]);
+      }
+    }
+  }
+
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after_sync();
+    tmem_dealloc<512>(tmem_base);
   }
 }
 

@@ -228,12 +228,10 @@ int launch_attention(Err& e, const CUtensorMap& tq, const CUtensorMap& tkv, cons
     e.set("attention: S=%d unsupported (1..256)", S);
     return 1;
   }
-  const AttnSmemLayout L = attn_smem_layout(S);
-  static int attr_bytes = 0;
-  if (L.total > attr_bytes) {
-    CK(e, cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               L.total));
-    attr_bytes = L.total;
+  static int version = -1;  // VITK_ATTN=2 selects the simpler non-persistent v2 kernel
+  if (version < 0) {
+    const char* v = getenv("VITK_ATTN");
+    version = (v && atoi(v) == 2) ? 2 : 3;
   }
   AttnParams p;
   p.S = S;
@@ -242,7 +240,27 @@ int launch_attention(Err& e, const CUtensorMap& tq, const CUtensorMap& tkv, cons
   p.q_rows = q_rows > 0 && q_rows < S ? q_rows : S;
   p.nblk = p.q_rows > 128 ? 2 : 1;
   p.scale_log2e = 0.125f * 1.4426950408889634f;  // head dim 64 -> 1/sqrt(64)
-  attention_kernel<<<frames * heads * p.nblk, ATT_THREADS, L.total, st>>>(tq, tkv, to, p);
+  if (version == 2) {
+    const AttnSmemLayout L = attn_smem_layout(S);
+    static int attr_bytes = 0;
+    if (L.total > attr_bytes) {
+      CK(e, cudaFuncSetAttribute(attention_v2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 L.total));
+      attr_bytes = L.total;
+    }
+    attention_v2_kernel<<<frames * heads * p.nblk, ATT_THREADS, L.total, st>>>(tq, tkv, to, p);
+  } else {
+    const Attn3SmemLayout L = attn3_smem_layout(S);
+    static int attr_bytes3 = 0;
+    if (L.total > attr_bytes3) {
+      CK(e, cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 L.total));
+      attr_bytes3 = L.total;
+    }
+    const int units = frames * heads;
+    const int grid = units < num_sms() ? units : num_sms();
+    attention_kernel<<<grid, ATT3_THREADS, L.total, st>>>(tq, tkv, to, p);
+  }
   CK(e, cudaGetLastError());
   return 0;
 }
