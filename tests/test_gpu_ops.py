@@ -116,13 +116,17 @@ def test_attention(lib, frames, S, heads):
     torch.testing.assert_close(out.float(), ref, rtol=1e-2, atol=1e-2)
 
 
-def test_attention_large_logits_are_stable(lib):
-    """Row-max subtraction: logits ~ +-60 must not overflow."""
-    frames, S, heads = 1, 197, 2
+@pytest.mark.parametrize("mult", [3.0, 8.0, 20.0])
+def test_attention_large_logits_are_stable(lib, mult):
+    """Row-max handling: logits of +-10 .. +-400 nats must neither overflow nor lose the row
+    maximum.  The kernel's one-pass fast path shifts by the max of the first 32 scores; rows whose
+    true maximum is > 100 binades above that are detected and redone with the exact two-pass
+    form — mult = 8 and 20 exercise that path, mult = 3 the boundary between the two."""
+    frames, S, heads = 2, 197, 2
     D = heads * 64
     g = torch.Generator().manual_seed(9)
     qkv = torch.randn(frames, S, 3 * D, generator=g)
-    qkv[..., : 2 * D] *= 8.0
+    qkv[..., : 2 * D] *= mult
     qkv = qkv.cuda().bfloat16()
     out = torch.empty(frames, S, D, device="cuda", dtype=torch.bfloat16)
     assert lib.vitk_op_attention(_p(qkv), _p(out), frames, S, heads, _s()) == 0

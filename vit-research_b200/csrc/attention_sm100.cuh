@@ -52,6 +52,7 @@ struct AttnParams {
   int q_rows;   // queries per frame that are needed (== S, or fewer: last-layer CLS shortcut)
   int nblk;     // query blocks per (frame, head): 1 if q_rows <= 128 else 2
   float scale_log2e;  // (1/sqrt(d)) * log2(e)
+  long long* dbg;     // developer timeline (tools/dev_attn_timeline.py): null in production
 };
 
 // tmQ : 3-D map over qkv [frames, S, 3*D] bf16, box {64, 128, 1}   (Q block)
@@ -268,14 +269,15 @@ constexpr int ATT3_THREADS = 384;
 constexpr int ATT3_STAGES = 2;
 
 struct Attn3SmemLayout {
-  int sk, kv_bytes, stage_bytes, off_bar, total;
+  int sk, kv_bytes, stage_bytes, off_o, off_bar, total;
 };
 __host__ __device__ inline Attn3SmemLayout attn3_smem_layout(int S) {
   Attn3SmemLayout L;
   L.sk = (S + 15) & ~15;
   L.kv_bytes = ((L.sk * 128) + 1023) & ~1023;
   L.stage_bytes = 2 * 16384 + 2 * L.kv_bytes;  // Q0 | Q1 | K | V
-  L.off_bar = ATT3_STAGES * L.stage_bytes;
+  L.off_o = ATT3_STAGES * L.stage_bytes;  // 2 x 16 KB output staging, one per softmax warpgroup
+  L.off_bar = L.off_o + 2 * 16384;
   L.total = L.off_bar + 256 + 1024;
   return L;
 }
@@ -295,7 +297,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   uint64_t* p_full = bars + 8;       // [2] slot, count 4 (one per warp)
   uint64_t* o_full = bars + 10;      // [2] slot
   uint64_t* slot_free = bars + 12;   // [2] slot, count 4
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14);
+  uint64_t* redo_bar = bars + 14;    // [2] slot: exact-path recomputation of S
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
@@ -316,6 +319,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       mbar_init(&p_full[i], 4);
       mbar_init(&o_full[i], 1);
       mbar_init(&slot_free[i], 4);
+      mbar_init(&redo_bar[i], 1);
     }
     fence_mbar_init();
   }
@@ -364,7 +368,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           uint8_t* sb = smem + st * L.stage_bytes;
           const uint32_t t_slot = tmem_base + s * 256;
           if (phs[s] == 0) {
-            if (!mbar_try_wait(&kv_full[st], sph) || !mbar_try_wait(&slot_free[s], uph ^ 1u)) continue;
+            if (!mbar_test_wait(&kv_full[st], sph) || !mbar_test_wait(&slot_free[s], uph ^ 1u)) continue;
             tc_fence_after_sync();
             if (b < nblk) {
               const uint64_t dq = make_smem_desc_sw128(smem_u32(sb + b * 16384), 1024, 0);
@@ -376,7 +380,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
             umma_commit(&s_full[s]);
             phs[s] = 1;
           } else {
-            if (!mbar_try_wait(&p_full[s], uph) || !mbar_try_wait(&v_full[st], sph)) continue;
+            if (!mbar_test_wait(&p_full[s], uph) || !mbar_test_wait(&v_full[st], sph)) continue;
             tc_fence_after_sync();
             if (b < nblk) {
               const uint32_t sv = smem_u32(sb + 32768 + L.kv_bytes);
@@ -407,6 +411,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     const uint32_t t_slot = tmem_base + g * 256 + lane_off;
     const uint32_t t_o = t_slot + static_cast<uint32_t>(SK / 2);
     int j = 0;
+    uint32_t redo_phase = 0;
     for (int u = blockIdx.x; u < units; u += gridDim.x, ++j) {
       const int st = j & 1;
       const uint32_t uph = j & 1;
@@ -415,39 +420,21 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       const bool blk_active = b < nblk;
       const int rows_valid = blk_active ? min(128, p.q_rows - b * 128) : 0;
       const bool warp_active = wq * 32 < rows_valid;
-      uint8_t* sO = smem + st * L.stage_bytes + b * 16384;  // Q_b's tile, dead after S = Q K^T
+      uint8_t* sO = smem + L.off_o + g * 16384;  // this warpgroup's private output staging
 
+      const bool dbg_on = p.dbg != nullptr && blockIdx.x == 0 && wq == 0 && lane == 0 && j < 16;
+      long long* dbg = p.dbg + (g * 16 + j) * 8;
+      if (dbg_on) dbg[0] = clock64();
       mbar_wait(&s_full[g], uph);
       tc_fence_after_sync();
+      if (dbg_on) dbg[1] = clock64();
       float sum = 0.f;
-      if (warp_active) {
-        // pass 1: row max over the S valid key columns
-        float mx = -INFINITY;
+      // exp2 of one 32- or 16-column chunk against the shift mxs -> bf16 pairs over the consumed
+      // S cells; accumulates the row sum.  kClamp bounds the exponent (fast path only).
+      auto exp_pass = [&](float mxs, bool clamp) {
+        float s4[4] = {0.f, 0.f, 0.f, 0.f};
         int c0 = 0;
         for (; c0 + 32 <= SK; c0 += 32) {
-          uint32_t v[32];
-          tmem_ld_32x32b_x32(t_slot + c0, v);
-          tmem_ld_wait();
-          if (c0 + 32 <= S) {
-#pragma unroll
-            for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
-          } else {
-#pragma unroll
-            for (int i = 0; i < 32; ++i)
-              if (c0 + i < S) mx = fmaxf(mx, __uint_as_float(v[i]));
-          }
-        }
-        if (c0 < SK) {
-          uint32_t v[16];
-          tmem_ld_32x32b_x16(t_slot + c0, v);
-          tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 16; ++i)
-            if (c0 + i < S) mx = fmaxf(mx, __uint_as_float(v[i]));
-        }
-        const float mxs = mx * p.scale_log2e;
-        // pass 2: p = exp2(s*scale - max*scale) -> bf16 pairs written over the consumed S cells
-        for (c0 = 0; c0 + 32 <= SK; c0 += 32) {
           uint32_t v[32];
           tmem_ld_32x32b_x32(t_slot + c0, v);
           tmem_ld_wait();
@@ -455,13 +442,15 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           const bool full = c0 + 32 <= S;
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
-            float e0 = ex2_approx(fmaf(__uint_as_float(v[2 * i]), p.scale_log2e, -mxs));
-            float e1 = ex2_approx(fmaf(__uint_as_float(v[2 * i + 1]), p.scale_log2e, -mxs));
+            float x0 = fmaf(__uint_as_float(v[2 * i]), p.scale_log2e, -mxs);
+            float x1 = fmaf(__uint_as_float(v[2 * i + 1]), p.scale_log2e, -mxs);
+            if (clamp) { x0 = fminf(x0, 100.f); x1 = fminf(x1, 100.f); }
+            float e0 = ex2_approx(x0), e1 = ex2_approx(x1);
             if (!full) {
               e0 = (c0 + 2 * i < S) ? e0 : 0.f;
               e1 = (c0 + 2 * i + 1 < S) ? e1 : 0.f;
             }
-            sum += e0 + e1;
+            s4[i & 3] += e0 + e1;
             pk[i] = pack_bf16x2(e0, e1);
           }
           tmem_st_32x32b_x16(t_slot + (c0 >> 1), pk);
@@ -473,23 +462,94 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           uint32_t pk[8];
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
-            float e0 = ex2_approx(fmaf(__uint_as_float(v[2 * i]), p.scale_log2e, -mxs));
-            float e1 = ex2_approx(fmaf(__uint_as_float(v[2 * i + 1]), p.scale_log2e, -mxs));
+            float x0 = fmaf(__uint_as_float(v[2 * i]), p.scale_log2e, -mxs);
+            float x1 = fmaf(__uint_as_float(v[2 * i + 1]), p.scale_log2e, -mxs);
+            if (clamp) { x0 = fminf(x0, 100.f); x1 = fminf(x1, 100.f); }
+            float e0 = ex2_approx(x0), e1 = ex2_approx(x1);
             e0 = (c0 + 2 * i < S) ? e0 : 0.f;
             e1 = (c0 + 2 * i + 1 < S) ? e1 : 0.f;
-            sum += e0 + e1;
+            s4[i & 3] += e0 + e1;
             pk[i] = pack_bf16x2(e0, e1);
           }
           tmem_st_32x32b_x8(t_slot + (c0 >> 1), pk);
         }
         tmem_st_wait();
+        return (s4[0] + s4[1]) + (s4[2] + s4[3]);
+      };
+      // row max over the first `upto` columns (<= S valid ones), 4 independent chains
+      auto max_pass = [&](int upto) {
+        float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        int c0 = 0;
+        for (; c0 + 32 <= SK && c0 < upto; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld_32x32b_x32(t_slot + c0, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (c0 + i < S) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(v[i]));
+        }
+        if (c0 < SK && c0 < upto) {
+          uint32_t v[16];
+          tmem_ld_32x32b_x16(t_slot + c0, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 16; ++i)
+            if (c0 + i < S) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(v[i]));
+        }
+        return fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+      };
+      // FAST PATH — one pass.  Softmax is shift invariant and bf16 / fp32 keep their relative
+      // precision at any magnitude, so the shift need not be the exact row maximum: any m0 with
+      // (max - m0)*scale inside the fp32 exponent range yields the same normalised
+      // probabilities.  m0 = max of the row's first <= 32 scores; exponents are clamped at
+      // 2^100 so nothing overflows.  A row whose true maximum lies > 100 binades above m0 (never
+      // observed on real activations) shows up as a huge / non-finite sum ...
+      bool redo = false;
+      if (warp_active) {
+        const float mxs = max_pass(32) * p.scale_log2e;
+        sum = exp_pass(mxs, true);
+        redo = !(sum < 1.0e30f);
+      }
+      if (dbg_on) dbg[2] = clock64();
+      // ... in which case the whole query block takes the EXACT PATH: S = Q K^T is recomputed
+      // into the slot (P has overwritten it) and the classic max pass + exp pass run.
+      tc_fence_before_sync();
+      if (named_bar_or(2 + g, 128, redo)) {
+        if (wq == 0 && lane == 0 && blk_active) {
+          tc_fence_after_sync();
+          uint8_t* sb = smem + st * L.stage_bytes;
+          const uint32_t idesc_s = make_idesc_bf16_f32(128, (uint32_t)SK, false, false);
+          const uint64_t dq = make_smem_desc_sw128(smem_u32(sb + b * 16384), 1024, 0);
+          const uint64_t dk = make_smem_desc_sw128(smem_u32(sb + 32768), 1024, 0);
+#pragma unroll
+          for (int k = 0; k < ATT_D / 16; ++k)
+            umma_bf16_ss(tmem_base + g * 256, dq + 2 * k, dk + 2 * k, idesc_s, k != 0 ? 1u : 0u);
+          umma_commit(&redo_bar[g]);
+        }
+        if (blk_active) {
+          mbar_wait(&redo_bar[g], redo_phase);
+          redo_phase ^= 1u;
+          tc_fence_after_sync();
+        }
+        if (warp_active) {
+          const float mxs = max_pass(SK) * p.scale_log2e;
+          sum = exp_pass(mxs, false);
+        }
       }
       tc_fence_before_sync();
       __syncwarp();
       if (lane == 0) mbar_arrive(&p_full[g]);
+      if (dbg_on) dbg[3] = clock64();
 
       mbar_wait(&o_full[g], uph);
       tc_fence_after_sync();
+      if (dbg_on) dbg[4] = clock64();
+      // O = P V has retired: this warpgroup no longer needs the stage's Q / K / V
+      if (wq == 0 && lane == 0) {
+        mbar_arrive(&stage_empty[st]);
+        tma_store_wait_read<0>();  // previous unit's store has long drained the staging tile
+      }
+      named_bar_sync(2 + g, 128);
       if (warp_active) {
         const float inv = 1.0f / sum;
         uint32_t v0[32], v1[32];
@@ -518,17 +578,17 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       named_bar_sync(2 + g, 128);
       if (wq == 0 && lane == 0) {
         if (blk_active) {
-          // rows of idle warps hold stale Q bytes: tokens >= S are clipped by the 3-D map, and
+          // rows of idle warps hold stale bytes: tokens >= S are clipped by the 3-D map, and
           // with q_rows < S (last-layer CLS shortcut) the extra rows are never read
           tma_store_3d(&tmO, sO, head * ATT_D, b * 128, frame);
           tma_store_commit();
-          tma_store_wait_read<0>();
         }
-        mbar_arrive(&stage_empty[st]);
       }
+      if (dbg_on) dbg[5] = clock64();
     }
   }
 
+  if (warp >= 4 && (warp & 3) == 0 && lane == 0) tma_store_wait_read<0>();  // before smem goes away
   tc_fence_before_sync();
   __syncthreads();
   if (warp == 2) {

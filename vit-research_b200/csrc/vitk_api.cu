@@ -221,6 +221,8 @@ int launch_gemm(Err& e, int epi, const CUtensorMap& a, const CUtensorMap& b, con
   return 1;
 }
 
+long long* g_attn_dbg = nullptr;  // developer timeline buffer (vitk_dev_attn_timeline)
+
 // q_rows > 0: only the first q_rows queries of every frame are needed (last layer: the CLS row)
 int launch_attention(Err& e, const CUtensorMap& tq, const CUtensorMap& tkv, const CUtensorMap& to,
                      int frames, int S, int heads, cudaStream_t st, int q_rows = 0) {
@@ -240,6 +242,7 @@ int launch_attention(Err& e, const CUtensorMap& tq, const CUtensorMap& tkv, cons
   p.q_rows = q_rows > 0 && q_rows < S ? q_rows : S;
   p.nblk = p.q_rows > 128 ? 2 : 1;
   p.scale_log2e = 0.125f * 1.4426950408889634f;  // head dim 64 -> 1/sqrt(64)
+  p.dbg = g_attn_dbg;
   if (version == 2) {
     const AttnSmemLayout L = attn_smem_layout(S);
     static int attr_bytes = 0;
@@ -1127,6 +1130,13 @@ extern "C" int vitk_op_attention(const void* qkv, void* out, int frames, int S, 
        launch_attention(e, tq, tkv, to, frames, S, heads, reinterpret_cast<cudaStream_t>(stream));
   if (rc) g_create_error = e.msg;
   return rc;
+}
+
+// Developer hook (not in include/vitk.h): device buffer of 2*16*8 int64 clock samples written by
+// CTA 0 of the attention kernel; pass NULL to switch the instrumentation off.
+extern "C" int vitk_dev_attn_timeline(long long* buf_dev) {
+  g_attn_dbg = buf_dev;
+  return 0;
 }
 
 extern "C" int vitk_op_patchify(const void* pixels, int fmt, void* out, int n, int C, int H, int W,

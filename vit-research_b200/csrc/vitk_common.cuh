@@ -61,6 +61,19 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+// Non-blocking probe (try_wait may suspend the thread for a hardware time slice; a loop that
+// polls several barriers must not)
+__device__ __forceinline__ bool mbar_test_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
 // Bounded wait: a protocol bug must trap, never hang the box (a hung GPU is a strike).
 // try_wait itself sleeps in hardware for a bounded time, so this loop is cheap.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
@@ -88,6 +101,20 @@ __device__ __forceinline__ void tc_fence_after_sync() {
 }
 __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads) {
   asm volatile("bar.sync %0, %1;\n" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// named barrier + OR reduction of a predicate over the participating threads
+__device__ __forceinline__ bool named_bar_or(uint32_t id, uint32_t nthreads, bool pred) {
+  uint32_t r;
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\t"
+      "setp.ne.u32 p, %3, 0;\n\t"
+      "barrier.cta.red.or.pred q, %1, %2, p;\n\t"
+      "selp.u32 %0, 1, 0, q;\n\t}\n"
+      : "=r"(r)
+      : "r"(id), "r"(nthreads), "r"((uint32_t)pred)
+      : "memory");
+  return r != 0;
 }
 
 // ----------------------------------------------------------------------------------------
@@ -188,6 +215,13 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16_f32(uint32_t M, uint32_t 
                                                            bool b_mn_major) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((a_mn_major ? 1u : 0u) << 15) |
          ((b_mn_major ? 1u : 0u) << 16) | ((N >> 3) << 17) | ((M >> 4) << 24);
+}
+// Same, but A is fp16 (A format field 0) while B stays bf16: used for P·V, where P comes out of
+// the packed-half exp2 unit as fp16 pairs.
+__host__ __device__ constexpr uint32_t make_idesc_f16a_bf16b_f32(uint32_t M, uint32_t N,
+                                                                 bool b_mn_major) {
+  return (1u << 4) | (0u << 7) | (1u << 10) | ((b_mn_major ? 1u : 0u) << 16) | ((N >> 3) << 17) |
+         ((M >> 4) << 24);
 }
 
 // D[tmem] (+)= A[smem] * B[smem]; issued by ONE thread.
@@ -353,6 +387,26 @@ __device__ __forceinline__ float ex2_approx(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
+}
+// {2^x0, 2^x1} as packed fp16 (x0 in the low half): ONE MUFU op for two exponentials.
+__device__ __forceinline__ uint32_t ex2_f16x2(float x0, float x1) {
+  uint32_t r;
+  asm("{\n\t.reg .b32 t;\n\t"
+      "cvt.rn.f16x2.f32 t, %2, %1;\n\t"
+      "ex2.approx.f16x2 %0, t;\n\t}\n"
+      : "=r"(r)
+      : "f"(x0), "f"(x1));
+  return r;
+}
+__device__ __forceinline__ float f16x2_sum(uint32_t v) {  // lo + hi in fp32
+  float a, b;
+  asm("{\n\t.reg .b16 l, h;\n\t"
+      "mov.b32 {l, h}, %2;\n\t"
+      "cvt.f32.f16 %0, l;\n\t"
+      "cvt.f32.f16 %1, h;\n\t}\n"
+      : "=f"(a), "=f"(b)
+      : "r"(v));
+  return a + b;
 }
 __device__ __forceinline__ float gelu_erf(float x) {
   const float a = fminf(fabsf(x), 6.0f);
