@@ -48,7 +48,7 @@ class ClockSampler:
                0x10: "sync_boost"}
 
     def __init__(self, device_index: int):
-        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self.samples, self.reasons, self.max_mhz, self.power = [], set(), None, []
         self._stop = threading.Event()
         self._thread = None
         try:
@@ -68,6 +68,7 @@ class ClockSampler:
         while not self._stop.is_set():
             try:
                 self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                self.power.append(self.nv.nvmlDeviceGetPowerUsage(self.h) / 1e3)
                 r = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
                 for bit, name in self.REASONS.items():
                     if r & bit:
@@ -91,8 +92,9 @@ class ClockSampler:
         if not self.samples:
             return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["unsampled"]}
         s = sorted(self.samples)
+        pw = sorted(self.power) or [0.0]
         return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
-                "samples": len(s)}
+                "samples": len(s), "power_w": round(pw[len(pw) // 2], 1)}
 
 
 # ---------------------------------------------------------------------------------------------
@@ -281,16 +283,25 @@ def run_ours(args, rank, local_rank, world):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_total = float(t.item())
 
-    # e2e: the public host-buffer API, H2D + D2H inside the timed region
-    def e2e_step(i):
-        return emb.embed_and_vote(host_frames[i % 2].numpy(), index, K_NEIGHBOURS, out=host_out)
+    # e2e: the public host-buffer STREAMING API (embed_and_vote_stream: what a user walking a
+    # frame list calls).  Every step uploads its own 256 uint8 frames from pinned host memory
+    # and downloads its embeddings + labels + neighbours inside the timed region; two steps are
+    # in flight so the copies overlap the previous / next step's forward.
+    host_out2 = tuple(torch.empty(a.shape, dtype=torch.from_numpy(a).dtype).pin_memory().numpy()
+                      for a in host_out)
+    outs = (host_out, host_out2)
 
-    for i in range(max(2, min(args.warmup, 3))):
-        e2e_step(i)
+    def e2e_run(n_steps):
+        acc = 0
+        frames_iter = (host_frames[i % 2].numpy() for i in range(n_steps))
+        for res in emb.embed_and_vote_stream(frames_iter, index, K_NEIGHBOURS, outs=outs):
+            acc += int(res[1][0])  # touch the step's result on the host
+        return acc
+
+    e2e_run(max(2, min(args.warmup, 3)))
     barrier()
     t0 = time.perf_counter()
-    for i in range(args.steps):
-        e2e_step(i)
+    e2e_run(args.steps)
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     if world > 1:

@@ -113,6 +113,18 @@ int vitk_embed_vote_host_u8(vitk_handle h, const uint8_t* frames_host, int n, in
                             float* emb_host, int32_t* label_host, int32_t* idx_host,
                             float* score_host, int32_t* counts_host);
 
+/* Streaming form of the call above for frame STREAMS — the reference's batched drivers
+ * (build_frame_store, ratt_write_clips_to_ragdb.py:197-209; extract_embeddings,
+ * smarter_generate_clips.py:69-94) walk a long frame list batch by batch.  Two batches may be in
+ * flight (slot 0 / 1): the H2D copy of batch i+1 and the D2H copy of batch i-1 overlap the
+ * forward of batch i on separate streams.  submit() returns immediately; the host output
+ * buffers (pinned for true overlap) are valid after wait(slot).  n <= max_batch per submit;
+ * k == 0 skips the vote (embeddings only; the vote outputs are then ignored). */
+int vitk_stream_submit(vitk_handle h, int slot, const uint8_t* frames_host, int n, int k, int metric,
+                       float* emb_host, int32_t* label_host, int32_t* idx_host, float* score_host,
+                       int32_t* counts_host);
+int vitk_stream_wait(vitk_handle h, int slot);
+
 /* ---- operator-level entry points (used by the parity tests, one kernel each) ----------- */
 /* C[M,N] = A[M,K] (bf16) · W[N,K]^T (bf16) with epilogue `epi` (VITK_EPI_*).
  * out is bf16 for the *_BF16 epilogues, f32 otherwise (row pitch = N elements). */

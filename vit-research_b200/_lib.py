@@ -55,6 +55,8 @@ SIGNATURES = {
     "vitk_embed": (_i, [_vp, _vp, _i, _i, _vp, _vp, _i, _vp]),
     "vitk_embed_host_u8": (_i, [_vp, _vp, _i, _vp, _i]),
     "vitk_embed_vote_host_u8": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
+    "vitk_stream_submit": (_i, [_vp, _i, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
+    "vitk_stream_wait": (_i, [_vp, _i]),
     "vitk_bank_set": (_i, [_vp, _vp, _i, _i, _vp, _i, _i]),
     "vitk_knn_vote": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "vitk_op_gemm": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _i, _vp]),

@@ -399,6 +399,16 @@ struct vitk_ctx {
   float* res_score = nullptr;
   cudaStream_t own_stream = nullptr;
   int64_t launches = 0;
+  // streaming host API (vitk_stream_submit / vitk_stream_wait): two batches in flight
+  struct StreamSlot {
+    uint8_t* pix = nullptr;
+    float *emb = nullptr, *score = nullptr;
+    int32_t *idx = nullptr, *label = nullptr, *counts = nullptr;
+    cudaEvent_t ev_h2d = nullptr, ev_done = nullptr, ev_out = nullptr;
+    bool busy = false;
+  } slots[2];
+  cudaStream_t in_stream = nullptr, out_stream = nullptr;
+  bool stream_ready = false;
 };
 
 namespace {
@@ -444,6 +454,15 @@ void free_ctx(vitk_ctx* c) {
   cudaFree(c->res_idx); cudaFree(c->res_label); cudaFree(c->res_counts); cudaFree(c->res_score);
   cudaFree(c->knn_q); cudaFree(c->knn_scores); cudaFree(c->knn_qb); cudaFree(c->knn_cand);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
+  for (auto& sl : c->slots) {
+    cudaFree(sl.pix); cudaFree(sl.emb); cudaFree(sl.score); cudaFree(sl.idx); cudaFree(sl.label);
+    cudaFree(sl.counts);
+    if (sl.ev_h2d) cudaEventDestroy(sl.ev_h2d);
+    if (sl.ev_done) cudaEventDestroy(sl.ev_done);
+    if (sl.ev_out) cudaEventDestroy(sl.ev_out);
+  }
+  if (c->in_stream) cudaStreamDestroy(c->in_stream);
+  if (c->out_stream) cudaStreamDestroy(c->out_stream);
   delete c;
 }
 
@@ -1192,5 +1211,87 @@ extern "C" int vitk_embed_vote_host_u8(vitk_handle h, const uint8_t* frames_host
                             cudaMemcpyDeviceToHost, st));
   }
   CK(e, cudaStreamSynchronize(st));
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// streaming host API: H2D of batch i+1 and D2H of batch i-1 overlap the forward of batch i
+// ------------------------------------------------------------------------------------------
+namespace {
+int stream_init(vitk_ctx* h) {
+  if (h->stream_ready) return 0;
+  Err& e = h->err;
+  const vitk_config& cfg = h->cfg;
+  const size_t mb = (size_t)cfg.max_batch;
+  for (auto& sl : h->slots) {
+    if (dev_alloc(e, &sl.pix, mb * cfg.image_h * cfg.image_w * cfg.channels) ||
+        dev_alloc(e, &sl.emb, mb * h->D) || dev_alloc(e, &sl.score, mb * 64) ||
+        dev_alloc(e, &sl.idx, mb * 64) || dev_alloc(e, &sl.label, mb) ||
+        dev_alloc(e, &sl.counts, mb * KNN_MAX_CLASSES))
+      return 1;
+    CK(e, cudaEventCreateWithFlags(&sl.ev_h2d, cudaEventDisableTiming));
+    CK(e, cudaEventCreateWithFlags(&sl.ev_done, cudaEventDisableTiming));
+    CK(e, cudaEventCreateWithFlags(&sl.ev_out, cudaEventDisableTiming));
+  }
+  CK(e, cudaStreamCreateWithFlags(&h->in_stream, cudaStreamNonBlocking));
+  CK(e, cudaStreamCreateWithFlags(&h->out_stream, cudaStreamNonBlocking));
+  h->stream_ready = true;
+  return 0;
+}
+}  // namespace
+
+extern "C" int vitk_stream_submit(vitk_handle h, int slot, const uint8_t* frames_host, int n, int k,
+                                  int metric, float* emb_host, int32_t* label_host,
+                                  int32_t* idx_host, float* score_host, int32_t* counts_host) {
+  if (!h) return 1;
+  Err& e = h->err;
+  if (!h->finalized) { e.set("vitk_stream_submit: weights not finalized"); return 1; }
+  if (slot < 0 || slot > 1) { e.set("vitk_stream_submit: slot must be 0 or 1"); return 1; }
+  if (!frames_host || !emb_host || n < 1 || n > h->cfg.max_batch) {
+    e.set("vitk_stream_submit: need 1 <= n <= max_batch (%d) frames per submit", h->cfg.max_batch);
+    return 1;
+  }
+  const bool vote = k > 0;
+  if (vote && (h->bank_m == 0 || k > 64 || h->bank_d != h->D)) {
+    e.set("vitk_stream_submit: k=%d needs a bank of width %d and k <= 64", k, h->D);
+    return 1;
+  }
+  CK(e, cudaSetDevice(h->device));
+  if (stream_init(h)) return 1;
+  vitk_ctx::StreamSlot& sl = h->slots[slot];
+  if (sl.busy) { e.set("vitk_stream_submit: slot %d still in flight (call vitk_stream_wait)", slot); return 1; }
+  const size_t fb = pixel_bytes_per_frame(h->cfg, PIX_U8_NHWC);
+  const int nc = h->bank_classes > 0 ? h->bank_classes : 1;
+  CK(e, cudaMemcpyAsync(sl.pix, frames_host, (size_t)n * fb, cudaMemcpyHostToDevice, h->in_stream));
+  CK(e, cudaEventRecord(sl.ev_h2d, h->in_stream));
+  cudaStream_t st = h->own_stream;
+  CK(e, cudaStreamWaitEvent(st, sl.ev_h2d, 0));
+  if (forward_chunk(h, sl.pix, PIX_U8_NHWC, n, sl.emb, nullptr, 1, st)) return 1;
+  if (vote && vitk_knn_vote(h, sl.emb, n, k, metric, 0, sl.idx, sl.score, sl.label, sl.counts, st))
+    return 1;
+  CK(e, cudaEventRecord(sl.ev_done, st));
+  cudaStream_t so = h->out_stream;
+  CK(e, cudaStreamWaitEvent(so, sl.ev_done, 0));
+  CK(e, cudaMemcpyAsync(emb_host, sl.emb, (size_t)n * h->D * 4, cudaMemcpyDeviceToHost, so));
+  if (vote) {
+    if (label_host) CK(e, cudaMemcpyAsync(label_host, sl.label, (size_t)n * 4, cudaMemcpyDeviceToHost, so));
+    if (idx_host) CK(e, cudaMemcpyAsync(idx_host, sl.idx, (size_t)n * k * 4, cudaMemcpyDeviceToHost, so));
+    if (score_host) CK(e, cudaMemcpyAsync(score_host, sl.score, (size_t)n * k * 4, cudaMemcpyDeviceToHost, so));
+    if (counts_host) CK(e, cudaMemcpyAsync(counts_host, sl.counts, (size_t)n * nc * 4, cudaMemcpyDeviceToHost, so));
+  }
+  CK(e, cudaEventRecord(sl.ev_out, so));
+  sl.busy = true;
+  return 0;
+}
+
+extern "C" int vitk_stream_wait(vitk_handle h, int slot) {
+  if (!h) return 1;
+  Err& e = h->err;
+  if (slot < 0 || slot > 1) { e.set("vitk_stream_wait: slot must be 0 or 1"); return 1; }
+  vitk_ctx::StreamSlot& sl = h->slots[slot];
+  if (!sl.busy) return 0;
+  CK(e, cudaSetDevice(h->device));
+  sl.busy = false;
+  CK(e, cudaEventSynchronize(sl.ev_out));
   return 0;
 }

@@ -218,6 +218,51 @@ class ViTEmbedder:
                                                ptr(counts)), self.handle, "vitk_embed_vote_host_u8")
         return emb, label, idx, score, counts
 
+    def embed_and_vote_stream(self, batches, index=None, k: int = 25, outs=None):
+        """Streaming form of embed_and_vote for long frame lists (the reference's batched
+        drivers: build_frame_store, ratt_write_clips_to_ragdb.py:197-209).  `batches` yields
+        uint8 (n<=max_batch,H,W,C) arrays (pinned for true copy/compute overlap); results are
+        yielded in order as (emb, label, idx, score, counts) host arrays, with two batches in
+        flight: the upload of batch i+1 and the download of batch i-1 overlap the forward of
+        batch i.  index=None (or k=0) skips the vote.  `outs`: optional pair of preallocated
+        output tuples, reused alternately (valid until the next-but-one result is produced)."""
+        g = self.geometry
+        k = int(k) if index is not None else 0
+        nc = max(index.n_classes, 1) if index is not None else 1
+        metric = index.metric if index is not None else 0
+        pending = []  # (slot, frames_ref, out, n)
+
+        def finish():
+            slot, _keep, out, n = pending.pop(0)
+            check(self.lib.vitk_stream_wait(self.handle, slot), self.handle, "vitk_stream_wait")
+            emb, label, idx, score, counts = out
+            return emb[:n], label[:n], idx[:n], score[:n], counts[:n]
+
+        for i, frames_np in enumerate(batches):
+            frames_np = np.ascontiguousarray(frames_np)
+            if frames_np.dtype != np.uint8 or frames_np.ndim != 4 or \
+                    frames_np.shape[1:] != (g.image_h, g.image_w, g.channels):
+                raise ValueError(f"frames {frames_np.shape}/{frames_np.dtype} do not match uint8 "
+                                 f"(N,{g.image_h},{g.image_w},{g.channels})")
+            n = frames_np.shape[0]
+            slot = i & 1
+            if len(pending) == 2:
+                yield finish()
+            if outs is not None:
+                out = outs[slot]
+            else:
+                kk = max(k, 1)
+                out = (np.empty((n, g.hidden), np.float32), np.empty((n,), np.int32),
+                       np.empty((n, kk), np.int32), np.empty((n, kk), np.float32),
+                       np.empty((n, nc), np.int32))
+            emb, label, idx, score, counts = out
+            check(self.lib.vitk_stream_submit(self.handle, slot, ptr(frames_np), n, k, metric,
+                                              ptr(emb), ptr(label), ptr(idx), ptr(score), ptr(counts)),
+                  self.handle, "vitk_stream_submit")
+            pending.append((slot, frames_np, out, n))
+        while pending:
+            yield finish()
+
     # ---- HF-style call: vit_model(pixel_values=...).last_hidden_state[:,0,:] ---------------
     def __call__(self, pixel_values=None, **_):
         """Returns an object whose .last_hidden_state is (N,1,hidden): only the CLS row exists
