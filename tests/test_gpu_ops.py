@@ -164,3 +164,118 @@ def test_bad_arguments_fail_loudly(lib):
     assert lib.vitk_op_gemm(_p(a), _p(a), _p(o), 128, 256, 100, 5, None, None, None, 1, _s()) != 0
     assert b"K=100" in lib.vitk_last_error(None)
     assert lib.vitk_op_attention(_p(a), _p(o), 1, 300, 1, _s()) != 0
+
+
+# ---------------------------------------------------------------------------------------------
+# fused forms the forward actually runs
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("M,N,K,epi", [(300, 768, 768, 0), (197 * 16, 3072, 768, 1), (200, 2048, 1024, 0),
+                                       (129, 2304, 768, 0), (1, 768, 768, 1)])
+def test_layernorm_folded_gemm(lib, M, N, K, epi):
+    """LN(x) @ W^T + b (-> gelu) computed as the GEMM of the RAW rows against gamma-scaled weights
+    with the per-row (mean, rstd) and per-column (c1, c2) applied in the epilogue
+    (HF modeling_vit.py:325-346) vs torch layer_norm -> linear in fp32."""
+    g = torch.Generator().manual_seed(M + N + K + epi)
+    dev = "cuda:0"
+    x = (torch.randn(M, K, generator=g) * 2 + 0.3).to(dev)
+    gm = (torch.randn(K, generator=g) * 0.3 + 1).to(dev)
+    bt = (torch.randn(K, generator=g) * 0.2).to(dev)
+    W = (torch.randn(N, K, generator=g) * 0.05).to(dev)
+    b = torch.randn(N, generator=g).to(dev)
+    parts = 2 * K // 256
+    xb = torch.empty(M, K, device=dev, dtype=torch.bfloat16)
+    stats = torch.full((M, parts, 2), float("nan"), device=dev)
+    assert lib.vitk_op_rowstats(_p(x), _p(xb), _p(stats), M, K, parts, _s()) == 0
+    Wf = (W * gm).bfloat16()
+    c1 = Wf.float().sum(1).contiguous()
+    c2 = (b + W @ bt).contiguous()
+    out = torch.full((M, N), float("nan"), device=dev, dtype=torch.bfloat16)
+    rc = lib.vitk_op_gemm_fused(_p(xb), _p(Wf), _p(out), M, N, K, epi, _p(c2), _p(c1), _p(stats), parts,
+                                1e-12, None, None, None, _s())
+    torch.cuda.synchronize()
+    assert rc == 0, lib.vitk_last_error(None)
+    ref = torch.nn.functional.layer_norm(x, (K,), gm, bt, 1e-12) @ W.t() + b
+    if epi == 1:
+        ref = torch.nn.functional.gelu(ref)
+    # bf16 rounding of the raw rows, of gamma*W and of the output
+    torch.testing.assert_close(out.float(), ref, rtol=2e-2, atol=3e-2)
+    assert torch.equal(xb, x.bfloat16())
+    sref = torch.stack([x.sum(1), (x * x).sum(1)], 1)
+    torch.testing.assert_close(stats[:, 0, :], sref, rtol=1e-5, atol=1e-3)
+    assert (stats[:, 1:, :] == 0).all()
+
+
+@pytest.mark.parametrize("M,N,K,inplace", [(300, 768, 768, True), (300, 768, 768, False),
+                                           (197 * 16, 768, 3072, True), (333, 1024, 1024, True),
+                                           (1, 768, 768, True)])
+def test_residual_gemm_emits_copy_and_row_sums(lib, M, N, K, inplace):
+    """out = acc + bias + resid (TMA-loaded residual, in place or not), bf16 copy == bf16(out),
+    per-row partial (sum, sumsq) per 128 columns of out (HF modeling_vit.py:337,343-346)."""
+    g = torch.Generator().manual_seed(M * 3 + N + K)
+    dev = "cuda:0"
+    A = (torch.randn(M, K, generator=g) * 0.5).to(dev).bfloat16()
+    W = (torch.randn(N, K, generator=g) * 0.05).to(dev).bfloat16()
+    bias = torch.randn(N, generator=g).to(dev)
+    resid = torch.randn(M, N, generator=g).to(dev)
+    ref = A.float() @ W.float().t() + bias + resid
+    out = resid.clone() if inplace else torch.full((M, N), float("nan"), device=dev)
+    parts = 2 * ((N + 255) // 256)
+    xb = torch.full((M, N), float("nan"), device=dev, dtype=torch.bfloat16)
+    st = torch.full((M, parts, 2), float("nan"), device=dev)
+    rc = lib.vitk_op_gemm_fused(_p(A), _p(W), _p(out), M, N, K, 3, _p(bias), None, None, 0, 0.0,
+                                _p(out) if inplace else _p(resid), _p(xb), _p(st), _s())
+    torch.cuda.synchronize()
+    assert rc == 0, lib.vitk_last_error(None)
+    torch.testing.assert_close(out, ref, rtol=1e-4, atol=1e-4 * max(1.0, K / 768))
+    assert torch.equal(xb, out.bfloat16())
+    cols = torch.arange(N, device=dev) // 128
+    sref = torch.zeros(M, parts, 2, device=dev)
+    sref[:, :, 0].index_add_(1, cols, out)
+    sref[:, :, 1].index_add_(1, cols, out * out)
+    torch.testing.assert_close(st, sref, rtol=1e-5, atol=1e-3)
+
+
+def test_gelu_polynomial_matches_erf_form(lib):
+    """The epilogue's degree-6 exponent polynomial vs torch's exact erf GELU over [-9, 9]."""
+    dev = "cuda:0"
+    M, N, K = 256, 4096, 64
+    xs = torch.linspace(-9, 9, M * N, device=dev).reshape(M, N)
+    A = torch.zeros(M, K, device=dev, dtype=torch.bfloat16)
+    W = torch.zeros(N, K, device=dev, dtype=torch.bfloat16)
+    # acc == 0, so out = gelu(bias column) is not what we want; drive x through the LN-free bias:
+    # use K=64 identity-free trick: out[m,n] = gelu(acc + bias[n]) with acc = A[m,:]·W[n,:]
+    A[:, 0] = 1.0
+    col = torch.linspace(-9, 9, N, device=dev)
+    W[:, 0] = col.bfloat16()
+    bias = (col - W[:, 0].float()).contiguous()  # acc + bias == col exactly in fp32
+    out = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+    assert lib.vitk_op_gemm(_p(A), _p(W), _p(out), M, N, K, 1, _p(bias), None, None, 1, _s()) == 0
+    torch.cuda.synchronize()
+    ref = torch.nn.functional.gelu(col.double()).float()
+    got = out[0].float()
+    assert (got - ref.bfloat16().float()).abs().max() <= ref.abs().max() * 2 ** -8
+    assert (out == out[0:1]).all() and xs.numel() == M * N
+
+
+def test_streaming_api_matches_synchronous_call(lib):
+    """vitk_stream_submit/wait (two batches in flight) returns exactly what the synchronous
+    host call returns for the same frames, in order, including a ragged last batch."""
+    import vit_research_b200 as v
+    geom = v.ViTGeometry(image_h=224, image_w=224, patch=16, channels=3, hidden=768, heads=12, mlp=3072,
+                         layers=2, ln_eps=1e-12, gelu_tanh=False)
+    emb = v.ViTEmbedder(geom, v.random_init_state_dict(geom, seed=3), device=0, max_batch=16)
+    g = torch.Generator().manual_seed(11)
+    bank = torch.nn.functional.normalize(torch.randn(300, 768, generator=g), dim=1).numpy()
+    labels = (np.arange(300) % 3).astype(np.int32)
+    index = v.BankIndex(emb, bank, labels, 3, metric="cosine", normalise_rows=True)
+    batches = [torch.randint(0, 256, (n, 224, 224, 3), generator=g, dtype=torch.uint8).numpy()
+               for n in (16, 16, 16, 5)]
+    want = [emb.embed_and_vote(b, index, 7) for b in batches]
+    got = [tuple(a.copy() for a in r) for r in emb.embed_and_vote_stream(iter(batches), index, 7)]
+    assert len(got) == len(want)
+    for w, r in zip(want, got):
+        for a, b in zip(w, r):
+            assert np.array_equal(a, b)
+    only = [r[0].copy() for r in emb.embed_and_vote_stream(iter(batches[:2]))]
+    assert np.array_equal(only[0], want[0][0]) and np.array_equal(only[1], want[1][0])
+    emb.close()

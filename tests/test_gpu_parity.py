@@ -271,3 +271,34 @@ def test_full_size_properties(v, banks):
     assert torch.equal(idx[:, 0].cpu(), torch.arange(256, dtype=torch.int32))
     assert (counts.sum(1) == 25).all()
     emb.close()
+
+
+# ---------------------------------------------------------------------------------------------
+# code-path variants must agree (they are selected by environment variables read once per process)
+# ---------------------------------------------------------------------------------------------
+def _fingerprint(env_extra):
+    import json
+    import subprocess
+    import sys
+    env = dict(os.environ)
+    env.update(env_extra)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "tools", "embed_fingerprint.py")], env=env,
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    return np.array(json.loads(r.stdout.strip().splitlines()[-1])["emb"])
+
+
+def test_code_path_variants_agree():
+    base = _fingerprint({})
+    assert base.shape == (11, 768) and np.isfinite(base).all()
+    # last layer on all tokens vs CLS rows only: the same arithmetic for the rows that are read
+    full = _fingerprint({"VITK_FULL_LAST_LAYER": "1"})
+    assert np.array_equal(base, full)
+    # single-CTA tcgen05.mma (cta_group::1) vs the CTA pair: same K order, same accumulators
+    cg1 = _fingerprint({"VITK_GEMM_CG": "1"})
+    assert np.array_equal(base, cg1)
+    # attention v2 (exact row max, two passes) vs v3 (shift by the first-32 max): rounding only
+    att2 = _fingerprint({"VITK_ATTN": "2"})
+    cos = (base * att2).sum(1) / (np.linalg.norm(base, axis=1) * np.linalg.norm(att2, axis=1))
+    assert cos.min() > 0.999999, cos.min()

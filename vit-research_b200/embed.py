@@ -190,10 +190,19 @@ class ViTEmbedder:
         if frames_np.ndim != 4 or frames_np.shape[1:] != (g.image_h, g.image_w, g.channels):
             raise ValueError(f"frames {frames_np.shape} do not match (N,{g.image_h},{g.image_w},"
                              f"{g.channels}); resize upstream (GPU resize is a SURVEY §8f item)")
-        out = np.empty((frames_np.shape[0], g.hidden), dtype=np.float32)
-        check(self.lib.vitk_embed_host_u8(self.handle, ptr(frames_np), frames_np.shape[0],
-                                          ptr(out), int(l2_normalise)), self.handle,
-              "vitk_embed_host_u8")
+        n = frames_np.shape[0]
+        out = np.empty((n, g.hidden), dtype=np.float32)
+        if n > self.max_batch and l2_normalise:
+            # the reference's 1024-frame batches (FRAME_BATCH_SIZE, ratt_write_clips_to_ragdb.py:29):
+            # stream max_batch-sized chunks so uploads / downloads overlap the forward
+            chunks = (frames_np[a:a + self.max_batch] for a in range(0, n, self.max_batch))
+            a = 0
+            for emb, *_ in self.embed_and_vote_stream(chunks):
+                out[a:a + emb.shape[0]] = emb
+                a += emb.shape[0]
+            return out
+        check(self.lib.vitk_embed_host_u8(self.handle, ptr(frames_np), n, ptr(out), int(l2_normalise)),
+              self.handle, "vitk_embed_host_u8")
         return out
 
     def embed_and_vote(self, frames_np: np.ndarray, index, k: int = 25, out=None):
