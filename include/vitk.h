@@ -92,6 +92,12 @@ int vitk_embed_host_u8(vitk_handle h, const uint8_t* frames_host, int n, float* 
 int vitk_bank_set(vitk_handle h, const float* rows_host, int m, int d, const int32_t* labels_host,
                   int n_classes, int normalise_rows);
 
+/* Same, for rows (m,d) f32 / labels (m) int32 or NULL that already live on the handle's device
+ * (a clip store produced by vitk_embed — build_frame_store, ratt_write_clips_to_ragdb.py:165-254 —
+ * never has to visit the host).  Synchronous on `stream`. */
+int vitk_bank_set_device(vitk_handle h, const float* rows_dev, int m, int d,
+                         const int32_t* labels_dev, int n_classes, int normalise_rows, void* stream);
+
 /* Top-k + vote.  Stands behind `collection.query(query_embeddings, n_results=k)`
  * (chroma.py:211-214; 'l2' space = squared L2 ascending) / RattChunkRetriever's
  * `sims = Q @ C.T; argpartition; argsort` (ratt_chunk_retriever.py:123,144-148; cosine
@@ -99,7 +105,11 @@ int vitk_bank_set(vitk_handle h, const float* rows_host, int m, int d, const int
  *   q_dev (n,d) f32; normalise_queries: q / (||q|| + 1e-8) first.
  *   idx_out (n,k) int32 bank rows in result order; score_out (n,k) f32 (cosine similarity, or
  *   squared L2 distance); label_out (n) int32 (first-max of counts); counts_out (n,n_classes).
- *   Any out pointer except idx_out/score_out may be NULL.  k <= 64. */
+ *   Any out pointer except idx_out/score_out may be NULL.  k <= 64.
+ * Banks of up to 2048 rows: fully asynchronous on `stream`.  Larger stores (the 1 M-row clip
+ * store of rag_vit / RattChunkRetriever) never materialise the (n,m) score matrix: the
+ * similarity GEMM's epilogue filters scores against a running per-query threshold into small
+ * candidate pools; that path synchronises `stream` once per call (pool-overflow check). */
 int vitk_knn_vote(vitk_handle h, const float* q_dev, int n, int k, int metric,
                   int normalise_queries, int32_t* idx_out, float* score_out, int32_t* label_out,
                   int32_t* counts_out, void* stream);
@@ -164,6 +174,9 @@ int vitk_op_patchify(const void* pixels_dev, int pixel_format, void* out_bf16_de
 
 /* Kernel launches issued by this handle since creation (bench.py's gpu_launches). */
 int64_t vitk_launch_count(vitk_handle h);
+/* Large-store k-NN stages that had to be redone because a candidate pool overflowed (0 on
+ * exchangeable stores; the parity tests provoke it with a store sorted by similarity). */
+int64_t vitk_knn_redo_count(vitk_handle h);
 
 #ifdef __cplusplus
 }

@@ -298,7 +298,9 @@ def test_code_path_variants_agree():
     # single-CTA tcgen05.mma (cta_group::1) vs the CTA pair: same K order, same accumulators
     cg1 = _fingerprint({"VITK_GEMM_CG": "1"})
     assert np.array_equal(base, cg1)
-    # attention v2 (exact row max, two passes) vs v3 (shift by the first-32 max): rounding only
+    # attention v2 (exact row max, two passes) vs v3 (shift by the first-32 max): the bf16 P tiles
+    # are rounded at a different scale, so the two agree to bf16 noise (either one is 0.99996 from
+    # the fp32 oracle; measured 0.999988 between them on B200), not bit for bit
     att2 = _fingerprint({"VITK_ATTN": "2"})
     cos = (base * att2).sum(1) / (np.linalg.norm(base, axis=1) * np.linalg.norm(att2, axis=1))
-    assert cos.min() > 0.999999, cos.min()
+    assert cos.min() > 0.9999, cos.min()

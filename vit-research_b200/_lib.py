@@ -58,6 +58,7 @@ SIGNATURES = {
     "vitk_stream_submit": (_i, [_vp, _i, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "vitk_stream_wait": (_i, [_vp, _i]),
     "vitk_bank_set": (_i, [_vp, _vp, _i, _i, _vp, _i, _i]),
+    "vitk_bank_set_device": (_i, [_vp, _vp, _i, _i, _vp, _i, _i, _vp]),
     "vitk_knn_vote": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "vitk_op_gemm": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _i, _vp]),
     "vitk_op_gemm_fused": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _i, _f, _vp, _vp, _vp, _vp]),
@@ -66,6 +67,7 @@ SIGNATURES = {
     "vitk_op_attention": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "vitk_op_patchify": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp]),
     "vitk_launch_count": (C.c_int64, [_vp]),
+    "vitk_knn_redo_count": (C.c_int64, [_vp]),
 }
 
 

@@ -38,6 +38,9 @@ enum GemmEpilogue : int {
                            //   optional: xb bf16 copy of out, per-row partial (sum, sumsq)
   EPI_TABLE_F32 = 4,       // out f32  = acc + table[m % table_rows, n]  (patch embed: pos+bias/CLS)
   EPI_F32 = 5,             // out f32  = acc                              (similarity scores)
+  EPI_THRESH_POOL = 6,     // no matrix out: (key, column) of every score that beats its row's
+                           //   running threshold is appended to that row's candidate pool
+                           //   (large-store top-k: the score matrix never exists — knn.cuh)
 };
 
 struct GemmParams {
@@ -55,6 +58,16 @@ struct GemmParams {
   long long stats_out_stride;
   const float* table;  // [table_rows, N]
   int table_rows;
+  // EPI_THRESH_POOL: key = acc (cosine) or 2*acc - bias[n] (squared-L2 order, bias = ||b||^2);
+  // composite = key_bits << 32 | ~(col_base + n); appended when composite > pool_thresh[m].
+  const unsigned long long* pool_thresh;  // [M]
+  uint2* pool;                            // [M, pool_cap] {bank row, key bits}
+  int* pool_n;                            // [M] entries appended (may exceed pool_cap: overflow)
+  int pool_cap;
+  int col_base;                           // bank row of column 0
+  int pool_l2;                            // 1: squared-L2 key
+  int pool_direct;                        // 1: pools are empty, N <= pool_cap: entry n goes to
+                                          //    slot n of its row's pool (no atomics, no filter)
 };
 
 constexpr int GEMM_BM = 128;
@@ -94,7 +107,7 @@ template <int EPI>
 struct EpiTraits {
   static constexpr bool kOutBf16 = (EPI == EPI_BIAS_BF16 || EPI == EPI_BIAS_GELU_BF16 ||
                                     EPI == EPI_BIAS_GELUT_BF16);
-  static constexpr bool kUsesVec = kOutBf16 || EPI == EPI_BIAS_RESID_F32;
+  static constexpr bool kUsesVec = kOutBf16 || EPI == EPI_BIAS_RESID_F32 || EPI == EPI_THRESH_POOL;
   static constexpr int kChunkCols = kOutBf16 ? 64 : 32;  // 128 B of output per row per chunk
 };
 
@@ -281,7 +294,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         for (int i = et; i < BN; i += GEMM_EPI_WARPS * 32) {
           const int n = n_blk * BN + i;
           sVec[i] = (p.stats != nullptr && n < p.N) ? __ldg(p.c1 + n) : 0.f;
-          sVec[BN + i] = (n < p.N) ? __ldg(p.bias + n) : 0.f;
+          sVec[BN + i] = (n < p.N && p.bias != nullptr) ? __ldg(p.bias + n) : 0.f;
         }
         named_bar_sync(1, GEMM_EPI_WARPS * 32);
       }
@@ -313,7 +326,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const int nt = tile + unit_stride;
         if (nt < num_tiles) {
           const int nn = (nt % n_tiles) * BN + et;
-          if (nn < p.N) {
+          if (nn < p.N && p.bias != nullptr) {
             prefetch_l1(p.bias + nn);
             if (p.stats != nullptr) prefetch_l1(p.c1 + nn);
           }
@@ -325,6 +338,15 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               prefetch_l1(np_ + 2 * p.stats_parts - 1);
             }
           }
+        }
+      }
+      unsigned long long pool_t = ~0ull;  // EPI_THRESH_POOL: this row's running threshold
+      float pool_tf = INFINITY;           // its key part as a float (v >= pool_tf <=> key bits >= t_hi)
+      if constexpr (EPI == EPI_THRESH_POOL) {
+        if (row < p.M) {
+          pool_t = __ldg(p.pool_thresh + row);
+          const uint32_t t_hi = static_cast<uint32_t>(pool_t >> 32);
+          pool_tf = t_hi == 0u ? -INFINITY : float_from_order_bits(t_hi);
         }
       }
       const float nmr = -mean * rstd;  // y = rstd*acc + nmr*c1 + c2
@@ -386,6 +408,40 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 xp[j] = o;
               }
             }
+          } else if constexpr (EPI == EPI_THRESH_POOL) {
+            if (p.pool_l2) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] = fmaf(2.0f, v[j], -sVec[BN + lcol0 + j]);
+            }
+            if (p.pool_direct) {
+              if (row < p.M) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                  if (col0 + j < p.N && col0 + j < p.pool_cap)
+                    p.pool[(size_t)row * p.pool_cap + col0 + j] = make_uint2(
+                        static_cast<uint32_t>(p.col_base + col0 + j), float_order_bits(v[j]));
+              }
+            } else {
+              // branch-free common case: one float compare per score against the key part of
+              // the threshold; the exact composite test runs only for the rare chunk with a hit
+              uint32_t hits = 0u;
+#pragma unroll
+              for (int j = 0; j < 32; ++j) hits |= (v[j] >= pool_tf) ? (1u << j) : 0u;
+              if (hits != 0u) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                  if (((hits >> j) & 1u) && col0 + j < p.N) {
+                    const uint32_t kb = float_order_bits(v[j]);
+                    const uint32_t bi = static_cast<uint32_t>(p.col_base + col0 + j);
+                    const unsigned long long comp = (static_cast<unsigned long long>(kb) << 32) | (~bi);
+                    if (comp > pool_t) {
+                      const int pos = atomicAdd(p.pool_n + row, 1);
+                      if (pos < p.pool_cap) p.pool[(size_t)row * p.pool_cap + pos] = make_uint2(bi, kb);
+                    }
+                  }
+                }
+              }
+            }
           } else if constexpr (EPI == EPI_TABLE_F32) {
             if (row < p.M) {
               const float4* tp = reinterpret_cast<const float4*>(
@@ -401,14 +457,16 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           }
           // the TMA store that last read this staging tile must have finished reading it (the
           // residual epilogue already waited before the residual was loaded into it)
-          if constexpr (EPI != EPI_BIAS_RESID_F32) {
+          if constexpr (EPI != EPI_BIAS_RESID_F32 && EPI != EPI_THRESH_POOL) {
             if (lane == 0) tma_store_wait_read<NBUF - 1>();
             __syncwarp();
           }
+          if constexpr (EPI != EPI_THRESH_POOL) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            float4 o = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-            *reinterpret_cast<float4*>(sbuf + lane * 128 + ((j ^ (lane & 7)) << 4)) = o;
+            for (int j = 0; j < 8; ++j) {
+              float4 o = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+              *reinterpret_cast<float4*>(sbuf + lane * 128 + ((j ^ (lane & 7)) << 4)) = o;
+            }
           }
         } else {
           uint32_t r0[32], r1[32];
@@ -456,6 +514,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             else mbar_arrive(&tempty_bar[acc]);
           }
         }
+        if constexpr (EPI == EPI_THRESH_POOL) continue;  // nothing is stored
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) {

@@ -4,9 +4,10 @@
 //   exact cosine top-k     nba_proj/retrieval/ratt_chunk_retriever.py:74-75,115-116,123,144-148
 //   Chroma L2 query        nba_proj/chroma.py:211-214, generate_clips_hmm.py:403-406 (squared L2)
 //   vote                   nba_proj/chroma.py:102-134 (counts, first-max argmax)
-// Pipeline: bf16 similarity GEMM (gemm_sm100.cuh, EPI_F32) -> warp-shuffle candidate selection of
-// kc >= k rows on the bf16 scores -> exact fp32 re-rank of the kc candidates -> ordered top-k ->
-// class counts -> label.  The re-rank is what makes the indices match an fp32/fp64 brute force:
+// Pipeline: bf16 similarity GEMM (gemm_sm100.cuh) -> warp-shuffle candidate selection of kc >= k
+// rows on the bf16 scores (small banks: register-resident select over the score matrix; large
+// stores: threshold-filter GEMM epilogue + pool select, no score matrix) -> exact fp32 re-rank of
+// the kc candidates -> ordered top-k -> class counts -> label.  The re-rank is what makes the indices match an fp32/fp64 brute force:
 // bf16 similarities alone permute near-ties (SURVEY.md §7 "Top-k index exactness").
 #pragma once
 #include "vitk_common.cuh"
@@ -40,6 +41,36 @@ prep_queries_kernel(const float* __restrict__ q, float* __restrict__ q_out,
   }
 }
 
+// Bank rows -> library-owned f32 copy (+ optional b / (||b|| + 1e-8), ratt_chunk_retriever.py:116),
+// bf16 copy for the similarity GEMM and ||b||^2 for the squared-L2 order.  One warp per row; the
+// norm is accumulated in double like the host path of vitk_bank_set.
+__global__ void __launch_bounds__(256)
+bank_prep_kernel(const float* __restrict__ rows, float* __restrict__ out, __nv_bfloat16* __restrict__ out_bf16,
+                 float* __restrict__ sqnorm, int m, int d, int normalise) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp >= m) return;
+  const float* r = rows + (size_t)warp * d;
+  float den = 1.f;
+  if (normalise) {
+    double s = 0.0;
+    for (int i = lane; i < d; i += 32) s += (double)r[i] * r[i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    den = (float)sqrt(s) + 1e-8f;
+  }
+  double s2 = 0.0;
+  for (int i = lane; i < d; i += 32) {
+    const float v = normalise ? r[i] / den : r[i];
+    out[(size_t)warp * d + i] = v;
+    out_bf16[(size_t)warp * d + i] = __float2bfloat16_rn(v);
+    s2 += (double)v * v;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+  if (lane == 0) sqnorm[warp] = (float)s2;
+}
+
 // Total order used everywhere: larger key first, ties -> smaller index first.
 __device__ __forceinline__ bool key_before(float ka, int ia, float kb, int ib) {
   return ka > kb || (ka == kb && ia < ib);
@@ -53,13 +84,6 @@ __device__ __forceinline__ void warp_argbest(float& k, int& i) {
     int oi = __shfl_xor_sync(0xffffffffu, i, o);
     if (key_before(ok, oi, k, i)) { k = ok; i = oi; }
   }
-}
-
-// Order-preserving map float -> uint32 (larger float <=> larger integer); 0 is below every
-// real value and marks "no row".
-__device__ __forceinline__ uint32_t float_order_bits(float f) {
-  const uint32_t u = __float_as_uint(f);
-  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 
 // Candidate selection, register-resident fast path (m <= 32*KPL): one warp per query, lane l
@@ -119,50 +143,146 @@ knn_candidates_reg_kernel(const float* __restrict__ scores, int ld,
   }
 }
 
-// Candidate selection, general path (any m).  One warp per query; lane l owns bank rows
-// l, l+32, ...  Each round every lane offers its best not-yet-taken row; the warp-shuffle
-// argmax picks the winner; only the winning lane rescans its rows for its next-best.
-// key = score (cosine) or 2*score - ||b||^2 (L2: larger == closer).
+// ---------------------------------------------------------------------------------------------
+// Large stores (m > 2048 rows; BASELINE configs[4]: 1 M-row clip store, top-10 cosine —
+// ratt_chunk_retriever.py:123,144-148 pulls every candidate to the host and argpartitions).
+// The score matrix [queries, m] is never materialised.  The store is walked in a few stages of
+// geometrically growing size; each stage is ONE similarity GEMM whose epilogue
+// (EPI_THRESH_POOL, gemm_sm100.cuh) compares every score with its query's running threshold —
+// the kc-th best composite key seen so far — and appends the rare survivors to a per-query pool.
+// Between stages knn_pool_select_kernel shrinks each pool back to its top kc and raises the
+// threshold.  Composite key = key_bits << 32 | ~row: a strict total order (key descending, row
+// ascending), so the final candidate SET is exactly the first kc rows of that order no matter
+// how the atomics interleave.  A pool that overflows is detected on the host after the last
+// stage and that stage is redone in quarters (a stage of <= cap - kc rows cannot overflow).
+// ---------------------------------------------------------------------------------------------
+constexpr int KNN_POOL_CAP = 2048;  // pool entries per query (64 per lane)
+
+// Sum over the 128 threads of a CTA (4 warps); `buf` = 4 ints of shared memory that no thread
+// still reads from an earlier call (callers alternate two buffers).
+__device__ __forceinline__ int block4_sum(int v, int* buf) {
+  v = __reduce_add_sync(0xffffffffu, v);
+  if ((threadIdx.x & 31) == 0) buf[threadIdx.x >> 5] = v;
+  __syncthreads();
+  return (buf[0] + buf[1]) + (buf[2] + buf[3]);
+}
+
+// One CTA (4 warps) per query.  Loads the pool into registers (16 entries per thread), finds
+// the kc-th largest composite — a 32-step bitwise binary search on the key bits (compare +
+// block-wide count), and only when several rows share the kc-th key a second search on ~row
+// among them — compacts the winners to the front of the pool, publishes the new threshold and,
+// when `cand` is given, the candidate rows for the re-rank (-1 padded).  direct_rows >= 0: the
+// pool was filled positionally by the first stage (entry i = row i of the stage) and holds
+// exactly that many entries.  Rows in [ex_lo, ex_hi) are dropped first (a stage being redone
+// after an overflow).  overflow[0] is set when a pool had been truncated.
 __global__ void __launch_bounds__(128)
-knn_candidates_scan_kernel(const float* __restrict__ scores, int ld, const float* __restrict__ bank_sqnorm,
-                      int nq, int m, int kc, int metric, int32_t* __restrict__ cand) {
-  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
-  if (warp >= nq) return;
-  const float* row = scores + (size_t)warp * ld;
-  auto key_of = [&](int i) -> float {
-    float s = row[i];
-    return metric == METRIC_L2 ? 2.0f * s - __ldg(bank_sqnorm + i) : s;
-  };
-  // lane-local best
-  float bk = -INFINITY;
-  int bi = 0x7fffffff;
-  for (int i = lane; i < m; i += 32) {
-    float k = key_of(i);
-    if (key_before(k, i, bk, bi)) { bk = k; bi = i; }
+knn_pool_select_kernel(uint2* __restrict__ pool, int* __restrict__ pool_n,
+                       unsigned long long* __restrict__ thresh, int nq, int kc, int direct_rows,
+                       int ex_lo, int ex_hi, int32_t* __restrict__ cand, int* __restrict__ overflow) {
+  constexpr int KPL = KNN_POOL_CAP / 128;
+  __shared__ int s_buf[2][4];
+  __shared__ uint32_t s_min[4];
+  const int qi = blockIdx.x;
+  const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
+  int count = direct_rows >= 0 ? direct_rows : pool_n[qi];
+  if (count > KNN_POOL_CAP) {
+    if (tid == 0) atomicExch(overflow, 1);
+    count = KNN_POOL_CAP;
   }
-  for (int c = 0; c < kc; ++c) {
-    float wk = bk;
-    int wi = bi;
-    warp_argbest(wk, wi);
-    if (lane == 0) cand[(size_t)warp * kc + c] = wi;
-    if (wi == bi && bi != 0x7fffffff) {
-      // this lane won: its next best is the best row strictly after (wk, wi) in the order
-      float nk = -INFINITY;
-      int ni = 0x7fffffff;
-      for (int i = lane; i < m; i += 32) {
-        float k = key_of(i);
-        if (key_before(wk, wi, k, i) && key_before(k, i, nk, ni)) { nk = k; ni = i; }
-      }
-      bk = nk;
-      bi = ni;
+  uint2* row = pool + (size_t)qi * KNN_POOL_CAP;
+  uint32_t hi[KPL], lo[KPL];  // key bits | ~row; hi == 0 marks an empty slot
+#pragma unroll
+  for (int j = 0; j < KPL; ++j) {
+    const int i = tid + 128 * j;
+    hi[j] = 0u;
+    lo[j] = 0u;
+    if (i < count) {
+      const uint2 e = row[i];
+      const bool excluded = (int)e.x >= ex_lo && (int)e.x < ex_hi;
+      if (!excluded) { hi[j] = e.y; lo[j] = ~e.x; }
     }
+  }
+  uint32_t t = 0u;
+  int flip = 0;
+#pragma unroll 1
+  for (int bit = 31; bit >= 0; --bit, flip ^= 1) {
+    const uint32_t tt = t | (1u << bit);
+    int c = 0;
+#pragma unroll
+    for (int j = 0; j < KPL; ++j) c += hi[j] >= tt ? 1 : 0;
+    if (block4_sum(c, s_buf[flip]) >= kc) t = tt;
+  }
+  // t == the kc-th largest key (with multiplicity), or 0 when fewer than kc entries exist
+  uint32_t t_lo = 0u;
+  if (t != 0u) {  // block-uniform
+    int gt = 0, eq = 0;
+    uint32_t lo_min = 0xffffffffu;
+#pragma unroll
+    for (int j = 0; j < KPL; ++j) {
+      gt += hi[j] > t ? 1 : 0;
+      if (hi[j] == t) { ++eq; lo_min = min(lo_min, lo[j]); }
+    }
+    gt = block4_sum(gt, s_buf[flip]); flip ^= 1;
+    eq = block4_sum(eq, s_buf[flip]); flip ^= 1;
+    const int need = kc - gt;  // >= 1 rows with key == t are wanted, lowest rows first
+    if (eq == need) {
+      lo_min = __reduce_min_sync(0xffffffffu, lo_min);
+      if (lane == 0) s_min[w] = lo_min;
+      __syncthreads();
+      t_lo = min(min(s_min[0], s_min[1]), min(s_min[2], s_min[3]));
+    } else {
+#pragma unroll 1
+      for (int bit = 31; bit >= 0; --bit, flip ^= 1) {
+        const uint32_t tt = t_lo | (1u << bit);
+        int c = 0;
+#pragma unroll
+        for (int j = 0; j < KPL; ++j) c += (hi[j] == t && lo[j] >= tt) ? 1 : 0;
+        if (block4_sum(c, s_buf[flip]) >= need) t_lo = tt;
+      }
+    }
+  }
+  // compaction: winners of warp w go after those of warps < w (all reads of the pool are done:
+  // every thread has passed at least one __syncthreads since its loads)
+  int mine = 0;
+#pragma unroll
+  for (int j = 0; j < KPL; ++j)
+    mine += (hi[j] != 0u && (hi[j] > t || (hi[j] == t && lo[j] >= t_lo))) ? 1 : 0;
+  const int total = block4_sum(mine, s_buf[flip]);
+  int base = 0;
+  for (int i = 0; i < w; ++i) base += s_buf[flip][i];
+  const uint32_t lt_mask = (1u << lane) - 1u;
+#pragma unroll
+  for (int j = 0; j < KPL; ++j) {
+    const bool pr = hi[j] != 0u && (hi[j] > t || (hi[j] == t && lo[j] >= t_lo));
+    const uint32_t b = __ballot_sync(0xffffffffu, pr);
+    if (pr) {
+      const int pos = base + __popc(b & lt_mask);
+      const uint32_t bi = ~lo[j];
+      row[pos] = make_uint2(bi, hi[j]);
+      if (cand != nullptr && pos < kc) cand[(size_t)qi * kc + pos] = (int32_t)bi;
+    }
+    base += __popc(b);
+  }
+  if (cand != nullptr)
+    for (int i = total + tid; i < kc; i += 128) cand[(size_t)qi * kc + i] = -1;
+  if (tid == 0) {
+    pool_n[qi] = total;
+    // the old threshold may be the composite of a row that was just excluded: step below it so
+    // the redo (strict >) can bring that row back
+    unsigned long long told = thresh[qi];
+    if (ex_hi > ex_lo && told > 0ull) told -= 1ull;
+    const unsigned long long tn = (static_cast<unsigned long long>(t) << 32) | t_lo;
+    thresh[qi] = tn > told ? tn : told;
   }
 }
 
-// Exact fp32 re-rank of the kc candidates, ordered top-k, vote.  One warp per query.
+// Exact fp32 re-rank of the kc candidates, ordered top-k, vote.  One CTA (4 warps) per query.
 //   cosine: score = <q, b>            (rows unit-normalised upstream), descending
 //   L2    : score = sum (q-b)^2       (Chroma 'l2' space returns squared L2), ascending
+// Each warp takes every 4th candidate, four at a time: the 32 lanes read the bank row coalesced
+// (float4 per lane per 128 columns), multiply against the query staged in shared memory and
+// reduce with xor-shuffles (every lane ends with the same, order-deterministic sum).  Warp 0
+// then extracts the k best in (score, row) order and votes.
 // Outputs: idx[nq,k], score[nq,k] in result order; counts[nq,n_classes]; label = first argmax
 // of counts (np.argmax semantics, chroma.py:128: ties -> left > right > none).
 __global__ void __launch_bounds__(128)
@@ -171,38 +291,32 @@ knn_rerank_vote_kernel(const float* __restrict__ q, const float* __restrict__ ba
                        int nq, int m, int d, int kc, int k, int metric, int n_classes,
                        int32_t* __restrict__ idx_out, float* __restrict__ score_out,
                        int32_t* __restrict__ label_out, int32_t* __restrict__ counts_out) {
-  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
-  if (warp >= nq) return;
-  // Each lane owns candidate slots lane, lane+32, ... and computes their full fp32 dot /
-  // squared distance itself: no shuffles, (KNN_MAX_CAND/32) x 4 independent loads in flight per
-  // lane, and the keys land exactly where the selection below expects them.  The query row is
-  // staged in shared memory (broadcast reads).
-  extern __shared__ float knn_q_smem[];
-  float* qs = knn_q_smem + (threadIdx.x >> 5) * d;
-  for (int i = lane * 4; i < d; i += 128)
-    *reinterpret_cast<float4*>(qs + i) = *reinterpret_cast<const float4*>(q + (size_t)warp * d + i);
-  __syncwarp();
-  float ck[KNN_MAX_CAND / 32];   // key (larger == better) of candidate slot lane + 32*s
-  int ci[KNN_MAX_CAND / 32];
-  const float* br[KNN_MAX_CAND / 32];
-  float acc[KNN_MAX_CAND / 32];
+  extern __shared__ float knn_q_smem[];  // [d] query row
+  __shared__ float s_key[KNN_MAX_CAND];
+  __shared__ int s_idx[KNN_MAX_CAND];
+  const int qi = blockIdx.x;
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (qi >= nq) return;
+  for (int i = threadIdx.x * 4; i < d; i += 128 * 4)
+    *reinterpret_cast<float4*>(knn_q_smem + i) = *reinterpret_cast<const float4*>(q + (size_t)qi * d + i);
+  __syncthreads();
+  for (int c0 = w * 4; c0 < kc; c0 += 16) {
+    const float* br[4];
+    int bi[4];
+    float acc[4];
 #pragma unroll
-  for (int s = 0; s < KNN_MAX_CAND / 32; ++s) {
-    const int c = lane + 32 * s;
-    int bi = c < kc ? cand[(size_t)warp * kc + c] : -1;
-    if (bi < 0 || bi >= m) bi = -1;
-    ci[s] = bi < 0 ? 0x7fffffff : bi;
-    br[s] = bank + (size_t)(bi < 0 ? 0 : bi) * d;
-    acc[s] = 0.f;
-  }
-  const int nslots = (kc + 31) >> 5;  // warp-uniform
-#pragma unroll 2
-  for (int i = 0; i < d; i += 4) {
-    const float4 a = *reinterpret_cast<const float4*>(qs + i);
+    for (int s = 0; s < 4; ++s) {
+      const int c = c0 + s;
+      int b = c < kc ? __ldg(cand + (size_t)qi * kc + c) : -1;
+      if (b < 0 || b >= m) b = -1;
+      bi[s] = b;
+      br[s] = bank + (size_t)(b < 0 ? 0 : b) * d;
+      acc[s] = 0.f;
+    }
+    for (int i = lane * 4; i < d; i += 128) {
+      const float4 a = *reinterpret_cast<const float4*>(knn_q_smem + i);
 #pragma unroll
-    for (int s = 0; s < KNN_MAX_CAND / 32; ++s) {
-      if (s < nslots) {
+      for (int s = 0; s < 4; ++s) {
         const float4 b = __ldg(reinterpret_cast<const float4*>(br[s] + i));
         if (metric == METRIC_L2) {
           const float dx = a.x - b.x, dy = a.y - b.y, dz = a.z - b.z, dw = a.w - b.w;
@@ -212,10 +326,25 @@ knn_rerank_vote_kernel(const float* __restrict__ q, const float* __restrict__ ba
         }
       }
     }
-  }
 #pragma unroll
-  for (int s = 0; s < KNN_MAX_CAND / 32; ++s)
-    ck[s] = ci[s] == 0x7fffffff ? -INFINITY : (metric == METRIC_L2 ? -acc[s] : acc[s]);
+    for (int s = 0; s < 4; ++s) {
+      const float tot = warp_sum(acc[s]);
+      if (lane == 0 && c0 + s < kc) {
+        s_key[c0 + s] = bi[s] < 0 ? -INFINITY : (metric == METRIC_L2 ? -tot : tot);
+        s_idx[c0 + s] = bi[s] < 0 ? 0x7fffffff : bi[s];
+      }
+    }
+  }
+  __syncthreads();
+  if (w != 0) return;
+  float ck[KNN_MAX_CAND / 32];   // key (larger == better) of candidate slot lane + 32*s
+  int ci[KNN_MAX_CAND / 32];
+#pragma unroll
+  for (int s = 0; s < KNN_MAX_CAND / 32; ++s) {
+    const int c = lane + 32 * s;
+    ck[s] = c < kc ? s_key[c] : -INFINITY;
+    ci[s] = c < kc ? s_idx[c] : 0x7fffffff;
+  }
   int cnt[KNN_MAX_CLASSES];
 #pragma unroll
   for (int j = 0; j < KNN_MAX_CLASSES; ++j) cnt[j] = 0;
@@ -230,7 +359,7 @@ knn_rerank_vote_kernel(const float* __restrict__ q, const float* __restrict__ ba
     int wi = bi;
     warp_argbest(wk, wi);
     if (wi == 0x7fffffff) {  // fewer than k candidates: pad like an empty Chroma slot
-      if (lane == 0) { idx_out[(size_t)warp * k + r] = -1; score_out[(size_t)warp * k + r] = 0.f; }
+      if (lane == 0) { idx_out[(size_t)qi * k + r] = -1; score_out[(size_t)qi * k + r] = 0.f; }
       continue;
     }
     if (wi == bi) {
@@ -242,17 +371,17 @@ knn_rerank_vote_kernel(const float* __restrict__ q, const float* __restrict__ ba
 #pragma unroll
     for (int j = 0; j < KNN_MAX_CLASSES; ++j) cnt[j] += (lab == j) ? 1 : 0;
     if (lane == 0) {
-      idx_out[(size_t)warp * k + r] = wi;
-      score_out[(size_t)warp * k + r] = metric == METRIC_L2 ? -wk : wk;
+      idx_out[(size_t)qi * k + r] = wi;
+      score_out[(size_t)qi * k + r] = metric == METRIC_L2 ? -wk : wk;
     }
   }
   if (lane == 0) {
     int best = 0;
     for (int j = 0; j < n_classes; ++j) {
-      if (counts_out) counts_out[(size_t)warp * n_classes + j] = cnt[j];
+      if (counts_out) counts_out[(size_t)qi * n_classes + j] = cnt[j];
       if (cnt[j] > cnt[best]) best = j;
     }
-    if (label_out) label_out[warp] = best;
+    if (label_out) label_out[qi] = best;
   }
 }
 

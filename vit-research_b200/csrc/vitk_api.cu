@@ -216,6 +216,7 @@ int launch_gemm(Err& e, int epi, const CUtensorMap& a, const CUtensorMap& b, con
     case EPI_BIAS_RESID_F32: return launch_gemm_e<EPI_BIAS_RESID_F32>(e, a, b, c, r, p, st);
     case EPI_TABLE_F32: return launch_gemm_e<EPI_TABLE_F32>(e, a, b, c, r, p, st);
     case EPI_F32: return launch_gemm_e<EPI_F32>(e, a, b, c, r, p, st);
+    case EPI_THRESH_POOL: return launch_gemm_e<EPI_THRESH_POOL>(e, a, b, c, r, p, st);
   }
   e.set("gemm: unknown epilogue %d", epi);
   return 1;
@@ -395,6 +396,14 @@ struct vitk_ctx {
   __nv_bfloat16* knn_qb = nullptr;
   int32_t* knn_cand = nullptr;
   int knn_cap_q = 0, knn_cap_m = 0;
+  // large-store path (bank_m > KNN_DIRECT_MAX): per-query candidate pools instead of scores
+  uint2* knn_pool = nullptr;
+  int* knn_pool_n = nullptr;
+  unsigned long long* knn_thresh = nullptr;
+  int* knn_overflow = nullptr;      // device, KNN_MAX_STAGES flags
+  int* knn_overflow_host = nullptr; // pinned
+  int knn_pool_cap_q = 0;
+  int64_t knn_redo_stages = 0;      // stages redone after a pool overflow (diagnostic)
   int32_t *res_idx = nullptr, *res_label = nullptr, *res_counts = nullptr;
   float* res_score = nullptr;
   cudaStream_t own_stream = nullptr;
@@ -453,6 +462,8 @@ void free_ctx(vitk_ctx* c) {
   cudaFree(c->bank); cudaFree(c->bank_sqnorm); cudaFree(c->bank_bf16); cudaFree(c->bank_labels);
   cudaFree(c->res_idx); cudaFree(c->res_label); cudaFree(c->res_counts); cudaFree(c->res_score);
   cudaFree(c->knn_q); cudaFree(c->knn_scores); cudaFree(c->knn_qb); cudaFree(c->knn_cand);
+  cudaFree(c->knn_pool); cudaFree(c->knn_pool_n); cudaFree(c->knn_thresh); cudaFree(c->knn_overflow);
+  if (c->knn_overflow_host) cudaFreeHost(c->knn_overflow_host);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
   for (auto& sl : c->slots) {
     cudaFree(sl.pix); cudaFree(sl.emb); cudaFree(sl.score); cudaFree(sl.idx); cudaFree(sl.label);
@@ -486,6 +497,7 @@ extern "C" const char* vitk_last_error(vitk_handle h) {
 }
 
 extern "C" int64_t vitk_launch_count(vitk_handle h) { return h ? h->launches : 0; }
+extern "C" int64_t vitk_knn_redo_count(vitk_handle h) { return h ? h->knn_redo_stages : 0; }
 
 extern "C" int vitk_create(const vitk_config* cfg, int device, vitk_handle* out) {
   Err e;
@@ -980,6 +992,47 @@ extern "C" int vitk_bank_set(vitk_handle h, const float* rows_host, int m, int d
   return 0;
 }
 
+// Device-resident variant of vitk_bank_set: rows_dev (m,d) f32 and labels_dev (m) int32 (or
+// NULL) already live on this handle's device (a store built by vitk_embed, or synthetic).  The
+// same row normalisation / bf16 copy / ||b||^2 are produced by one kernel pass.
+extern "C" int vitk_bank_set_device(vitk_handle h, const float* rows_dev, int m, int d,
+                                    const int32_t* labels_dev, int n_classes, int normalise_rows,
+                                    void* stream) {
+  if (!h) return 1;
+  Err& e = h->err;
+  if (!rows_dev || m < 1 || d < 64 || d % 64 != 0) {
+    e.set("vitk_bank_set_device: need m >= 1 rows and d a multiple of 64 (got m=%d d=%d)", m, d);
+    return 1;
+  }
+  if (n_classes < 0 || n_classes > KNN_MAX_CLASSES) {
+    e.set("vitk_bank_set_device: n_classes must be in [0,%d]", KNN_MAX_CLASSES);
+    return 1;
+  }
+  CK(e, cudaSetDevice(h->device));
+  CK(e, cudaDeviceSynchronize());
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  cudaFree(h->bank); cudaFree(h->bank_sqnorm); cudaFree(h->bank_bf16); cudaFree(h->bank_labels);
+  h->bank = nullptr; h->bank_sqnorm = nullptr; h->bank_bf16 = nullptr; h->bank_labels = nullptr;
+  h->bank_m = 0;
+  if (dev_alloc(e, &h->bank, (size_t)m * d) || dev_alloc(e, &h->bank_bf16, (size_t)m * d) ||
+      dev_alloc(e, &h->bank_sqnorm, (size_t)m) || dev_alloc(e, &h->bank_labels, (size_t)m))
+    return 1;
+  bank_prep_kernel<<<(m + 7) / 8, 256, 0, st>>>(rows_dev, h->bank, h->bank_bf16, h->bank_sqnorm, m, d,
+                                                normalise_rows);
+  CK(e, cudaGetLastError());
+  if (labels_dev)
+    CK(e, cudaMemcpyAsync(h->bank_labels, labels_dev, (size_t)m * 4, cudaMemcpyDeviceToDevice, st));
+  else
+    CK(e, cudaMemsetAsync(h->bank_labels, 0, (size_t)m * 4, st));
+  CK(e, cudaStreamSynchronize(st));
+  if (tmap_operand(e, &h->tm_bank, h->bank_bf16, m, d, 128)) return 1;
+  h->bank_m = m;
+  h->bank_d = d;
+  h->bank_classes = labels_dev ? n_classes : 0;
+  h->launches += 1;
+  return 0;
+}
+
 namespace {
 int knn_candidates_for(int k, int m) {
   // bf16 similarity error on unit vectors is ~1e-4..1e-3; the slack keeps every true top-k
@@ -989,6 +1042,114 @@ int knn_candidates_for(int k, int m) {
   if (kc > m) kc = m;
   if (kc < k) kc = k < m ? k : m;
   return kc;
+}
+
+constexpr int KNN_DIRECT_MAX = 2048;  // banks up to this many rows: score matrix + register select
+constexpr int KNN_MAX_STAGES = 32;
+
+// One stage of the large-store walk: bank rows [lo, hi) through the threshold-filter GEMM, then
+// the pool select (flag = overflow slot; ex_* = rows to drop from the pools first; cand != null
+// on the final select).
+int knn_stage(vitk_ctx* h, int n, int kc, int metric, int lo, int hi, int flag, bool direct,
+              cudaStream_t st) {
+  Err& e = h->err;
+  const int d = h->bank_d;
+  CUtensorMap ta, tb;
+  if (tmap_operand(e, &ta, h->knn_qb, n, d, GEMM_BM) ||
+      tmap_operand(e, &tb, h->bank_bf16 + (size_t)lo * d, hi - lo, d, 128))
+    return 1;
+  GemmParams gp{};
+  gp.M = n; gp.N = hi - lo; gp.K = d;
+  gp.bias = metric == METRIC_L2 ? h->bank_sqnorm + lo : nullptr;
+  gp.pool_thresh = h->knn_thresh; gp.pool = h->knn_pool; gp.pool_n = h->knn_pool_n;
+  gp.pool_cap = KNN_POOL_CAP; gp.col_base = lo; gp.pool_l2 = metric == METRIC_L2 ? 1 : 0;
+  gp.pool_direct = direct ? 1 : 0;
+  if (launch_gemm(e, EPI_THRESH_POOL, ta, tb, ta, ta, gp, st)) return 1;
+  knn_pool_select_kernel<<<n, 128, 0, st>>>(h->knn_pool, h->knn_pool_n, h->knn_thresh, n,
+                                                      kc, direct ? hi - lo : -1, 0, 0, nullptr,
+                                                      h->knn_overflow + flag);
+  CK(e, cudaGetLastError());
+  h->launches += 2;
+  return 0;
+}
+
+// Candidate rows (h->knn_cand [n, kc]) for a bank of more than KNN_DIRECT_MAX rows.  All stages
+// are launched back to back; ONE stream synchronisation at the end reads the overflow flags.  A
+// flagged stage (its pool was truncated; thresholds stay valid lower bounds, so later stages are
+// unaffected) is redone in quarters with the final thresholds.
+int knn_large_candidates(vitk_ctx* h, int n, int kc, int metric, cudaStream_t st) {
+  Err& e = h->err;
+  const int m = h->bank_m;
+  if (n > h->knn_pool_cap_q) {
+    CK(e, cudaStreamSynchronize(st));
+    cudaFree(h->knn_pool); cudaFree(h->knn_pool_n); cudaFree(h->knn_thresh);
+    h->knn_pool = nullptr; h->knn_pool_n = nullptr; h->knn_thresh = nullptr;
+    h->knn_pool_cap_q = 0;
+    if (dev_alloc(e, &h->knn_pool, (size_t)n * KNN_POOL_CAP) || dev_alloc(e, &h->knn_pool_n, (size_t)n) ||
+        dev_alloc(e, &h->knn_thresh, (size_t)n))
+      return 1;
+    if (!h->knn_overflow && dev_alloc(e, &h->knn_overflow, (size_t)KNN_MAX_STAGES)) return 1;
+    if (!h->knn_overflow_host)
+      CK(e, cudaMallocHost(reinterpret_cast<void**>(&h->knn_overflow_host), KNN_MAX_STAGES * sizeof(int)));
+    h->knn_pool_cap_q = n;
+  }
+  CK(e, cudaMemsetAsync(h->knn_pool_n, 0, (size_t)n * sizeof(int), st));
+  CK(e, cudaMemsetAsync(h->knn_thresh, 0, (size_t)n * sizeof(unsigned long long), st));
+  // stage sizes: the first fills the empty pools (threshold 0: everything is appended), later
+  // ones grow by g, chosen so the EXPECTED survivors per pool (kc * g on exchangeable rows) stay
+  // 4x below the pool capacity
+  int g = (KNN_POOL_CAP - kc) / (4 * kc);
+  g = g < 2 ? 2 : g > 8 ? 8 : g;
+  struct Stage { int lo, hi; };
+  std::vector<Stage> todo;
+  for (int lo = 0, step = KNN_POOL_CAP; lo < m;) {
+    const long long want = (long long)lo + step;
+    const int hi = want < m ? (int)want : m;
+    todo.push_back({lo, hi});
+    lo = hi;
+    step = g * hi;
+    if ((int)todo.size() == KNN_MAX_STAGES - 1) step = m;  // cannot happen for m < 2^31, g >= 2
+  }
+  bool first_pass = true;  // its first stage meets empty pools: filled positionally, no atomics
+  while (!todo.empty()) {
+    std::vector<Stage> next;
+    for (size_t base = 0; base < todo.size(); base += KNN_MAX_STAGES) {
+      const size_t cnt = todo.size() - base < (size_t)KNN_MAX_STAGES ? todo.size() - base : KNN_MAX_STAGES;
+      CK(e, cudaMemsetAsync(h->knn_overflow, 0, KNN_MAX_STAGES * sizeof(int), st));
+      for (size_t i = 0; i < cnt; ++i)
+        if (knn_stage(h, n, kc, metric, todo[base + i].lo, todo[base + i].hi, (int)i,
+                      first_pass && base + i == 0, st))
+          return 1;
+      CK(e, cudaMemcpyAsync(h->knn_overflow_host, h->knn_overflow, KNN_MAX_STAGES * sizeof(int),
+                            cudaMemcpyDeviceToHost, st));
+      CK(e, cudaStreamSynchronize(st));
+      for (size_t i = 0; i < cnt; ++i) {
+        if (!h->knn_overflow_host[i]) continue;
+        const Stage s = todo[base + i];
+        const int rows = s.hi - s.lo;
+        if (rows <= KNN_POOL_CAP - kc) {
+          e.set("vitk_knn_vote: candidate pool overflow in a %d-row stage (internal error)", rows);
+          return 1;
+        }
+        h->knn_redo_stages += 1;
+        // forget whatever the truncated stage left in the pools, keep the thresholds
+        knn_pool_select_kernel<<<n, 128, 0, st>>>(h->knn_pool, h->knn_pool_n, h->knn_thresh,
+                                                            n, kc, -1, s.lo, s.hi, nullptr, h->knn_overflow);
+        CK(e, cudaGetLastError());
+        h->launches += 1;
+        const int q4 = (rows + 3) / 4;
+        for (int lo = s.lo; lo < s.hi; lo += q4) next.push_back({lo, lo + q4 < s.hi ? lo + q4 : s.hi});
+      }
+    }
+    todo.swap(next);
+    first_pass = false;
+  }
+  // final select: candidates for the fp32 re-rank
+  knn_pool_select_kernel<<<n, 128, 0, st>>>(h->knn_pool, h->knn_pool_n, h->knn_thresh, n, kc,
+                                                      -1, 0, 0, h->knn_cand, h->knn_overflow);
+  CK(e, cudaGetLastError());
+  h->launches += 1;
+  return 0;
 }
 }  // namespace
 
@@ -1005,32 +1166,41 @@ extern "C" int vitk_knn_vote(vitk_handle h, const float* q_dev, int n, int k, in
   CK(e, cudaSetDevice(h->device));
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const int m = h->bank_m, d = h->bank_d;
-  const int ld = (m + 3) & ~3;  // TMA row pitch must be a multiple of 16 B
+  if (d % 4 != 0 || (size_t)d * sizeof(float) > 40 * 1024) {
+    e.set("vitk_knn_vote: d=%d must be a multiple of 4 and at most 10240", d);
+    return 1;
+  }
+  const bool large = m > KNN_DIRECT_MAX;
+  const int ld = large ? 4 : (m + 3) & ~3;  // TMA row pitch must be a multiple of 16 B
   if (n > h->knn_cap_q || ld > h->knn_cap_m) {
     CK(e, cudaStreamSynchronize(st));
     cudaFree(h->knn_q); cudaFree(h->knn_qb); cudaFree(h->knn_scores); cudaFree(h->knn_cand);
     h->knn_q = nullptr; h->knn_qb = nullptr; h->knn_scores = nullptr; h->knn_cand = nullptr;
     const int cq = n > h->knn_cap_q ? n : h->knn_cap_q;
+    const int cm = ld > h->knn_cap_m ? ld : h->knn_cap_m;
     h->knn_cap_q = 0;
     if (dev_alloc(e, &h->knn_q, (size_t)cq * d) || dev_alloc(e, &h->knn_qb, (size_t)cq * d) ||
-        dev_alloc(e, &h->knn_scores, (size_t)cq * ld) ||
+        dev_alloc(e, &h->knn_scores, (size_t)cq * cm) ||
         dev_alloc(e, &h->knn_cand, (size_t)cq * KNN_MAX_CAND))
       return 1;
     h->knn_cap_q = cq;
-    h->knn_cap_m = ld;
+    h->knn_cap_m = cm;
   }
   const int kc = knn_candidates_for(k, m);
   prep_queries_kernel<<<(n + 7) / 8, 256, 0, st>>>(q_dev, h->knn_q, h->knn_qb, n, d,
                                                    normalise_queries);
   CK(e, cudaGetLastError());
-  CUtensorMap ta, tc;
-  if (tmap_operand(e, &ta, h->knn_qb, n, d, GEMM_BM) ||
-      tmap_output(e, &tc, h->knn_scores, n, ld, false))
-    return 1;
-  GemmParams gp{};
-  gp.M = n; gp.N = m; gp.K = d;
-  if (launch_gemm(e, EPI_F32, ta, h->tm_bank, tc, tc, gp, st)) return 1;
-  {
+  h->launches += 1;
+  if (large) {
+    if (knn_large_candidates(h, n, kc, metric, st)) return 1;
+  } else {
+    CUtensorMap ta, tc;
+    if (tmap_operand(e, &ta, h->knn_qb, n, d, GEMM_BM) ||
+        tmap_output(e, &tc, h->knn_scores, n, ld, false))
+      return 1;
+    GemmParams gp{};
+    gp.M = n; gp.N = m; gp.K = d;
+    if (launch_gemm(e, EPI_F32, ta, h->tm_bank, tc, tc, gp, st)) return 1;
     const int blocks = (n + 3) / 4;
     const float* sc = h->knn_scores;
     const float* sq = h->bank_sqnorm;
@@ -1039,19 +1209,15 @@ extern "C" int vitk_knn_vote(vitk_handle h, const float* q_dev, int n, int k, in
     else if (m <= 512) knn_candidates_reg_kernel<16><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd);
     else if (m <= 1024) knn_candidates_reg_kernel<32><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd);
     else if (m <= 1536) knn_candidates_reg_kernel<48><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd);
-    else if (m <= 2048) knn_candidates_reg_kernel<64><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd);
-    else knn_candidates_scan_kernel<<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd);
+    else knn_candidates_reg_kernel<64><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd);
+    CK(e, cudaGetLastError());
+    h->launches += 2;
   }
-  CK(e, cudaGetLastError());
-  if (d % 4 != 0 || (size_t)4 * d * sizeof(float) > 48 * 1024) {
-    e.set("vitk_knn_vote: d=%d must be a multiple of 4 and at most 3072", d);
-    return 1;
-  }
-  knn_rerank_vote_kernel<<<(n + 3) / 4, 128, (size_t)4 * d * sizeof(float), st>>>(
+  knn_rerank_vote_kernel<<<n, 128, (size_t)d * sizeof(float), st>>>(
       h->knn_q, h->bank, h->bank_classes ? h->bank_labels : nullptr, h->knn_cand, n, m, d, kc, k,
       metric, h->bank_classes, idx_out, score_out, label_out, counts_out);
   CK(e, cudaGetLastError());
-  h->launches += 4;
+  h->launches += 1;
   return 0;
 }
 

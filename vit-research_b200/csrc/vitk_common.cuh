@@ -424,6 +424,15 @@ __device__ __forceinline__ float gelu_tanh(float x) {  // TF Model Garden activa
   float u = k0 * (x + k1 * x * x * x);
   return 0.5f * x * (1.0f + tanhf(u));
 }
+// Order-preserving map float -> uint32 (larger float <=> larger integer); 0 is below every
+// real value and marks "no row".
+__device__ __forceinline__ uint32_t float_order_bits(float f) {
+  const uint32_t u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float float_from_order_bits(uint32_t k) {  // inverse of the above
+  return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -50,18 +50,36 @@ class BankIndex:
         self.lib = _lib.load()
         self._owner = embedder_or_handle
         self.handle = getattr(embedder_or_handle, "handle", embedder_or_handle)
-        rows = np.ascontiguousarray(rows, dtype=np.float32)
-        rows = rows.reshape(rows.shape[0], -1)
-        self.m, self.d = rows.shape
         self.metric = {"l2": _lib.METRIC_L2, "cosine": _lib.METRIC_COSINE}[metric]
         self.metric_name = metric
         self.n_classes = int(n_classes) if labels is not None else 0
-        self.labels = None if labels is None else np.ascontiguousarray(labels, dtype=np.int32)
-        self.ids = list(ids) if ids is not None else [str(i) for i in range(self.m)]
         self.metadatas = metadatas
-        check(self.lib.vitk_bank_set(self.handle, ptr(rows), self.m, self.d, ptr(self.labels),
-                                     self.n_classes, int(normalise_rows)), self.handle,
-              "vitk_bank_set")
+        if hasattr(rows, "is_cuda"):
+            # a store that already lives on the GPU (e.g. embeddings this library produced, or the
+            # 1 M-row synthetic clip store of BASELINE configs[4]): no host round trip
+            import torch
+            if not rows.is_cuda or rows.dtype != torch.float32:
+                raise VitkError("a tensor bank must be CUDA float32 (numpy arrays go through the host path)")
+            rows = rows.reshape(rows.shape[0], -1).contiguous()
+            self.m, self.d = rows.shape
+            lab = None
+            if labels is not None:
+                lab = torch.as_tensor(labels, dtype=torch.int32, device=rows.device).contiguous()
+                if lab.numel() and (int(lab.min()) < 0 or int(lab.max()) >= max(self.n_classes, 1)):
+                    raise VitkError("vitk_bank_set_device failed: label outside [0,n_classes)")
+            self.labels = None if lab is None else lab.cpu().numpy()
+            check(self.lib.vitk_bank_set_device(self.handle, ptr(rows), self.m, self.d, ptr(lab),
+                                                self.n_classes, int(normalise_rows), stream_ptr(None)),
+                  self.handle, "vitk_bank_set_device")
+        else:
+            rows = np.ascontiguousarray(rows, dtype=np.float32)
+            rows = rows.reshape(rows.shape[0], -1)
+            self.m, self.d = rows.shape
+            self.labels = None if labels is None else np.ascontiguousarray(labels, dtype=np.int32)
+            check(self.lib.vitk_bank_set(self.handle, ptr(rows), self.m, self.d, ptr(self.labels),
+                                         self.n_classes, int(normalise_rows)), self.handle,
+                  "vitk_bank_set")
+        self.ids = list(ids) if ids is not None else None
 
     def search(self, q, k, normalise_queries=False, stream=None):
         """q: CUDA float32 (n,d).  Returns CUDA tensors (idx i32 (n,k), score f32 (n,k),
