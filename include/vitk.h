@@ -135,6 +135,27 @@ int vitk_stream_submit(vitk_handle h, int slot, const uint8_t* frames_host, int 
                        int32_t* counts_host);
 int vitk_stream_wait(vitk_handle h, int slot);
 
+/* ---- vote -> HMM smoothing (the step right after the path) ------------------------------ */
+/* Stands behind class hmm (nba_proj/hmm.py:5-135: add_first, add_col_to_lattice,
+ * decode_sequence) as driven by generate_clips_hmm.py:238-245,484-490: a 3-state
+ * (left,right,none) log-space Viterbi with the reference's fixed transitions, its per-step
+ * Python round(x,3), its tie rules and its backtrace as written (it starts one column early
+ * and reads backpointers one column off; entries 0 and 1 of each sequence come back -1).
+ * Sequences (videos) are independent: frame range [seq_offsets[i], seq_offsets[i+1]) each,
+ * seq_offsets_host has n_seq+1 entries starting at 0.
+ *   counts_dev (T,3) int32 = the vote counts vitk_knn_vote produced with n_classes == 3 and this
+ *   k; with static one-hot banks the reference's emission means are count/k.
+ *   states_out_dev (T) int32 in {0 left,1 right,2 none,-1}; dp_out_dev optional (T,3) float64
+ *   rounded lattice.  Asynchronous on `stream`. */
+int vitk_hmm_decode_counts(vitk_handle h, const int32_t* counts_dev, int k,
+                           const int32_t* seq_offsets_host, int n_seq, int32_t* states_out_dev,
+                           double* dp_out_dev, void* stream);
+/* Same for arbitrary per-frame probabilities (T,3) float64 on the host (the dicts handed to
+ * add_first / add_col_to_lattice); outputs on the host; synchronous. */
+int vitk_hmm_decode_probs_host(vitk_handle h, const double* probs_host,
+                               const int32_t* seq_offsets_host, int n_seq, int32_t* states_out_host,
+                               double* dp_out_host);
+
 /* ---- operator-level entry points (used by the parity tests, one kernel each) ----------- */
 /* C[M,N] = A[M,K] (bf16) · W[N,K]^T (bf16) with epilogue `epi` (VITK_EPI_*).
  * out is bf16 for the *_BF16 epilogues, f32 otherwise (row pitch = N elements). */

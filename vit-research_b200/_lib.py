@@ -60,6 +60,8 @@ SIGNATURES = {
     "vitk_bank_set": (_i, [_vp, _vp, _i, _i, _vp, _i, _i]),
     "vitk_bank_set_device": (_i, [_vp, _vp, _i, _i, _vp, _i, _i, _vp]),
     "vitk_knn_vote": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
+    "vitk_hmm_decode_counts": (_i, [_vp, _vp, _i, _vp, _i, _vp, _vp, _vp]),
+    "vitk_hmm_decode_probs_host": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
     "vitk_op_gemm": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _i, _vp]),
     "vitk_op_gemm_fused": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _i, _f, _vp, _vp, _vp, _vp]),
     "vitk_op_rowstats": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),

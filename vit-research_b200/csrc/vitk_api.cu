@@ -19,6 +19,7 @@
 #include "elementwise.cuh"
 #include "gemm_sm100.cuh"
 #include "knn.cuh"
+#include "hmm.cuh"
 
 using namespace vitk;
 
@@ -406,6 +407,11 @@ struct vitk_ctx {
   int64_t knn_redo_stages = 0;      // stages redone after a pool overflow (diagnostic)
   int32_t *res_idx = nullptr, *res_label = nullptr, *res_counts = nullptr;
   float* res_score = nullptr;
+  // Viterbi workspace (grown on demand)
+  double *hmm_loge = nullptr, *hmm_table = nullptr;
+  int8_t* hmm_bp = nullptr;
+  int* hmm_offsets = nullptr;
+  int hmm_cap_t = 0, hmm_cap_seq = 0, hmm_cap_k = -1;
   cudaStream_t own_stream = nullptr;
   int64_t launches = 0;
   // streaming host API (vitk_stream_submit / vitk_stream_wait): two batches in flight
@@ -464,6 +470,7 @@ void free_ctx(vitk_ctx* c) {
   cudaFree(c->knn_q); cudaFree(c->knn_scores); cudaFree(c->knn_qb); cudaFree(c->knn_cand);
   cudaFree(c->knn_pool); cudaFree(c->knn_pool_n); cudaFree(c->knn_thresh); cudaFree(c->knn_overflow);
   if (c->knn_overflow_host) cudaFreeHost(c->knn_overflow_host);
+  cudaFree(c->hmm_loge); cudaFree(c->hmm_table); cudaFree(c->hmm_bp); cudaFree(c->hmm_offsets);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
   for (auto& sl : c->slots) {
     cudaFree(sl.pix); cudaFree(sl.emb); cudaFree(sl.score); cudaFree(sl.idx); cudaFree(sl.label);
@@ -1219,6 +1226,124 @@ extern "C" int vitk_knn_vote(vitk_handle h, const float* q_dev, int n, int k, in
   CK(e, cudaGetLastError());
   h->launches += 1;
   return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// vote -> HMM smoothing (hmm.py:5-135)
+// ------------------------------------------------------------------------------------------
+namespace {
+HmmParams hmm_params() {
+  HmmParams hp;
+  hp.log_stay = std::log(0.985);
+  hp.log_to_none = std::log(0.015);
+  hp.log_from_none = std::log(0.15);
+  hp.log_none_none = std::log(0.7);
+  hp.log_third = std::log(1.0 / 3.0);
+  return hp;
+}
+
+int hmm_prepare(vitk_ctx* h, const int32_t* seq_offsets_host, int n_seq, int* total, cudaStream_t st) {
+  Err& e = h->err;
+  if (!seq_offsets_host || n_seq < 1) { e.set("vitk_hmm: need at least one sequence"); return 1; }
+  if (seq_offsets_host[0] != 0) { e.set("vitk_hmm: seq_offsets[0] must be 0"); return 1; }
+  for (int i = 0; i < n_seq; ++i)
+    if (seq_offsets_host[i + 1] < seq_offsets_host[i]) { e.set("vitk_hmm: seq_offsets must not decrease"); return 1; }
+  const int T = seq_offsets_host[n_seq];
+  if (T > h->hmm_cap_t || n_seq > h->hmm_cap_seq) {
+    CK(e, cudaStreamSynchronize(st));
+    cudaFree(h->hmm_loge); cudaFree(h->hmm_bp); cudaFree(h->hmm_offsets);
+    h->hmm_loge = nullptr; h->hmm_bp = nullptr; h->hmm_offsets = nullptr;
+    h->hmm_cap_t = h->hmm_cap_seq = 0;
+    const int ct = T > 1 ? T : 1;
+    if (dev_alloc(e, &h->hmm_loge, (size_t)ct * 3) || dev_alloc(e, &h->hmm_bp, (size_t)ct * 3) ||
+        dev_alloc(e, &h->hmm_offsets, (size_t)n_seq + 1))
+      return 1;
+    h->hmm_cap_t = ct;
+    h->hmm_cap_seq = n_seq;
+  }
+  CK(e, cudaMemcpyAsync(h->hmm_offsets, seq_offsets_host, ((size_t)n_seq + 1) * sizeof(int),
+                        cudaMemcpyHostToDevice, st));
+  *total = T;
+  return 0;
+}
+}  // namespace
+
+extern "C" int vitk_hmm_decode_counts(vitk_handle h, const int32_t* counts_dev, int k,
+                                      const int32_t* seq_offsets_host, int n_seq,
+                                      int32_t* states_out_dev, double* dp_out_dev, void* stream) {
+  if (!h) return 1;
+  Err& e = h->err;
+  if (!counts_dev || !states_out_dev || k < 1 || k > 4096) { e.set("vitk_hmm_decode_counts: bad argument"); return 1; }
+  CK(e, cudaSetDevice(h->device));
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  int T = 0;
+  if (hmm_prepare(h, seq_offsets_host, n_seq, &T, st)) return 1;
+  if (T == 0) return 0;
+  if (h->hmm_cap_k != k) {
+    // emission table on the host: std::log is the libm CPython's math.log calls
+    std::vector<double> tab(2 * ((size_t)k + 1));
+    for (int c = 0; c <= k; ++c) {
+      const double p = (double)c / (double)k;
+      tab[c] = std::log(p + 0.000001);                       // hmm.py:36-38
+      tab[(size_t)k + 1 + c] = std::log(c == 0 ? 0.000001 : p);  // hmm.py:45-50
+    }
+    CK(e, cudaStreamSynchronize(st));
+    cudaFree(h->hmm_table);
+    h->hmm_table = nullptr;
+    if (dev_alloc(e, &h->hmm_table, tab.size())) return 1;
+    CK(e, cudaMemcpy(h->hmm_table, tab.data(), tab.size() * sizeof(double), cudaMemcpyHostToDevice));
+    h->hmm_cap_k = k;
+  }
+  hmm_emission_from_counts_kernel<<<n_seq, 256, 0, st>>>(counts_dev, h->hmm_offsets, n_seq, k,
+                                                         h->hmm_table, h->hmm_loge);
+  CK(e, cudaGetLastError());
+  hmm_viterbi_kernel<<<n_seq, 32, 0, st>>>(h->hmm_loge, h->hmm_offsets, n_seq, hmm_params(), h->hmm_bp,
+                                           states_out_dev, dp_out_dev);
+  CK(e, cudaGetLastError());
+  h->launches += 2;
+  return 0;
+}
+
+extern "C" int vitk_hmm_decode_probs_host(vitk_handle h, const double* probs_host,
+                                          const int32_t* seq_offsets_host, int n_seq,
+                                          int32_t* states_out_host, double* dp_out_host) {
+  if (!h) return 1;
+  Err& e = h->err;
+  if (!probs_host || !states_out_host) { e.set("vitk_hmm_decode_probs_host: bad argument"); return 1; }
+  CK(e, cudaSetDevice(h->device));
+  cudaStream_t st = h->own_stream;
+  int T = 0;
+  if (hmm_prepare(h, seq_offsets_host, n_seq, &T, st)) return 1;
+  if (T == 0) return 0;
+  std::vector<double> loge((size_t)T * 3);
+  for (int sq = 0; sq < n_seq; ++sq) {
+    for (int f = seq_offsets_host[sq]; f < seq_offsets_host[sq + 1]; ++f) {
+      const bool first = f == seq_offsets_host[sq];
+      for (int j = 0; j < 3; ++j) {
+        const double p = probs_host[(size_t)f * 3 + j];
+        loge[(size_t)f * 3 + j] = first ? std::log(p + 0.000001) : std::log(p == 0.0 ? 0.000001 : p);
+      }
+    }
+  }
+  int32_t* states_dev = nullptr;
+  double* dp_dev = nullptr;
+  if (dev_alloc(e, &states_dev, (size_t)T)) return 1;
+  if (dp_out_host && dev_alloc(e, &dp_dev, (size_t)T * 3)) { cudaFree(states_dev); return 1; }
+  int rc = 0;
+  do {
+    if (cudaMemcpyAsync(h->hmm_loge, loge.data(), loge.size() * sizeof(double), cudaMemcpyHostToDevice, st) != cudaSuccess) { rc = 1; break; }
+    hmm_viterbi_kernel<<<n_seq, 32, 0, st>>>(h->hmm_loge, h->hmm_offsets, n_seq, hmm_params(), h->hmm_bp,
+                                             states_dev, dp_dev);
+    if (cudaGetLastError() != cudaSuccess) { rc = 1; break; }
+    h->launches += 1;
+    if (cudaMemcpyAsync(states_out_host, states_dev, (size_t)T * 4, cudaMemcpyDeviceToHost, st) != cudaSuccess) { rc = 1; break; }
+    if (dp_out_host && cudaMemcpyAsync(dp_out_host, dp_dev, (size_t)T * 24, cudaMemcpyDeviceToHost, st) != cudaSuccess) { rc = 1; break; }
+    if (cudaStreamSynchronize(st) != cudaSuccess) { rc = 1; break; }
+  } while (false);
+  if (rc) e.set("vitk_hmm_decode_probs_host: CUDA error: %s", cudaGetErrorString(cudaGetLastError()));
+  cudaFree(states_dev);
+  cudaFree(dp_dev);
+  return rc;
 }
 
 // ------------------------------------------------------------------------------------------
