@@ -73,7 +73,8 @@ int vitk_finalize_weights(vitk_handle h);
  * `cls / (norm + 1e-8)` when l2_normalise != 0) — ratt_write_clips_to_ragdb.py:146-153.
  *   pixels_dev : VITK_PIX_F32_NCHW / BF16_NCHW: (n,C,H,W) already rescaled+normalised;
  *                VITK_PIX_U8_NHWC: (n,H,W,C) raw uint8, the HF processor's rescale (1/255) and
- *                normalise ((x-.5)/.5) are applied on the fly (image_processing_vit.py:20-27).
+ *                normalise ((x-.5)/.5) are applied on the fly, fused as transformers 5.5 does:
+ *                (x - 127.5) / 127.5 in float32 (image_processing_vit.py:20-27).
  *   emb_f32_dev: (n, hidden) float32 out.  emb_bf16_dev: optional (n, hidden) bf16 out or NULL. */
 int vitk_embed(vitk_handle h, const void* pixels_dev, int pixel_format, int n, float* emb_f32_dev,
                void* emb_bf16_dev, int l2_normalise, void* stream);
@@ -83,6 +84,21 @@ int vitk_embed(vitk_handle h, const void* pixels_dev, int pixel_format, int n, f
  * synchronous.  frames_host: (n,H,W,C) uint8 (pinned or pageable). emb_host: (n, hidden) f32. */
 int vitk_embed_host_u8(vitk_handle h, const uint8_t* frames_host, int n, float* emb_host,
                        int l2_normalise);
+
+/* ---- preprocessing front-end (the step right before the path) -------------------------- */
+/* Stands behind `processor(images=frames_list, return_tensors="pt")` in hf_vit_embed_batch
+ * (ratt_write_clips_to_ragdb.py:143-146): ViTImageProcessor's resize to the model resolution —
+ * torchvision BILINEAR, antialias=True, on uint8 (image_processing_vit.py:20-27 [3P]) — as one
+ * CUDA kernel, bit-identical (ATen's fixed-point separable algorithm: horizontal pass, uint8
+ * intermediate kept in shared memory, vertical pass).  frames_dev (n,in_h,in_w,C) uint8 ->
+ * out_dev (n,image_h,image_w,C) uint8, which vitk_embed takes as VITK_PIX_U8_NHWC (the fused
+ * rescale+normalise happens there).  Asynchronous on `stream`. */
+int vitk_preprocess_resize_u8(vitk_handle h, const uint8_t* frames_dev, int n, int in_h, int in_w,
+                              uint8_t* out_dev, void* stream);
+/* hf_vit_embed_batch(frames_np) for host frames of ANY size: H2D of the raw frames, resize,
+ * forward in max_batch chunks, D2H of the embeddings; synchronous. */
+int vitk_embed_resize_host_u8(vitk_handle h, const uint8_t* frames_host, int n, int in_h, int in_w,
+                              float* emb_host, int l2_normalise);
 
 /* ---- banks + k-NN vote ---------------------------------------------------------------- */
 /* Replicated embedding bank.  Stands behind np.load('*_embeddings.npz') + the Chroma bank

@@ -1,0 +1,105 @@
+"""ORACLE (test infrastructure only — never imported by the product path).
+
+CPU restatement of the reference's frame preprocessing, i.e. what `processor(images=frames_list,
+return_tensors="pt")` does inside hf_vit_embed_batch (nba_proj/ratt_write_clips_to_ragdb.py:143-146)
+with `ViTImageProcessor` [3P transformers 5.5.0 models/vit/image_processing_vit.py:20-27,
+image_processing_backends.py TorchvisionBackend.resize/_preprocess]:
+  uint8 HWC -> CHW -> torchvision resize to 224x224, BILINEAR, antialias=True, ON UINT8
+  -> fused rescale+normalise (x - 127.5) / 127.5 -> float32 NCHW.
+The uint8 antialiased resize is ATen's separable fixed-point kernel (the Pillow algorithm):
+horizontal pass then vertical pass, uint8 in between, int16 weights with a per-dimension
+precision (aten/src/ATen/native/cpu/UpSampleKernel.cpp: _compute_indices_min_size_weights_aa,
+_compute_index_ranges_int16_weights).  Restated here in numpy.
+
+Pinned: tests/test_oracle_cpu.py checks this restatement bit for bit against the reference's own
+processor (transformers.ViTImageProcessor, importable in this image) on seeded frames, and against
+tests/golden/preprocess_golden.npz produced by it (tools/make_golden_preprocess.py).
+"""
+from __future__ import annotations
+
+import math
+
+import numpy as np
+
+
+def aa_weights(in_size: int, out_size: int):
+    """Per output index: (xmin, xsize, int16 weights[max_interp]) and the shared precision."""
+    scale = in_size / out_size
+    support = 1.0 * scale if scale >= 1.0 else 1.0          # interp_size(2) * 0.5 [* scale]
+    max_interp = int(math.ceil(support)) * 2 + 1
+    invscale = 1.0 / scale if scale >= 1.0 else 1.0
+    xmin = np.zeros(out_size, np.int64)
+    xsize = np.zeros(out_size, np.int64)
+    w = np.zeros((out_size, max_interp), np.float64)
+    wt_max = 0.0
+    for i in range(out_size):
+        center = scale * (i + 0.5)
+        lo = max(int(center - support + 0.5), 0)
+        n = min(int(center + support + 0.5), in_size) - lo
+        n = min(max(n, 0), max_interp)
+        tot = 0.0
+        for j in range(n):
+            x = abs((j + lo - center + 0.5) * invscale)
+            w[i, j] = 1.0 - x if x < 1.0 else 0.0
+            tot += w[i, j]
+        if tot != 0.0:
+            for j in range(n):
+                w[i, j] /= tot
+                wt_max = max(wt_max, w[i, j])
+        xmin[i], xsize[i] = lo, n
+    prec = 0
+    while prec < 22:
+        if int(0.5 + wt_max * (1 << (prec + 1))) >= (1 << 15):
+            break
+        prec += 1
+    wi = np.where(w < 0, (-0.5 + w * (1 << prec)).astype(np.int64), (0.5 + w * (1 << prec)).astype(np.int64))
+    return xmin, xsize, wi.astype(np.int64), prec
+
+
+def _resize_axis_u8(img: np.ndarray, out_size: int, axis: int) -> np.ndarray:
+    in_size = img.shape[axis]
+    if in_size == out_size:
+        return img
+    xmin, xsize, wi, prec = aa_weights(in_size, out_size)
+    src = np.moveaxis(img, axis, 0).astype(np.int64)
+    out = np.empty((out_size,) + src.shape[1:], np.int64)
+    for i in range(out_size):
+        acc = np.full(src.shape[1:], 1 << (prec - 1), np.int64)
+        for j in range(int(xsize[i])):
+            acc += wi[i, j] * src[xmin[i] + j]
+        out[i] = acc >> prec
+    return np.moveaxis(np.clip(out, 0, 255).astype(np.uint8), 0, axis)
+
+
+def resize_u8(frames: np.ndarray, out_h: int = 224, out_w: int = 224) -> np.ndarray:
+    """(N,H,W,C) uint8 -> (N,out_h,out_w,C) uint8: horizontal pass, then vertical."""
+    x = _resize_axis_u8(np.asarray(frames, np.uint8), out_w, 2)
+    return _resize_axis_u8(x, out_h, 1)
+
+
+def pixel_values(frames: np.ndarray, out_h: int = 224, out_w: int = 224) -> np.ndarray:
+    """The processor's output: float32 (N,C,out_h,out_w); rescale and normalise fused the way
+    transformers 5.5 does: (u8 - 127.5) / 127.5 in float32."""
+    r = resize_u8(frames, out_h, out_w).astype(np.float32)
+    r = (r - np.float32(127.5)) / np.float32(127.5)
+    return np.ascontiguousarray(r.transpose(0, 3, 1, 2))
+
+
+GOLDEN_CASES = {"tf_432x768": (432, 768), "hd_180x320": (180, 320), "up_60x90": (60, 90),
+                "tall_300x224": (300, 224), "odd_97x131": (97, 131)}
+
+
+def synthetic_frames(name: str, n: int = 1) -> np.ndarray:
+    """Seeded (n,h,w,3) uint8 inputs of the golden cases, integer arithmetic only (identical on
+    every platform): gradients + blocks + noise, so rounding and the antialias support are hit."""
+    h, w = GOLDEN_CASES[name]
+    rng = np.random.default_rng(sum(map(ord, name)))
+    yy, xx = np.mgrid[0:h, 0:w]
+    out = []
+    for i in range(n):
+        base = (xx * (3 + i) + yy * (5 + 2 * i)) % 256
+        img = np.stack([base, base[::-1], base[:, ::-1]], -1).astype(np.int64)
+        img += rng.integers(-40, 41, (h, w, 3))
+        img[h // 4:h // 2, w // 3:w // 2] = rng.integers(0, 256, 3)
+        out.append(np.clip(img, 0, 255).astype(np.uint8))
+    return np.stack(out)

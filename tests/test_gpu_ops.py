@@ -144,7 +144,7 @@ def test_patchify_is_exact(lib, fmt):
     g = torch.Generator().manual_seed(fmt)
     if fmt == 2:
         pix = torch.randint(0, 256, (n, H, W, C_), generator=g, dtype=torch.uint8).cuda()
-        x = (((pix.float() * (1 / 255.0)) - 0.5) / 0.5).permute(0, 3, 1, 2)
+        x = ((pix.float() - 127.5) / 127.5).permute(0, 3, 1, 2)
     else:
         x = (torch.randn(n, C_, H, W, generator=g) * 0.5).clamp(-1, 1).cuda()
         pix = x if fmt == 0 else x.bfloat16()

@@ -97,7 +97,9 @@ def test_wrong_image_size_raises_like_hf(v, b16):
     with pytest.raises(ValueError):
         emb.embed(torch.zeros(1, 3, 200, 224, device="cuda"))
     with pytest.raises(ValueError):
-        emb.embed_frames(np.zeros((1, 100, 100, 3), np.uint8))
+        emb.embed_frames(np.zeros((1, 100, 100, 4), np.uint8))   # wrong channel count
+    # other frame SIZES no longer raise: like hf_vit_embed_batch, the processor's resize runs first
+    assert emb.embed_frames(np.zeros((1, 100, 100, 3), np.uint8)).shape == (1, 768)
 
 
 def test_chunking_is_invisible(v, b16):

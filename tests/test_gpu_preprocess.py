@@ -1,0 +1,85 @@
+"""GPU parity of the preprocessing front-end through the C ABI: the CUDA
+resize kernel is BIT-EXACT against the restated ATen/Pillow fixed-point algorithm (oracle, pinned
+on the reference's ViTImageProcessor) and against the golden images produced by that processor;
+frames of any size then embed like the reference's hf_vit_embed_batch."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def v():
+    import vit_research_b200 as v
+    assert torch.cuda.is_available()
+    v.load()
+    return v
+
+
+@pytest.fixture(scope="module")
+def model_emb(v):
+    from oracle import vit_ref
+    model = vit_ref.build_hf_model("vit_b16_l2", 0, randomise_ln=True)
+    e = v.ViTEmbedder.from_hf(model, device=0, max_batch=8)
+    yield model, e
+    e.close()
+
+
+def test_resize_matches_golden_images_of_the_reference_processor(v, model_emb, golden_dir):
+    from oracle import preprocess_ref
+    _, emb = model_emb
+    z = np.load(os.path.join(golden_dir, "preprocess_golden.npz"))
+    for c in [str(x) for x in z["cases"]]:
+        f = preprocess_ref.synthetic_frames(c)
+        got = emb.resize_frames(torch.from_numpy(f).cuda()).cpu().numpy()
+        assert np.array_equal(got, z[c + "_out"]), c
+
+
+@pytest.mark.parametrize("hw", [(432, 768), (720, 1280), (1080, 1920), (224, 224), (224, 500), (500, 224),
+                                (17, 23), (225, 223), (2160, 3840)])
+def test_resize_is_bit_exact_against_oracle(v, model_emb, hw):
+    from oracle import preprocess_ref
+    _, emb = model_emb
+    n = 3 if hw[0] * hw[1] < 1_000_000 else 1
+    f = np.random.default_rng(hw[1]).integers(0, 256, (n, hw[0], hw[1], 3), dtype=np.uint8)
+    got = emb.resize_frames(torch.from_numpy(f).cuda()).cpu().numpy()
+    assert np.array_equal(got, preprocess_ref.resize_u8(f))
+
+
+def test_frames_of_any_size_embed_like_the_reference(v, model_emb):
+    """hf_vit_embed_batch on 432x768 frames (the reference's TF-path frame size): processor
+    (oracle) -> HF ViTModel fp32 vs GPU resize -> bf16 forward; cosine >= 0.999 per frame."""
+    from oracle import preprocess_ref, vit_ref
+    model, emb = model_emb
+    f = np.random.default_rng(5).integers(0, 256, (11, 432, 768, 3), dtype=np.uint8)
+    want = vit_ref.hf_embed(model, torch.from_numpy(preprocess_ref.pixel_values(f)), normalise=True)
+    v.install(emb)
+    got = v.hf_vit_embed_batch(f)           # 11 frames > max_batch 8: chunked inside
+    assert got.shape == (11, 768) and got.dtype == np.float32
+    cos = (got * want).sum(1) / (np.linalg.norm(got, axis=1) * np.linalg.norm(want, axis=1))
+    assert cos.min() >= 0.999, cos
+    # identical to resizing explicitly and embedding the 224x224 result
+    small = emb.resize_frames(torch.from_numpy(f).cuda()).cpu().numpy()
+    assert np.array_equal(emb.embed_frames(small), got)
+
+
+def test_build_frame_store_from_image_files(v, model_emb, tmp_path):
+    """build_frame_store (ratt_write_clips_to_ragdb.py:182-233) end to end: PNG files -> PIL loader
+    -> embed -> memmap store the reference's reader opens."""
+    from PIL import Image
+    _, emb = model_emb
+    rng = np.random.default_rng(2)
+    frames = rng.integers(0, 256, (19, 224, 224, 3), dtype=np.uint8)
+    paths = []
+    for i, fr in enumerate(frames):
+        p = str(tmp_path / f"frame_{i:04d}.png")
+        Image.fromarray(fr).save(p)
+        paths.append(p)
+    v.store.build_frame_store(paths, batch_size=8, num_workers=4, store_name="t", embedder=emb,
+                              cache_dir=str(tmp_path / "cache"))
+    mm, fp, idx = v.store.load_frame_store("t", cache_dir=str(tmp_path / "cache"))
+    assert mm.shape == (19, 768) and fp == paths and idx[paths[3]] == 3
+    assert np.array_equal(np.asarray(mm), emb.embed_frames(frames))

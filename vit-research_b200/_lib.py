@@ -57,6 +57,8 @@ SIGNATURES = {
     "vitk_embed_vote_host_u8": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "vitk_stream_submit": (_i, [_vp, _i, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "vitk_stream_wait": (_i, [_vp, _i]),
+    "vitk_preprocess_resize_u8": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),
+    "vitk_embed_resize_host_u8": (_i, [_vp, _vp, _i, _i, _i, _vp, _i]),
     "vitk_bank_set": (_i, [_vp, _vp, _i, _i, _vp, _i, _i]),
     "vitk_bank_set_device": (_i, [_vp, _vp, _i, _i, _vp, _i, _i, _vp]),
     "vitk_knn_vote": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),

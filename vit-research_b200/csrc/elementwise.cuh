@@ -8,7 +8,7 @@ namespace vitk {
 enum PixelFormat : int {
   PIX_F32_NCHW = 0,  // HF pixel_values (N,3,H,W) float32, already rescaled/normalised
   PIX_BF16_NCHW = 1, // same, bf16
-  PIX_U8_NHWC = 2,   // raw frames (N,H,W,3) uint8; the kernel applies x/255 then (x-mean)/std
+  PIX_U8_NHWC = 2,   // raw frames (N,H,W,3) uint8; the kernel applies (x - 127.5) / 127.5
 };
 
 struct PatchifyParams {
@@ -16,7 +16,7 @@ struct PatchifyParams {
   __nv_bfloat16* out;  // [n*(P+1), K]   row f*(P+1) is the all-zero CLS row
   int n, C, H, W, ps, gh, gw, K;
   int fmt;
-  float scale, mean, inv_std;  // u8 path: v = (x*scale - mean) * inv_std   (HF: 1/255, .5, 2)
+  float mean, std;  // u8 path: v = (x - mean) / std   (HF fused rescale+normalise: 127.5, 127.5)
 };
 
 // im2col for a stride==kernel convolution (HF modeling_vit.py:151,167): K index = (c, ky, kx).
@@ -58,10 +58,9 @@ __global__ void __launch_bounds__(256) patchify_kernel(const PatchifyParams p) {
                            (((size_t)f * p.H + y) * p.W + x) * p.C + c;
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-          // separate roundings (no FMA contraction): bit-identical to the HF processor's
-          // float32 rescale-then-normalise (image_processing_vit.py:20-27)
-          float u = __fmul_rn((float)s[j * p.C], p.scale);
-          v[j] = __fmul_rn(__fsub_rn(u, p.mean), p.inv_std);
+          // bit-identical to the HF processor's fused float32 rescale+normalise
+          // (transformers 5.5 image_processing_backends.py: tvF.normalize(x, 127.5, 127.5))
+          v[j] = __fdiv_rn(__fsub_rn((float)s[j * p.C], p.mean), p.std);
         }
         o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]);
         o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);

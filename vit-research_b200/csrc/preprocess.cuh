@@ -1,0 +1,95 @@
+// preprocess.cuh — the step right before the hot path: raw uint8 HWC frames of any size ->
+// uint8 frames at the model's resolution, bit-identical to what the reference's processor feeds
+// the model.  Reference: `processor(images=frames_list, return_tensors="pt")` inside
+// hf_vit_embed_batch (nba_proj/ratt_write_clips_to_ragdb.py:143-146) = ViTImageProcessor
+// [3P transformers 5.5 image_processing_vit.py:20-27] -> torchvision resize (BILINEAR,
+// antialias=True) ON UINT8 -> ATen's separable fixed-point kernel (the Pillow algorithm):
+// horizontal pass, uint8 intermediate, vertical pass, int16 weights with a per-dimension
+// precision.  The weight tables are built on the host in double exactly as ATen does
+// (vitk_api.cu: build_resize_axis); this kernel only does the integer arithmetic, so the result
+// is bit-exact by construction.  The fused rescale+normalise happens in patchify_kernel.
+//
+// HBM-bound byte work: one CTA produces TY output rows of one frame.  It runs the horizontal
+// pass for the input rows those outputs need into shared memory (uint8, out_w*C bytes per
+// row), then the vertical pass out of shared memory, so the intermediate image never touches
+// HBM and each input byte is read from HBM once (plus the vertical-support overlap between
+// neighbouring CTAs, which hits L2).
+#pragma once
+#include "vitk_common.cuh"
+
+namespace vitk {
+
+struct ResizeAxis {     // device pointers into one table blob
+  const int* xmin;      // [out]
+  const int* xsize;     // [out]
+  const short* w;       // [out, taps]
+  int taps;             // max_interp_size
+  int prec;             // weights precision (bits)
+  int in_size, out_size;
+};
+
+struct ResizeParams {
+  const uint8_t* in;    // (n, in_h, in_w, C)
+  uint8_t* out;         // (n, out_h, out_w, C)
+  int n, C;
+  ResizeAxis hx, vy;    // horizontal (width) and vertical (height) tables
+  int ty;               // output rows per CTA
+  int max_rows;         // input rows a CTA may need (shared-memory rows)
+};
+
+__device__ __forceinline__ uint8_t clip8(int v) { return (uint8_t)(v < 0 ? 0 : (v > 255 ? 255 : v)); }
+
+__global__ void __launch_bounds__(256) resize_u8_aa_kernel(const ResizeParams p) {
+  extern __shared__ uint8_t rs_smem[];  // [max_rows][out_w*C] horizontally resized rows
+  const int f = blockIdx.y;
+  const int y0 = blockIdx.x * p.ty;
+  const int y1 = min(y0 + p.ty, p.vy.out_size);
+  const int in_w = p.hx.in_size, out_w = p.hx.out_size, in_h = p.vy.in_size, out_h = p.vy.out_size;
+  const int C = p.C;
+  const int row_elems = out_w * C;
+  // input rows [r0, r1) feed output rows [y0, y1)
+  const int r0 = p.vy.xmin[y0];
+  int r1 = r0;
+  for (int y = y0; y < y1; ++y) r1 = max(r1, p.vy.xmin[y] + p.vy.xsize[y]);
+  const int rows = min(r1 - r0, p.max_rows);
+  const uint8_t* src = p.in + (size_t)f * in_h * in_w * C;
+  // ---- horizontal pass (ATen: ImagingResampleHorizontal) ----
+  const bool h_identity = in_w == out_w;
+  for (int i = threadIdx.x; i < rows * row_elems; i += blockDim.x) {
+    const int r = i / row_elems, e = i - r * row_elems;
+    const int x = e / C, c = e - x * C;
+    const uint8_t* line = src + (size_t)(r0 + r) * in_w * C;
+    uint8_t v;
+    if (h_identity) {
+      v = line[e];
+    } else {
+      const int lo = p.hx.xmin[x], cnt = p.hx.xsize[x];
+      const short* w = p.hx.w + (size_t)x * p.hx.taps;
+      int acc = 1 << (p.hx.prec - 1);
+      for (int j = 0; j < cnt; ++j) acc += (int)w[j] * (int)line[(lo + j) * C + c];
+      v = clip8(acc >> p.hx.prec);
+    }
+    rs_smem[i] = v;
+  }
+  __syncthreads();
+  // ---- vertical pass (ATen: ImagingResampleVertical) ----
+  const bool v_identity = in_h == out_h;
+  uint8_t* dst = p.out + (size_t)f * out_h * row_elems;
+  for (int i = threadIdx.x; i < (y1 - y0) * row_elems; i += blockDim.x) {
+    const int yy = i / row_elems, e = i - yy * row_elems;
+    const int y = y0 + yy;
+    uint8_t v;
+    if (v_identity) {
+      v = rs_smem[(size_t)(y - r0) * row_elems + e];
+    } else {
+      const int lo = p.vy.xmin[y] - r0, cnt = p.vy.xsize[y];
+      const short* w = p.vy.w + (size_t)y * p.vy.taps;
+      int acc = 1 << (p.vy.prec - 1);
+      for (int j = 0; j < cnt; ++j) acc += (int)w[j] * (int)rs_smem[(size_t)(lo + j) * row_elems + e];
+      v = clip8(acc >> p.vy.prec);
+    }
+    dst[(size_t)y * row_elems + e] = v;
+  }
+}
+
+}  // namespace vitk

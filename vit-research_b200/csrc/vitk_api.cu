@@ -4,6 +4,7 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -20,6 +21,7 @@
 #include "gemm_sm100.cuh"
 #include "knn.cuh"
 #include "hmm.cuh"
+#include "preprocess.cuh"
 
 using namespace vitk;
 
@@ -321,9 +323,8 @@ int launch_patchify(Err& e, const void* pix, int fmt, __nv_bfloat16* out, int n,
   p.gh = H / ps; p.gw = W / ps;
   p.K = C * ps * ps;
   p.fmt = fmt;
-  p.scale = 1.0f / 255.0f;  // HF ViTImageProcessor: rescale_factor 1/255, mean .5, std .5
-  p.mean = 0.5f;
-  p.inv_std = 2.0f;
+  p.mean = 127.5f;  // HF ViTImageProcessor: rescale 1/255, mean .5, std .5, fused
+  p.std = 127.5f;
   long long total = (long long)n * (p.gh * p.gw + 1) * (p.K / 8);
   long long blocks = (total + 255) / 256;
   if (blocks > 148 * 32) blocks = 148 * 32;
@@ -407,6 +408,16 @@ struct vitk_ctx {
   int64_t knn_redo_stages = 0;      // stages redone after a pool overflow (diagnostic)
   int32_t *res_idx = nullptr, *res_label = nullptr, *res_counts = nullptr;
   float* res_score = nullptr;
+  // resize plans: weight tables per input geometry (built once, kept on the device)
+  struct ResizePlan {
+    void* blob = nullptr;
+    ResizeAxis hx{}, vy{};
+    int ty = 0, max_rows = 0;
+    size_t smem = 0;
+  };
+  std::map<std::pair<int, int>, ResizePlan> resize_plans;
+  uint8_t* raw_stage = nullptr;   // device staging for raw frames of vitk_embed_resize_host_u8
+  size_t raw_stage_bytes = 0;
   // Viterbi workspace (grown on demand)
   double *hmm_loge = nullptr, *hmm_table = nullptr;
   int8_t* hmm_bp = nullptr;
@@ -471,6 +482,8 @@ void free_ctx(vitk_ctx* c) {
   cudaFree(c->knn_pool); cudaFree(c->knn_pool_n); cudaFree(c->knn_thresh); cudaFree(c->knn_overflow);
   if (c->knn_overflow_host) cudaFreeHost(c->knn_overflow_host);
   cudaFree(c->hmm_loge); cudaFree(c->hmm_table); cudaFree(c->hmm_bp); cudaFree(c->hmm_offsets);
+  for (auto& kv : c->resize_plans) cudaFree(kv.second.blob);
+  cudaFree(c->raw_stage);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
   for (auto& sl : c->slots) {
     cudaFree(sl.pix); cudaFree(sl.emb); cudaFree(sl.score); cudaFree(sl.idx); cudaFree(sl.label);
@@ -1225,6 +1238,178 @@ extern "C" int vitk_knn_vote(vitk_handle h, const float* q_dev, int n, int k, in
       metric, h->bank_classes, idx_out, score_out, label_out, counts_out);
   CK(e, cudaGetLastError());
   h->launches += 1;
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// preprocessing front-end: antialiased bilinear uint8 resize (preprocess.cuh)
+// ------------------------------------------------------------------------------------------
+namespace {
+struct HostAxis {
+  std::vector<int> xmin, xsize;
+  std::vector<short> w;
+  int taps = 0, prec = 0;
+};
+
+// ATen UpSampleKernel.cpp: _compute_indices_min_size_weights_aa + _compute_index_ranges_int16_weights
+// for the bilinear filter (interp_size 2, align_corners false), all in double.
+HostAxis build_resize_axis(int in_size, int out_size) {
+  HostAxis a;
+  const double scale = (double)in_size / (double)out_size;
+  const double support = scale >= 1.0 ? 1.0 * scale : 1.0;
+  a.taps = (int)std::ceil(support) * 2 + 1;
+  const double invscale = scale >= 1.0 ? 1.0 / scale : 1.0;
+  a.xmin.resize(out_size);
+  a.xsize.resize(out_size);
+  std::vector<double> wd((size_t)out_size * a.taps, 0.0);
+  double wt_max = 0.0;
+  for (int i = 0; i < out_size; ++i) {
+    const double center = scale * (i + 0.5);
+    long long lo = (long long)(center - support + 0.5);
+    if (lo < 0) lo = 0;
+    long long hi = (long long)(center + support + 0.5);
+    if (hi > in_size) hi = in_size;
+    long long n = hi - lo;
+    if (n < 0) n = 0;
+    if (n > a.taps) n = a.taps;
+    double tot = 0.0;
+    double* w = wd.data() + (size_t)i * a.taps;
+    for (long long j = 0; j < n; ++j) {
+      double x = ((double)(j + lo) - center + 0.5) * invscale;
+      if (x < 0.0) x = -x;
+      w[j] = x < 1.0 ? 1.0 - x : 0.0;
+      tot += w[j];
+    }
+    if (tot != 0.0)
+      for (long long j = 0; j < n; ++j) {
+        w[j] /= tot;
+        if (w[j] > wt_max) wt_max = w[j];
+      }
+    a.xmin[i] = (int)lo;
+    a.xsize[i] = (int)n;
+  }
+  int prec = 0;
+  for (; prec < 22; ++prec) {
+    const int next = (int)(0.5 + wt_max * (double)(1 << (prec + 1)));
+    if (next >= (1 << 15)) break;
+  }
+  a.prec = prec;
+  a.w.resize(wd.size());
+  for (size_t i = 0; i < wd.size(); ++i)
+    a.w[i] = (short)(wd[i] < 0 ? (int)(-0.5 + wd[i] * (double)(1 << prec)) : (int)(0.5 + wd[i] * (double)(1 << prec)));
+  return a;
+}
+
+int get_resize_plan(vitk_ctx* h, int in_h, int in_w, vitk_ctx::ResizePlan** out) {
+  Err& e = h->err;
+  auto key = std::make_pair(in_h, in_w);
+  auto it = h->resize_plans.find(key);
+  if (it != h->resize_plans.end()) { *out = &it->second; return 0; }
+  const int out_h = h->cfg.image_h, out_w = h->cfg.image_w, C = h->cfg.channels;
+  HostAxis hx = build_resize_axis(in_w, out_w), vy = build_resize_axis(in_h, out_h);
+  // one blob: hx.xmin | hx.xsize | vy.xmin | vy.xsize | hx.w | vy.w
+  const size_t ints = (size_t)2 * out_w + 2 * out_h;
+  const size_t bytes = ints * 4 + (hx.w.size() + vy.w.size()) * 2;
+  std::vector<uint8_t> blob(bytes);
+  int* ip = reinterpret_cast<int*>(blob.data());
+  memcpy(ip, hx.xmin.data(), (size_t)out_w * 4);
+  memcpy(ip + out_w, hx.xsize.data(), (size_t)out_w * 4);
+  memcpy(ip + 2 * out_w, vy.xmin.data(), (size_t)out_h * 4);
+  memcpy(ip + 2 * out_w + out_h, vy.xsize.data(), (size_t)out_h * 4);
+  short* sp = reinterpret_cast<short*>(blob.data() + ints * 4);
+  memcpy(sp, hx.w.data(), hx.w.size() * 2);
+  memcpy(sp + hx.w.size(), vy.w.data(), vy.w.size() * 2);
+  vitk_ctx::ResizePlan pl;
+  uint8_t* dev = nullptr;
+  if (dev_alloc(e, &dev, bytes)) return 1;
+  CK(e, cudaMemcpy(dev, blob.data(), bytes, cudaMemcpyHostToDevice));
+  pl.blob = dev;
+  const int* dip = reinterpret_cast<const int*>(dev);
+  const short* dsp = reinterpret_cast<const short*>(dev + ints * 4);
+  pl.hx = ResizeAxis{dip, dip + out_w, dsp, hx.taps, hx.prec, in_w, out_w};
+  pl.vy = ResizeAxis{dip + 2 * out_w, dip + 2 * out_w + out_h, dsp + hx.w.size(), vy.taps, vy.prec, in_h, out_h};
+  // output rows per CTA: as many as keep the horizontally resized input rows within 96 KB
+  const size_t row_bytes = (size_t)out_w * C;
+  int ty = 16;
+  int max_rows = 0;
+  for (; ty >= 1; ty /= 2) {
+    max_rows = 0;
+    for (int y0 = 0; y0 < out_h; y0 += ty) {
+      int r1 = 0;
+      const int y1 = y0 + ty < out_h ? y0 + ty : out_h;
+      for (int y = y0; y < y1; ++y) r1 = std::max(r1, vy.xmin[y] + vy.xsize[y]);
+      max_rows = std::max(max_rows, r1 - vy.xmin[y0]);
+    }
+    if ((size_t)max_rows * row_bytes <= 96 * 1024) break;
+  }
+  if (ty < 1) { cudaFree(dev); e.set("resize: %dx%d -> %dx%d needs too much shared memory", in_h, in_w, out_h, out_w); return 1; }
+  pl.ty = ty;
+  pl.max_rows = max_rows;
+  pl.smem = (size_t)max_rows * row_bytes;
+  static bool attr_set = false;
+  if (!attr_set) {
+    CK(e, cudaFuncSetAttribute(resize_u8_aa_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+    attr_set = true;
+  }
+  *out = &h->resize_plans.emplace(key, pl).first->second;
+  return 0;
+}
+
+int launch_resize(vitk_ctx* h, const uint8_t* in_dev, int n, int in_h, int in_w, uint8_t* out_dev,
+                  cudaStream_t st) {
+  Err& e = h->err;
+  vitk_ctx::ResizePlan* pl = nullptr;
+  if (get_resize_plan(h, in_h, in_w, &pl)) return 1;
+  ResizeParams p;
+  p.in = in_dev; p.out = out_dev; p.n = n; p.C = h->cfg.channels;
+  p.hx = pl->hx; p.vy = pl->vy; p.ty = pl->ty; p.max_rows = pl->max_rows;
+  dim3 grid((unsigned)((h->cfg.image_h + pl->ty - 1) / pl->ty), (unsigned)n, 1);
+  resize_u8_aa_kernel<<<grid, 256, pl->smem, st>>>(p);
+  CK(e, cudaGetLastError());
+  h->launches += 1;
+  return 0;
+}
+}  // namespace
+
+extern "C" int vitk_preprocess_resize_u8(vitk_handle h, const uint8_t* frames_dev, int n, int in_h,
+                                         int in_w, uint8_t* out_dev, void* stream) {
+  if (!h) return 1;
+  Err& e = h->err;
+  if (!frames_dev || !out_dev || n < 0 || in_h < 1 || in_w < 1) { e.set("vitk_preprocess_resize_u8: bad argument"); return 1; }
+  if (n == 0) return 0;
+  if (n > 65535) { e.set("vitk_preprocess_resize_u8: at most 65535 frames per call"); return 1; }
+  CK(e, cudaSetDevice(h->device));
+  return launch_resize(h, frames_dev, n, in_h, in_w, out_dev, reinterpret_cast<cudaStream_t>(stream));
+}
+
+extern "C" int vitk_embed_resize_host_u8(vitk_handle h, const uint8_t* frames_host, int n, int in_h,
+                                         int in_w, float* emb_host, int l2_normalise) {
+  if (!h) return 1;
+  Err& e = h->err;
+  if (!h->finalized) { e.set("vitk_embed_resize_host_u8: weights not finalized"); return 1; }
+  if (!frames_host || !emb_host || n < 0 || in_h < 1 || in_w < 1) { e.set("vitk_embed_resize_host_u8: bad argument"); return 1; }
+  CK(e, cudaSetDevice(h->device));
+  cudaStream_t st = h->own_stream;
+  const size_t fb = (size_t)in_h * in_w * h->cfg.channels;
+  const int mb = h->cfg.max_batch;
+  if (h->raw_stage_bytes < fb * mb) {
+    CK(e, cudaStreamSynchronize(st));
+    cudaFree(h->raw_stage);
+    h->raw_stage = nullptr;
+    h->raw_stage_bytes = 0;
+    if (dev_alloc(e, &h->raw_stage, fb * mb)) return 1;
+    h->raw_stage_bytes = fb * mb;
+  }
+  for (int off = 0; off < n; off += mb) {
+    const int cn = n - off < mb ? n - off : mb;
+    CK(e, cudaMemcpyAsync(h->raw_stage, frames_host + (size_t)off * fb, (size_t)cn * fb,
+                          cudaMemcpyHostToDevice, st));
+    if (launch_resize(h, h->raw_stage, cn, in_h, in_w, h->pix_stage, st)) return 1;
+    if (forward_chunk(h, h->pix_stage, PIX_U8_NHWC, cn, h->emb, nullptr, l2_normalise, st)) return 1;
+    CK(e, cudaMemcpyAsync(emb_host + (size_t)off * h->D, h->emb, (size_t)cn * h->D * 4,
+                          cudaMemcpyDeviceToHost, st));
+  }
+  CK(e, cudaStreamSynchronize(st));
   return 0;
 }
 

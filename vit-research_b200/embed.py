@@ -180,6 +180,24 @@ class ViTEmbedder:
                                   int(l2_normalise), stream_ptr(stream)), self.handle, "vitk_embed")
         return out
 
+    def resize_frames(self, frames, out=None, stream=None):
+        """CUDA uint8 (N,H,W,C) frames of any size -> CUDA uint8 (N,image_h,image_w,C): the HF
+        processor's resize (BILINEAR, antialias, on uint8) as one kernel, bit-identical."""
+        import torch
+
+        g = self.geometry
+        if not frames.is_cuda or frames.dtype != torch.uint8 or frames.dim() != 4 or \
+                frames.shape[3] != g.channels:
+            raise VitkError(f"resize_frames() wants a CUDA uint8 (N,H,W,{g.channels}) tensor")
+        frames = frames.contiguous()
+        n, ih, iw = frames.shape[:3]
+        if out is None:
+            out = torch.empty((n, g.image_h, g.image_w, g.channels), dtype=torch.uint8, device=frames.device)
+        check(self.lib.vitk_preprocess_resize_u8(self.handle, ptr(frames), n, ih, iw, ptr(out),
+                                                 stream_ptr(stream)), self.handle,
+              "vitk_preprocess_resize_u8")
+        return out
+
     # ---- host path (what hf_vit_embed_batch does) -----------------------------------------
     def embed_frames(self, frames_np: np.ndarray, l2_normalise: bool = True) -> np.ndarray:
         """(N,H,W,3) uint8 host frames at the model's resolution -> (N,hidden) float32 host."""
@@ -187,9 +205,17 @@ class ViTEmbedder:
         frames_np = np.ascontiguousarray(frames_np)
         if frames_np.dtype != np.uint8:
             raise VitkError("embed_frames wants uint8")
-        if frames_np.ndim != 4 or frames_np.shape[1:] != (g.image_h, g.image_w, g.channels):
-            raise ValueError(f"frames {frames_np.shape} do not match (N,{g.image_h},{g.image_w},"
-                             f"{g.channels}); resize upstream (GPU resize is a SURVEY §8f item)")
+        if frames_np.ndim != 4 or frames_np.shape[3] != g.channels:
+            raise ValueError(f"frames {frames_np.shape} are not (N,H,W,{g.channels})")
+        if frames_np.shape[1:3] != (g.image_h, g.image_w):
+            # any other size: the processor's antialiased bilinear uint8 resize runs on the GPU
+            # (preprocess.cuh), bit-identical to ViTImageProcessor
+            n, ih, iw = frames_np.shape[:3]
+            out = np.empty((n, g.hidden), dtype=np.float32)
+            check(self.lib.vitk_embed_resize_host_u8(self.handle, ptr(frames_np), n, ih, iw, ptr(out),
+                                                     int(l2_normalise)), self.handle,
+                  "vitk_embed_resize_host_u8")
+            return out
         n = frames_np.shape[0]
         out = np.empty((n, g.hidden), dtype=np.float32)
         if n > self.max_batch and l2_normalise:
