@@ -23,4 +23,4 @@ for g in range(2):
     for j in range(12):
         r = t[g, j, :6] - t0
         d = [r[1] - r[0], r[2] - r[1], r[3] - r[2], r[4] - r[3], r[5] - r[4]]
-        print(f"g{g} j{j:2d} blk{g ^ (j & 1)}  start {r[0]:7d}  wait_S {d[0]:5d}  pass1 {d[1]:5d}  pass2 {d[2]:5d}  wait_O {d[3]:5d}  epi {d[4]:5d}  total {r[5]-r[0]:6d}")
+        print(f"g{g} j{j:2d} blk{g ^ (j & 1)}  start {r[0]:7d}  wait_S {d[0]:5d}  pass1 {d[1]:5d}  pass2 {d[2]:5d}  wait_O {d[3]:5d}  epi {d[4]:5d}  total {r[5]-r[0]:6d}  | PV issue after P {t[g, j, 6] - t0 - r[3]:5d}  issue took {t[g, j, 7] - t[g, j, 6]:5d}  O after commit {r[4] - (t[g, j, 7] - t0):5d}")

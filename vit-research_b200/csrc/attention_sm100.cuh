@@ -265,6 +265,37 @@ attention_v2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 // MMAs, loads and stores proceed.  v2 ran 2 independent CTAs/SM with every phase serialised
 // inside a CTA and K/V loaded twice (127 us/layer at 256 frames).
 // =============================================================================================
+// ---- softmax building blocks of the v3 fast path (one thread == one query row) ----
+// The compiler must not move arithmetic on registers filled by an in-flight tcgen05.ld above the
+// tcgen05.wait::ld that completes it: thread the registers through an empty asm after the wait.
+__device__ __forceinline__ void reg_fence16(uint32_t* r) {
+  asm volatile("" : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]),
+                    "+r"(r[7]), "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]),
+                    "+r"(r[13]), "+r"(r[14]), "+r"(r[15]));
+}
+// exp2(s*scale - mxs) (exponent clamped at 100) of NC = 32 or 16 scores starting at column c0 ->
+// bf16 pairs stored over S cells [c0/2, c0/2 + NC/2) (already consumed); accumulates row sums.
+template <int NC>
+__device__ __forceinline__ void att_exp_chunk(const uint32_t* v, int c0, int S, float scale, float mxs,
+                                              float (&s4)[4], uint32_t t_slot) {
+  uint32_t pk[NC / 2];
+  const bool full = c0 + NC <= S;
+#pragma unroll
+  for (int i = 0; i < NC / 2; ++i) {
+    const float x0 = fminf(fmaf(__uint_as_float(v[2 * i]), scale, -mxs), 100.f);
+    const float x1 = fminf(fmaf(__uint_as_float(v[2 * i + 1]), scale, -mxs), 100.f);
+    float e0 = ex2_approx(x0), e1 = ex2_approx(x1);
+    if (!full) {
+      e0 = (c0 + 2 * i < S) ? e0 : 0.f;
+      e1 = (c0 + 2 * i + 1 < S) ? e1 : 0.f;
+    }
+    s4[i & 3] += e0 + e1;
+    pk[i] = pack_bf16x2(e0, e1);
+  }
+  if constexpr (NC == 32) tmem_st_32x32b_x16(t_slot + (c0 >> 1), *reinterpret_cast<const uint32_t(*)[16]>(pk));
+  else tmem_st_32x32b_x8(t_slot + (c0 >> 1), *reinterpret_cast<const uint32_t(*)[8]>(pk));
+}
+
 constexpr int ATT3_THREADS = 384;
 constexpr int ATT3_STAGES = 2;
 
@@ -298,7 +329,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   uint64_t* o_full = bars + 10;      // [2] slot
   uint64_t* slot_free = bars + 12;   // [2] slot, count 4
   uint64_t* redo_bar = bars + 14;    // [2] slot: exact-path recomputation of S
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
+  uint64_t* turn_bar = bars + 16;    // [2] group: "your turn on the exp2 units", count 4
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 18);
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
@@ -320,6 +352,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       mbar_init(&o_full[i], 1);
       mbar_init(&slot_free[i], 4);
       mbar_init(&redo_bar[i], 1);
+      mbar_init(&turn_bar[i], 4);
     }
     fence_mbar_init();
   }
@@ -382,14 +415,20 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           } else {
             if (!mbar_test_wait(&p_full[s], uph) || !mbar_test_wait(&v_full[st], sph)) continue;
             tc_fence_after_sync();
+            const bool mdbg = p.dbg != nullptr && blockIdx.x == 0 && j < 16;
+            if (mdbg) p.dbg[(s * 16 + j) * 8 + 6] = clock64();
             if (b < nblk) {
               const uint32_t sv = smem_u32(sb + 32768 + L.kv_bytes);
-              for (int kk = 0; kk < SK / 16; ++kk) {
-                const uint64_t dv = make_smem_desc_sw128(sv + kk * 16 * 128, 1024, 1024);
-                umma_bf16_ts(t_slot + SK / 2, t_slot + kk * 8, dv, idesc_o, kk != 0 ? 1u : 0u);
-              }
+              // descriptor of K-step kk = first one + kk * (16 rows * 128 B >> 4) in the address field
+              const uint64_t dv0 = make_smem_desc_sw128(sv, 1024, 1024);
+              const uint32_t t_o_acc = t_slot + SK / 2;
+              umma_bf16_ts(t_o_acc, t_slot, dv0, idesc_o, 0u);
+#pragma unroll 4
+              for (int kk = 1; kk < SK / 16; ++kk)
+                umma_bf16_ts(t_o_acc, t_slot + kk * 8, dv0 + (uint64_t)(kk * 128), idesc_o, 1u);
             }
             umma_commit(&o_full[s]);
+            if (mdbg) p.dbg[(s * 16 + j) * 8 + 7] = clock64();
             phs[s] = 0;
             uj[s] = j + 1;
           }
@@ -426,6 +465,14 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       long long* dbg = p.dbg + (g * 16 + j) * 8;
       if (dbg_on) dbg[0] = clock64();
       mbar_wait(&s_full[g], uph);
+      // The two warpgroups take turns in the softmax: g0(unit j) -> g1(unit j) -> g0(unit j+1) ...
+      // Left alone they run in lock-step — both in the exp2 loop at once (the MUFU pipe is the
+      // loop's bound, so the pass takes twice as long), then both waiting while the single MMA
+      // thread issues their two P.V chains back to back (~1100 cycles each: 13 instructions at
+      // ~85 cycles).  Alternating puts one group's MMAs / epilogue / next S under the other
+      // group's exp2 pass (tools/dev_attn_timeline.py: 8300 -> ~5500 cycles per unit).
+      if (g == 0) { if (j > 0) mbar_wait(&turn_bar[0], (uint32_t)(j - 1) & 1u); }
+      else mbar_wait(&turn_bar[1], uph);
       tc_fence_after_sync();
       if (dbg_on) dbg[1] = clock64();
       float sum = 0.f;
@@ -506,8 +553,50 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       // observed on real activations) shows up as a huge / non-finite sum ...
       bool redo = false;
       if (warp_active) {
-        const float mxs = max_pass(32) * p.scale_log2e;
-        sum = exp_pass(mxs, true);
+        // Software-pipelined: the tcgen05.ld of chunk c+1 is in flight while chunk c goes
+        // through the exp2 loop (two register buffers), and the first chunk serves both the
+        // shift estimate and the first exp2 pass — with two softmax warps per scheduler the
+        // TMEM load latency was otherwise exposed once per chunk.
+        uint32_t va[32], vb[32];
+        const int n32 = SK >> 5;
+        const bool tail = (SK & 16) != 0;
+        if (n32 > 0) tmem_ld_32x32b_x32(t_slot, va);
+        else tmem_ld_32x32b_x16(t_slot, *reinterpret_cast<uint32_t(*)[16]>(va));
+        tmem_ld_wait();
+        reg_fence16(va);
+        if (n32 > 0) reg_fence16(va + 16);
+        float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        const int first = n32 > 0 ? 32 : 16;
+#pragma unroll
+        for (int i = 0; i < 32; ++i)
+          if (i < first && i < S) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(va[i]));
+        const float mxs = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])) * p.scale_log2e;
+        float s4[4] = {0.f, 0.f, 0.f, 0.f};
+        int c = 0;
+        for (; c + 2 <= n32; c += 2) {  // va holds chunk c
+          tmem_ld_32x32b_x32(t_slot + (c + 1) * 32, vb);
+          att_exp_chunk<32>(va, c * 32, S, p.scale_log2e, mxs, s4, t_slot);
+          tmem_ld_wait();
+          reg_fence16(vb);
+          reg_fence16(vb + 16);
+          if (c + 2 < n32) tmem_ld_32x32b_x32(t_slot + (c + 2) * 32, va);
+          else if (tail) tmem_ld_32x32b_x16(t_slot + (c + 2) * 32, *reinterpret_cast<uint32_t(*)[16]>(va));
+          att_exp_chunk<32>(vb, (c + 1) * 32, S, p.scale_log2e, mxs, s4, t_slot);
+          tmem_ld_wait();
+          reg_fence16(va);
+          reg_fence16(va + 16);
+        }
+        if (c < n32) {  // odd number of 32-column chunks: va holds the last one
+          if (tail) tmem_ld_32x32b_x16(t_slot + (c + 1) * 32, *reinterpret_cast<uint32_t(*)[16]>(vb));
+          att_exp_chunk<32>(va, c * 32, S, p.scale_log2e, mxs, s4, t_slot);
+          tmem_ld_wait();
+          reg_fence16(vb);
+          if (tail) att_exp_chunk<16>(vb, (c + 1) * 32, S, p.scale_log2e, mxs, s4, t_slot);
+        } else if (tail) {  // va holds the 16-column tail
+          att_exp_chunk<16>(va, n32 * 32, S, p.scale_log2e, mxs, s4, t_slot);
+        }
+        tmem_st_wait();
+        sum = (s4[0] + s4[1]) + (s4[2] + s4[3]);
         redo = !(sum < 1.0e30f);
       }
       if (dbg_on) dbg[2] = clock64();
@@ -538,7 +627,10 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       }
       tc_fence_before_sync();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&p_full[g]);
+      if (lane == 0) {
+        mbar_arrive(&p_full[g]);
+        mbar_arrive(&turn_bar[g ^ 1]);  // hand the exp2 units to the other warpgroup
+      }
       if (dbg_on) dbg[3] = clock64();
 
       mbar_wait(&o_full[g], uph);
