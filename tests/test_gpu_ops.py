@@ -236,7 +236,7 @@ def test_residual_gemm_emits_copy_and_row_sums(lib, M, N, K, inplace):
 
 
 def test_gelu_polynomial_matches_erf_form(lib):
-    """The epilogue's degree-6 exponent polynomial vs torch's exact erf GELU over [-9, 9]."""
+    """The epilogue exponent polynomial (packed-fp32 degree-5 form) vs torch exact erf GELU over [-9, 9]."""
     dev = "cuda:0"
     M, N, K = 256, 4096, 64
     xs = torch.linspace(-9, 9, M * N, device=dev).reshape(M, N)

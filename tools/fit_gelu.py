@@ -5,7 +5,8 @@ A=6.0
 a = np.linspace(0, A, 200001)
 target = np.log2(0.5*erfc(a/np.sqrt(2)))
 w = a*0.5*erfc(a/np.sqrt(2)) + 1e-4   # abs err of gelu = a * h * ln2 * dq
-for deg in (5,6,7,8):
+import sys
+for deg in tuple(int(a) for a in sys.argv[1:]) or (5,6,7,8):
     # weighted LSQ in Chebyshev basis then iterate reweighting (Lawson) for minimax
     t = 2*a/A-1
     V = np.polynomial.chebyshev.chebvander(t, deg)

@@ -479,19 +479,26 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             v[j] = __uint_as_float(r0[j]);
             v[32 + j] = __uint_as_float(r1[j]);
           }
+          // packed fp32 (FFMA2): y = rstd*acc + (nmr*c1 + c2), then the activation, two columns
+          // per issue slot
+          const float2 rstd2 = make_float2(rstd, rstd), nmr2 = make_float2(nmr, nmr);
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
             const float4 a = *reinterpret_cast<const float4*>(sVec + lcol0 + 4 * j);
             const float4 bb = *reinterpret_cast<const float4*>(sVec + BN + lcol0 + 4 * j);
-            const float av[4] = {a.x, a.y, a.z, a.w};
-            const float bv[4] = {bb.x, bb.y, bb.z, bb.w};
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              float x = fmaf(rstd, v[4 * j + i], fmaf(nmr, av[i], bv[i]));
-              if constexpr (EPI == EPI_BIAS_GELU_BF16) x = gelu_erf(x);
-              if constexpr (EPI == EPI_BIAS_GELUT_BF16) x = gelu_tanh(x);
-              v[4 * j + i] = x;
+            float2 x0 = __ffma2_rn(rstd2, make_float2(v[4 * j], v[4 * j + 1]),
+                                   __ffma2_rn(nmr2, make_float2(a.x, a.y), make_float2(bb.x, bb.y)));
+            float2 x1 = __ffma2_rn(rstd2, make_float2(v[4 * j + 2], v[4 * j + 3]),
+                                   __ffma2_rn(nmr2, make_float2(a.z, a.w), make_float2(bb.z, bb.w)));
+            if constexpr (EPI == EPI_BIAS_GELU_BF16) {
+              x0 = gelu_erf2(x0);
+              x1 = gelu_erf2(x1);
             }
+            if constexpr (EPI == EPI_BIAS_GELUT_BF16) {
+              x0 = make_float2(gelu_tanh(x0.x), gelu_tanh(x0.y));
+              x1 = make_float2(gelu_tanh(x1.x), gelu_tanh(x1.y));
+            }
+            v[4 * j] = x0.x; v[4 * j + 1] = x0.y; v[4 * j + 2] = x1.x; v[4 * j + 3] = x1.y;
           }
           if (lane == 0) tma_store_wait_read<NBUF - 1>();
           __syncwarp();

@@ -419,6 +419,25 @@ __device__ __forceinline__ float gelu_erf(float x) {
   q = fmaf(q, a, -9.999995828e-01f);
   return fmaxf(x, 0.0f) - fabsf(x) * ex2_approx(q);
 }
+// Two GELUs per call on Blackwell's packed fp32 pipe (FFMA2: one issue slot, two FMAs).  Same
+// form as gelu_erf with a degree-5 exponent polynomial written in na = -min(|x|, 6) (odd
+// coefficients sign-flipped), so the last step is one packed FMA: max(x,0) + na * 2^q(na).  Max
+// |error| vs the float64 erf form 1.7e-6 (tools/fit_gelu.py 5) — 1/10 of a bf16 half-ulp at the
+// smallest outputs that survive the rounding — at 7.5 issue slots per element instead of 12.5:
+// the fc1 epilogue, not the MMA, paces that GEMM (tools/dev_fc1_probe.py: 1295 TFLOP/s without
+// the epilogue math, 1020 with the scalar form).
+__device__ __forceinline__ float2 gelu_erf2(float2 x) {
+  const float2 na = make_float2(fmaxf(-fabsf(x.x), -6.0f), fmaxf(-fabsf(x.y), -6.0f));
+  float2 q = make_float2(3.641535586e-04f, 3.641535586e-04f);
+  q = __ffma2_rn(q, na, make_float2(6.357131992e-03f, 6.357131992e-03f));
+  q = __ffma2_rn(q, na, make_float2(5.011198297e-02f, 5.011198297e-02f));
+  q = __ffma2_rn(q, na, make_float2(-4.617313147e-01f, -4.617313147e-01f));
+  q = __ffma2_rn(q, na, make_float2(1.150063276e+00f, 1.150063276e+00f));
+  q = __ffma2_rn(q, na, make_float2(-1.000129342e+00f, -1.000129342e+00f));
+  const float2 e = make_float2(ex2_approx(q.x), ex2_approx(q.y));
+  const float2 mx = make_float2(fmaxf(x.x, 0.0f), fmaxf(x.y, 0.0f));
+  return __ffma2_rn(na, e, mx);
+}
 __device__ __forceinline__ float gelu_tanh(float x) {  // TF Model Garden activations.gelu
   const float k0 = 0.7978845608028654f, k1 = 0.044715f;
   float u = k0 * (x + k1 * x * x * x);
