@@ -84,3 +84,59 @@ def test_gather_over_gloo(world, n_frames):
         p.join(60)
         assert p.exitcode == 0
     assert sorted(res) == [(r, True) for r in range(world)]
+
+
+# ---------------------------------------------------------------------------------------------
+# row-sharded store: the exchange step (all-gather queries -> local top-k -> all-gather -> merge)
+# ---------------------------------------------------------------------------------------------
+def test_merge_topk_orders_by_score_then_row():
+    idx = torch.tensor([[7, 3, -1, 9, 1, 5]], dtype=torch.int32)
+    sc = torch.tensor([[0.5, 0.9, 0.0, 0.5, 0.5, 0.1]])
+    i, s = shard.merge_topk(idx, sc, 4)
+    assert i.tolist() == [[3, 1, 7, 9]] and torch.allclose(s, torch.tensor([[0.9, 0.5, 0.5, 0.5]]))
+    i, s = shard.merge_topk(idx, -sc, 3, descending=False)          # distances: ascending
+    assert i.tolist() == [[3, 1, 7]]
+    i, s = shard.merge_topk(idx[:, :2], sc[:, :2], 4)               # fewer candidates than k: -1 padded
+    assert i.tolist() == [[3, 7, -1, -1]]
+
+
+def _store_worker(rank, world, port, q):
+    import numpy as np
+    from oracle import knn_ref
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        rng = np.random.default_rng(0)
+        m, nq, k, d = 1000, 37, 10, 64
+        store = knn_ref.normalise(rng.standard_normal((m, d)).astype(np.float32))
+        queries = knn_ref.normalise(rng.standard_normal((nq, d)).astype(np.float32))
+        ra, rb = shard.frame_ranges(m, world)[rank]       # this rank's store rows
+        qa, qb = shard.frame_ranges(nq, world)[rank]      # this rank's queries
+
+        def local_search(qq, kk):  # the checker stands in for BankIndex.search on the CPU
+            i, s, _ = knn_ref.cosine_topk(qq.numpy(), store[ra:rb], kk, dtype=np.float32)
+            return torch.from_numpy(i.astype(np.int32)), torch.from_numpy(s.astype(np.float32))
+
+        gi, gs = shard.search_sharded_store(local_search, torch.from_numpy(queries[qa:qb]), k, ra, nq)
+        wi, ws, _ = knn_ref.cosine_topk(queries[qa:qb], store, k, dtype=np.float32)
+        ok = gi.shape == (qb - qa, k) and np.array_equal(gi.numpy(), wi) and \
+            np.allclose(gs.numpy(), ws, atol=1e-6)
+        q.put((rank, bool(ok)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_sharded_store_exchange_over_gloo(world):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_store_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=180) for _ in procs]
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    assert sorted(res) == [(r, True) for r in range(world)]

@@ -9,7 +9,7 @@ CUDA tensors (bench.py, N > 1) and over gloo with CPU tensors (tests/test_shard_
 """
 from __future__ import annotations
 
-from typing import Iterator, List, Sequence, Tuple
+from typing import Callable, Iterator, List, Sequence, Tuple
 
 import numpy as np
 import torch
@@ -86,3 +86,63 @@ def label_frames_sharded(embedder, index, frames: Sequence, k: int = 25, batch: 
     emb_t = torch.cat(embs, 0) if embs else torch.zeros((0, hidden), dtype=torch.float32)
     lab_t = torch.cat(labs, 0) if labs else torch.zeros((0,), dtype=torch.int32)
     return gather_frames(emb_t.to(device), n), gather_frames(lab_t.to(device), n)
+
+
+# ---------------------------------------------------------------------------------------------
+# Row-sharded clip store (the "exchange step" alternative for BASELINE configs[4]):
+# rank r holds store rows [row_ranges[r]) and its own share of the queries.
+# ---------------------------------------------------------------------------------------------
+def merge_topk(idx: torch.Tensor, score: torch.Tensor, k: int, descending: bool = True):
+    """Merge per-shard candidate lists: idx/score (Q, C) with GLOBAL row ids (-1 = empty slot) ->
+    (Q, k) best in (score, then lower row id) order — the same total order the kernels use."""
+    q, c = idx.shape
+    big = torch.iinfo(torch.int64).max
+    rid = torch.where(idx < 0, torch.full_like(idx, big, dtype=torch.int64), idx.to(torch.int64))
+    key = score.to(torch.float64)
+    key = torch.where(idx < 0, torch.full_like(key, float("-inf") if descending else float("inf")), key)
+    # stable two-pass sort: by row id, then by score
+    o1 = torch.argsort(rid, dim=1, stable=True)
+    key1 = torch.gather(key, 1, o1)
+    o2 = torch.argsort(key1, dim=1, descending=descending, stable=True)
+    order = torch.gather(o1, 1, o2)[:, :k]
+    out_idx = torch.gather(idx, 1, order)
+    out_score = torch.gather(score, 1, order)
+    if c < k:
+        pad = k - c
+        out_idx = torch.cat([out_idx, torch.full((q, pad), -1, dtype=idx.dtype, device=idx.device)], 1)
+        out_score = torch.cat([out_score, torch.zeros((q, pad), dtype=score.dtype, device=score.device)], 1)
+    return out_idx, out_score
+
+
+def search_sharded_store(local_search: Callable, q_local: torch.Tensor, k: int, row_offset: int,
+                         n_queries: int, descending: bool = True, group=None):
+    """Top-k of this rank's queries against a store whose rows are sharded over the ranks.
+
+    local_search(q (Q,d) tensor, k) -> (idx (Q,k) int32 LOCAL rows, score (Q,k) f32): the rank's
+    BankIndex.search on its shard (`lambda q, k: index.search(q, k)[:2]`).  One exchange step:
+    all-gather the queries (n_queries rows in total, sharded with frame_ranges), search the local
+    shard for ALL of them, all-gather the (global row, score) lists — 8·k bytes per query per rank —
+    and merge world·k -> k for the rank's own queries.  Returns (idx (Q_local,k) global rows, score).
+    """
+    import torch.distributed as dist
+
+    if not (dist.is_available() and dist.is_initialized()):
+        idx, score = local_search(q_local, k)
+        idx = torch.where(idx >= 0, idx + row_offset, idx)
+        return merge_topk(idx, score, k, descending)
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    q_all = gather_frames(q_local, n_queries, group)
+    idx, score = local_search(q_all, k)
+    idx = torch.where(idx >= 0, idx + row_offset, idx).to(torch.int32).contiguous()
+    score = score.to(torch.float32).contiguous()
+    nq_all = idx.shape[0]
+    all_idx = torch.empty((world * nq_all, k), dtype=idx.dtype, device=idx.device)
+    all_score = torch.empty((world * nq_all, k), dtype=score.dtype, device=score.device)
+    dist.all_gather_into_tensor(all_idx, idx, group=group)      # rank-major concatenation
+    dist.all_gather_into_tensor(all_score, score, group=group)
+    all_idx = all_idx.view(world, nq_all, k)
+    all_score = all_score.view(world, nq_all, k)
+    a, b = frame_ranges(n_queries, world)[rank]
+    mine_idx = all_idx[:, a:b].permute(1, 0, 2).reshape(b - a, world * k)
+    mine_score = all_score[:, a:b].permute(1, 0, 2).reshape(b - a, world * k)
+    return merge_topk(mine_idx, mine_score, k, descending)
