@@ -37,6 +37,10 @@ typedef struct vitk_config {
   float ln_eps;               /* HF 1e-12; TF Model Garden 1e-6 */
   int32_t gelu_tanh;          /* 0: exact erf GELU (HF "gelu"); 1: tanh approximation (TF) */
   int32_t max_batch;          /* frames per vitk_embed call the workspace is sized for */
+  float u8_mean, u8_std;      /* VITK_PIX_U8_NHWC pixels enter the model as (x - u8_mean) / u8_std.
+                               * 0,0 = the HF processor (127.5, 127.5: rescale 1/255, mean .5, std .5
+                               * fused); the reference's TF scripts feed RAW pixels: 0, 1
+                               * (write_embeddings.py:185, generate_clips_hmm.py:397-401) */
 } vitk_config;
 
 enum { VITK_PIX_F32_NCHW = 0, VITK_PIX_BF16_NCHW = 1, VITK_PIX_U8_NHWC = 2 };

@@ -99,7 +99,10 @@ def test_layernorm(lib, rows, d):
 
 
 @pytest.mark.parametrize("frames,S,heads", [(1, 197, 1), (3, 197, 12), (2, 4, 12), (3, 64, 2),
-                                            (2, 128, 2), (2, 129, 3), (2, 256, 2), (1, 250, 16)])
+                                            (2, 128, 2), (2, 129, 3), (2, 256, 2), (1, 250, 16),
+                                            # wide form (keys in two halves, 512 TMEM columns): the
+                                            # reference's TF-path geometry has 313 tokens
+                                            (2, 257, 2), (3, 313, 12), (1, 320, 3), (2, 385, 2), (1, 448, 2)])
 def test_attention(lib, frames, S, heads):
     D = heads * 64
     g = torch.Generator().manual_seed(frames * 1000 + S + heads)
@@ -163,7 +166,7 @@ def test_bad_arguments_fail_loudly(lib):
     o = torch.zeros(128, 256, device="cuda")
     assert lib.vitk_op_gemm(_p(a), _p(a), _p(o), 128, 256, 100, 5, None, None, None, 1, _s()) != 0
     assert b"K=100" in lib.vitk_last_error(None)
-    assert lib.vitk_op_attention(_p(a), _p(o), 1, 300, 1, _s()) != 0
+    assert lib.vitk_op_attention(_p(a), _p(o), 1, 500, 1, _s()) != 0   # S > 448
 
 
 # ---------------------------------------------------------------------------------------------

@@ -124,6 +124,38 @@ def test_vit_l16_geometry(v):
     emb.close()
 
 
+def test_tf_path_geometry_432x768_patch32(v):
+    """The reference's TF-path hyper-parameters (generate_clips_hmm.py:48-56): 432x768 frames fed
+    un-normalised (raw 0..255), patch 32 'valid' -> 313 tokens, LayerNorm eps 1e-6, tanh-GELU,
+    (B,1,1,768) pre_logits.  Oracle: HF ViTModel configured with exactly that geometry (the TF
+    Model Garden block is absent here, so TF semantics beyond the geometry stay unpinned)."""
+    from oracle import vit_ref
+    model = vit_ref.build_hf_model("vit_tf432_l2", 2, randomise_ln=True)
+    emb = v.ViTEmbedder.from_hf(model, device=0, max_batch=4)
+    assert emb.geometry.tokens == 313 and emb.geometry.gelu_tanh and emb.geometry.ln_eps == 1e-6
+    g = torch.Generator().manual_seed(3)
+    frames = torch.randint(0, 256, (6, 432, 768, 3), generator=g, dtype=torch.uint8)
+    px = frames.permute(0, 3, 1, 2).float().contiguous()          # raw pixel values, NCHW
+    want = vit_ref.hf_embed(model, px, normalise=False)
+    got = emb.embed(px.cuda(), l2_normalise=False).cpu().numpy()  # 6 frames > max_batch 4: chunked
+    assert got.shape == (6, 768)
+    assert _cos(got, want).min() >= COS_BAR, _cos(got, want)
+    # the CLS-only last layer and the full last layer agree bit for bit on this geometry too
+    hs = emb(pixel_values=px[:2].cuda()).last_hidden_state
+    assert hs.shape == (2, 1, 768) and torch.equal(hs[:, 0].cpu(), torch.from_numpy(got[:2]))
+    emb.close()
+    # Keras-style call on raw uint8 frames, as the TF scripts do (write_embeddings.py:185-188):
+    # geometry.u8_mean/u8_std = 0/1 feeds the pixel values unchanged -> identical embeddings
+    import dataclasses
+    g_tf = dataclasses.replace(v.ViTGeometry.from_hf_config(model.config), u8_mean=0.0, u8_std=1.0)
+    assert g_tf == dataclasses.replace(v.ViTGeometry.tf_432x768(), layers=2)
+    emb2 = v.ViTEmbedder(g_tf, model.state_dict(), device=0, max_batch=4)
+    out = emb2.predict(frames.numpy(), batch_size=1024, verbose=0)["pre_logits"]
+    assert out.shape == (6, 1, 1, 768) and out.dtype == np.float32
+    assert np.array_equal(out.reshape(6, 768), got)
+    emb2.close()
+
+
 # ------------------------------------------------------------------------------------------
 # k-NN + vote
 # ------------------------------------------------------------------------------------------

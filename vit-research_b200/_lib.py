@@ -34,6 +34,7 @@ class VitkConfig(C.Structure):
         ("channels", C.c_int32), ("hidden", C.c_int32), ("heads", C.c_int32),
         ("mlp", C.c_int32), ("layers", C.c_int32), ("ln_eps", C.c_float),
         ("gelu_tanh", C.c_int32), ("max_batch", C.c_int32),
+        ("u8_mean", C.c_float), ("u8_std", C.c_float),
     ]
 
 

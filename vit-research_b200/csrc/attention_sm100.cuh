@@ -28,20 +28,28 @@ constexpr uint32_t ATT_TMEM_COLS = 256;
 constexpr int ATT_MIN_SMEM = 78 * 1024;
 
 struct AttnSmemLayout {
-  int sk;  // keys rounded up to 16 (MMA N / K extent)
+  int sk;      // keys rounded up to 16 (MMA N / K extent)
+  int kv_box;  // rows per K / V TMA box: sk, or for sk > 256 (box and MMA-N limit) the first of
+               // two halves, a multiple of 16
   int off_q, off_k, off_v, off_bar, total;
 };
+constexpr int ATT_MAX_S = 448;  // wide form: both halves of the keys within the 256 box / MMA-N limit
 
 __host__ __device__ inline AttnSmemLayout attn_smem_layout(int S) {
   AttnSmemLayout L;
   L.sk = (S + 15) & ~15;
-  int kv_bytes = ((L.sk * 128) + 1023) & ~1023;
+  L.kv_box = L.sk <= 256 ? L.sk : ((L.sk / 2 + 15) & ~15);
+  // rows the K / V loads deliver: sk, or both halves of the wide form (2*kv_box >= sk)
+  const int kv_rows = L.sk <= 256 ? L.sk : 2 * L.kv_box;
+  int kv_bytes = ((kv_rows * 128) + 1023) & ~1023;
   L.off_q = 0;
   L.off_k = 16384;
   L.off_v = L.off_k + kv_bytes;
   L.off_bar = L.off_v + kv_bytes;
   L.total = L.off_bar + 64 + 1024;  // + alignment slack
   if (L.total < ATT_MIN_SMEM) L.total = ATT_MIN_SMEM;
+  // wide form: the CTA owns all 512 TMEM columns, so at most ONE CTA may be resident per SM
+  if (L.sk > 256 && L.total < 116 * 1024) L.total = 116 * 1024;
   return L;
 }
 
@@ -58,7 +66,12 @@ struct AttnParams {
 // tmQ : 3-D map over qkv [frames, S, 3*D] bf16, box {64, 128, 1}   (Q block)
 // tmKV: same tensor,                          box {64, sk, 1}      (K and V)
 // tmO : 3-D map over out [frames, S, D] bf16, box {64, 128, 1}
-__global__ void __launch_bounds__(ATT_THREADS, 2)
+// WIDE = false: S <= 256, 256 TMEM columns, two CTAs per SM.  WIDE = true: 256 < S <= 448 (the
+// reference's TF-path geometry: 432x768 frames, patch 32 -> 313 tokens, generate_clips_hmm.py:48-56):
+// 512 TMEM columns, one CTA per SM, K / V loaded as two TMA boxes and S = Q K^T issued as two
+// N-halves (box and MMA-N extents stop at 256).
+template <bool WIDE>
+__global__ void __launch_bounds__(ATT_THREADS, WIDE ? 1 : 2)
 attention_v2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
                  const __grid_constant__ CUtensorMap tmO, const AttnParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -93,14 +106,18 @@ attention_v2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     mbar_init(bar_o, 1);
     fence_mbar_init();
     // ---- loads: Q block + K on one barrier, V on another (issued before the TMEM alloc) ----
-    const uint32_t kv_bytes = SK * 128;
+    const uint32_t kv_bytes = (WIDE ? 2 * L.kv_box : SK) * 128;
     mbar_arrive_expect_tx(bar_qk, 128 * 128 + kv_bytes);
     tma_load_3d(smem + L.off_q, &tmQ, bar_qk, head * ATT_D, blk * 128, frame);
     tma_load_3d(smem + L.off_k, &tmKV, bar_qk, D + head * ATT_D, 0, frame);
+    if constexpr (WIDE)
+      tma_load_3d(smem + L.off_k + L.kv_box * 128, &tmKV, bar_qk, D + head * ATT_D, L.kv_box, frame);
     mbar_arrive_expect_tx(bar_v, kv_bytes);
     tma_load_3d(smem + L.off_v, &tmKV, bar_v, 2 * D + head * ATT_D, 0, frame);
+    if constexpr (WIDE)
+      tma_load_3d(smem + L.off_v + L.kv_box * 128, &tmKV, bar_v, 2 * D + head * ATT_D, L.kv_box, frame);
   }
-  if (warp == 1) tmem_alloc<ATT_TMEM_COLS>(tmem_slot);
+  if (warp == 1) tmem_alloc<WIDE ? 512u : ATT_TMEM_COLS>(tmem_slot);
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
@@ -112,12 +129,20 @@ attention_v2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     // ---- S = Q K^T ----
     mbar_wait(bar_qk, 0);
     tc_fence_after_sync();
-    const uint32_t idesc_s = make_idesc_bf16_f32(128, (uint32_t)SK, false, false);
-    const uint64_t dk = make_smem_desc_sw128(smem_u32(smem + L.off_k), 1024, 0);
     const uint64_t dq = make_smem_desc_sw128(smem_u32(smem + L.off_q), 1024, 0);
+    const int n1 = WIDE ? L.kv_box : SK;  // keys [0, n1) and, wide only, [n1, SK)
+    const uint32_t idesc_s = make_idesc_bf16_f32(128, (uint32_t)n1, false, false);
+    const uint64_t dk = make_smem_desc_sw128(smem_u32(smem + L.off_k), 1024, 0);
 #pragma unroll
     for (int k = 0; k < ATT_D / 16; ++k)
       umma_bf16_ss(tmem_base, dq + 2 * k, dk + 2 * k, idesc_s, k != 0 ? 1u : 0u);
+    if constexpr (WIDE) {
+      const uint32_t idesc_s2 = make_idesc_bf16_f32(128, (uint32_t)(SK - n1), false, false);
+      const uint64_t dk2 = make_smem_desc_sw128(smem_u32(smem + L.off_k + n1 * 128), 1024, 0);
+#pragma unroll
+      for (int k = 0; k < ATT_D / 16; ++k)
+        umma_bf16_ss(tmem_base + (uint32_t)n1, dq + 2 * k, dk2 + 2 * k, idesc_s2, k != 0 ? 1u : 0u);
+    }
     umma_commit(bar_s);
   }
 
@@ -248,7 +273,7 @@ attention_v2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   }
   if (warp == 1) {
     tc_fence_after_sync();
-    tmem_dealloc<ATT_TMEM_COLS>(tmem_base);
+    tmem_dealloc<WIDE ? 512u : ATT_TMEM_COLS>(tmem_base);
   }
 }
 

@@ -230,8 +230,8 @@ long long* g_attn_dbg = nullptr;  // developer timeline buffer (vitk_dev_attn_ti
 // q_rows > 0: only the first q_rows queries of every frame are needed (last layer: the CLS row)
 int launch_attention(Err& e, const CUtensorMap& tq, const CUtensorMap& tkv, const CUtensorMap& to,
                      int frames, int S, int heads, cudaStream_t st, int q_rows = 0) {
-  if (S < 1 || S > 256) {
-    e.set("attention: S=%d unsupported (1..256)", S);
+  if (S < 1 || S > ATT_MAX_S) {
+    e.set("attention: S=%d unsupported (1..%d)", S, ATT_MAX_S);
     return 1;
   }
   static int version = -1;  // VITK_ATTN=2 selects the simpler non-persistent v2 kernel
@@ -244,18 +244,29 @@ int launch_attention(Err& e, const CUtensorMap& tq, const CUtensorMap& tkv, cons
   p.heads = heads;
   p.frames = frames;
   p.q_rows = q_rows > 0 && q_rows < S ? q_rows : S;
-  p.nblk = p.q_rows > 128 ? 2 : 1;
+  p.nblk = (p.q_rows + 127) / 128;
   p.scale_log2e = 0.125f * 1.4426950408889634f;  // head dim 64 -> 1/sqrt(64)
   p.dbg = g_attn_dbg;
-  if (version == 2) {
+  if (S > 256) {
+    // the TF-path geometry (313 tokens): one CTA per (frame, head, 128-query block), all 512 TMEM
+    // columns, keys in two halves
+    const AttnSmemLayout L = attn_smem_layout(S);
+    static int attr_bytes_w = 0;
+    if (L.total > attr_bytes_w) {
+      CK(e, cudaFuncSetAttribute(attention_v2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 L.total));
+      attr_bytes_w = L.total;
+    }
+    attention_v2_kernel<true><<<frames * heads * p.nblk, ATT_THREADS, L.total, st>>>(tq, tkv, to, p);
+  } else if (version == 2) {
     const AttnSmemLayout L = attn_smem_layout(S);
     static int attr_bytes = 0;
     if (L.total > attr_bytes) {
-      CK(e, cudaFuncSetAttribute(attention_v2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+      CK(e, cudaFuncSetAttribute(attention_v2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  L.total));
       attr_bytes = L.total;
     }
-    attention_v2_kernel<<<frames * heads * p.nblk, ATT_THREADS, L.total, st>>>(tq, tkv, to, p);
+    attention_v2_kernel<false><<<frames * heads * p.nblk, ATT_THREADS, L.total, st>>>(tq, tkv, to, p);
   } else {
     const Attn3SmemLayout L = attn3_smem_layout(S);
     static int attr_bytes3 = 0;
@@ -307,9 +318,11 @@ int launch_rowstats(Err& e, const float* x, __nv_bfloat16* xb, float* stats, int
 }
 
 int launch_patchify(Err& e, const void* pix, int fmt, __nv_bfloat16* out, int n, int C, int H,
-                    int W, int ps, cudaStream_t st) {
-  if (ps % 8 != 0 || H % ps != 0 || W % ps != 0) {
-    e.set("patchify: patch %d must be a multiple of 8 dividing %dx%d", ps, H, W);
+                    int W, int ps, cudaStream_t st, float u8_mean = 127.5f, float u8_std = 127.5f) {
+  // stride == kernel convolution with 'valid' padding: trailing rows / columns that do not fill
+  // a patch are ignored (432 rows at patch 32 -> 13 patch rows, like Conv2d / Conv2D 'valid')
+  if (ps % 8 != 0 || H < ps || W < ps || W % 8 != 0) {
+    e.set("patchify: patch %d must be a multiple of 8 and fit %dx%d (width a multiple of 8)", ps, H, W);
     return 1;
   }
   if (fmt < 0 || fmt > 2) {
@@ -323,8 +336,8 @@ int launch_patchify(Err& e, const void* pix, int fmt, __nv_bfloat16* out, int n,
   p.gh = H / ps; p.gw = W / ps;
   p.K = C * ps * ps;
   p.fmt = fmt;
-  p.mean = 127.5f;  // HF ViTImageProcessor: rescale 1/255, mean .5, std .5, fused
-  p.std = 127.5f;
+  p.mean = u8_mean;  // default: HF ViTImageProcessor (rescale 1/255, mean .5, std .5, fused)
+  p.std = u8_std;
   long long total = (long long)n * (p.gh * p.gw + 1) * (p.K / 8);
   long long blocks = (total + 255) / 256;
   if (blocks > 148 * 32) blocks = 148 * 32;
@@ -534,8 +547,11 @@ extern "C" int vitk_create(const vitk_config* cfg, int device, vitk_handle* out)
   }
   if (cfg->hidden != cfg->heads * 64) { e.set("hidden must be heads*64"); return fail(nullptr); }
   if (cfg->hidden != 768 && cfg->hidden != 1024) { e.set("hidden must be 768 or 1024"); return fail(nullptr); }
-  if (cfg->image_h % cfg->patch || cfg->image_w % cfg->patch || cfg->patch % 8) {
-    e.set("patch must divide the image and be a multiple of 8"); return fail(nullptr);
+  // the patch convolution is 'valid': rows / columns that do not fill a patch are dropped (the
+  // reference's TF path feeds 432x768 frames to patch 32: 13 x 24 patches, generate_clips_hmm.py:48-56)
+  if (cfg->patch < 8 || cfg->patch % 8 || cfg->image_h < cfg->patch || cfg->image_w < cfg->patch ||
+      cfg->image_w % 8) {
+    e.set("patch must be a multiple of 8 that fits the image; image width a multiple of 8"); return fail(nullptr);
   }
   if (cfg->hidden % 256 || cfg->mlp % 256 || cfg->max_batch < 1) {
     e.set("hidden/mlp must be multiples of 256 and max_batch >= 1"); return fail(nullptr);
@@ -553,7 +569,7 @@ extern "C" int vitk_create(const vitk_config* cfg, int device, vitk_handle* out)
     const char* v = getenv("VITK_FULL_LAST_LAYER");
     c->cls_only_last = !(v && atoi(v) == 1);
   }
-  if (c->S > 256) { e.set("tokens per frame %d > 256 unsupported by the attention kernel", c->S); return fail(c); }
+  if (c->S > ATT_MAX_S) { e.set("tokens per frame %d > %d unsupported by the attention kernel", c->S, ATT_MAX_S); return fail(c); }
   if (c->Kp % 64) { e.set("channels*patch^2 must be a multiple of 64"); return fail(c); }
   if (cudaSetDevice(device) != cudaSuccess) { e.set("cudaSetDevice failed"); return fail(c); }
   const size_t D = c->D, F = c->F, Kp = c->Kp;
@@ -788,7 +804,7 @@ int get_maps(vitk_ctx* c, int n, BatchMaps** out) {
   Err& e = c->err;
   BatchMaps m;
   const int M = n * c->S, D = c->D, F = c->F;
-  const int sk = attn_smem_layout(c->S).sk;
+  const int sk = attn_smem_layout(c->S).kv_box;
   int rc = tmap_operand(e, &m.a_patch, c->act, M, c->Kp, GEMM_BM) |
            tmap_operand(e, &m.a_act, c->act, M, D, GEMM_BM) |
            tmap_operand(e, &m.a_h, c->hbuf, M, F, GEMM_BM) |
@@ -818,7 +834,8 @@ int forward_chunk(vitk_ctx* c, const void* pix, int fmt, int n, float* emb_f32,
   const int M = n * c->S, D = c->D, F = c->F;
   const vitk_config& cfg = c->cfg;
   // (a3) im2col, (a3/a4) patch GEMM + CLS/pos/bias table -> fp32 residual stream
-  if (launch_patchify(e, pix, fmt, c->act, n, cfg.channels, cfg.image_h, cfg.image_w, cfg.patch, st))
+  if (launch_patchify(e, pix, fmt, c->act, n, cfg.channels, cfg.image_h, cfg.image_w, cfg.patch, st,
+                      cfg.u8_std != 0.f ? cfg.u8_mean : 127.5f, cfg.u8_std != 0.f ? cfg.u8_std : 127.5f))
     return 1;
   GemmParams gp{};
   gp.M = M; gp.N = D; gp.K = c->Kp;
@@ -1618,9 +1635,9 @@ extern "C" int vitk_op_attention(const void* qkv, void* out, int frames, int S, 
   Err& e = g_op_err;
   const int D = heads * 64;
   CUtensorMap tq, tkv, to;
-  int rc = (S < 1 || S > 256) ? (e.set("vitk_op_attention: S outside [1,256]"), 1) : 0;
+  int rc = (S < 1 || S > ATT_MAX_S) ? (e.set("vitk_op_attention: S outside [1,%d]", ATT_MAX_S), 1) : 0;
   rc = rc || tmap_tokens(e, &tq, qkv, frames, S, 3 * D, 128) ||
-       tmap_tokens(e, &tkv, qkv, frames, S, 3 * D, attn_smem_layout(S).sk) ||
+       tmap_tokens(e, &tkv, qkv, frames, S, 3 * D, attn_smem_layout(S).kv_box) ||
        tmap_tokens(e, &to, out, frames, S, D, 128) ||
        launch_attention(e, tq, tkv, to, frames, S, heads, reinterpret_cast<cudaStream_t>(stream));
   if (rc) g_create_error = e.msg;

@@ -35,6 +35,8 @@ class ViTGeometry:
     layers: int = 12
     ln_eps: float = 1e-12
     gelu_tanh: bool = False
+    u8_mean: float = 127.5   # uint8 pixels enter the model as (x - u8_mean) / u8_std: the HF
+    u8_std: float = 127.5    # processor's fused rescale+normalise; the TF scripts feed raw pixels (0, 1)
 
     @property
     def tokens(self) -> int:
@@ -47,6 +49,15 @@ class ViTGeometry:
     @classmethod
     def vit_l16(cls) -> "ViTGeometry":
         return cls(hidden=1024, heads=16, mlp=4096, layers=24)
+
+    @classmethod
+    def tf_432x768(cls, patch: int = 32) -> "ViTGeometry":
+        """The reference's TF-path hyper-parameters (generate_clips_hmm.py:48-56,
+        models/vit_backbone.py:158-177): 432x768 raw-pixel frames, patch 32 'valid' (313 tokens),
+        LayerNorm eps 1e-6, tanh-GELU.  (patch 256 -> 3 patches + CLS is the bank-writing variant,
+        write_embeddings.py:101-109.)"""
+        return cls(image_h=432, image_w=768, patch=patch, ln_eps=1e-6, gelu_tanh=True,
+                   u8_mean=0.0, u8_std=1.0)
 
     @classmethod
     def from_hf_config(cls, cfg) -> "ViTGeometry":
@@ -117,7 +128,8 @@ class ViTEmbedder:
         torch.cuda.set_device(self.device)
         g = geometry
         cfg = VitkConfig(g.image_h, g.image_w, g.patch, g.channels, g.hidden, g.heads, g.mlp,
-                         g.layers, g.ln_eps, int(g.gelu_tanh), self.max_batch)
+                         g.layers, g.ln_eps, int(g.gelu_tanh), self.max_batch, float(g.u8_mean),
+                         float(g.u8_std))
         check(self.lib.vitk_create(C.byref(cfg), self.device, C.byref(self.handle)), None,
               "vitk_create")
         for name, t in state_dict.items():
@@ -308,8 +320,9 @@ class ViTEmbedder:
     # ---- Keras-style call: model.predict(x)['pre_logits'] ---------------------------------
     def predict(self, x, batch_size: int = 32, verbose: int = 0):
         """x: (B,H,W,3) uint8/float host array.  Returns {'pre_logits': (B,1,1,hidden)}
-        (write_embeddings.py:185-188, rag_vit.py:463-464).  NOTE: applies the HF rescale /
-        normalise; the TF scripts feed raw 0..255 pixels to random weights."""
+        (write_embeddings.py:185-188, rag_vit.py:463-464).  Pixels enter the model as
+        (x - geometry.u8_mean) / geometry.u8_std: the HF processor's values by default, raw 0..255
+        like the TF scripts with ViTGeometry.tf_432x768()."""
         x = np.asarray(x)
         if x.dtype != np.uint8:
             x = np.clip(x, 0, 255).astype(np.uint8)
