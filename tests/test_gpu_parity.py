@@ -338,3 +338,27 @@ def test_code_path_variants_agree():
     att2 = _fingerprint({"VITK_ATTN": "2"})
     cos = (base * att2).sum(1) / (np.linalg.norm(base, axis=1) * np.linalg.norm(att2, axis=1))
     assert cos.min() > 0.9999, cos.min()
+
+
+def test_empty_and_ragged_inputs(v, b16, banks):
+    """Empty batches return empty results (no launch, no error); a 1-frame batch and a batch one
+    past a multiple of max_batch give the same rows as the big batch."""
+    from oracle import vit_ref
+    _, emb = b16
+    rows, labels = banks
+    assert emb.embed_frames(np.zeros((0, 224, 224, 3), np.uint8)).shape == (0, 768)
+    assert emb.embed(torch.zeros((0, 3, 224, 224), device="cuda")).shape == (0, 768)
+    index = v.BankIndex(emb, rows, labels, 3, metric="l2")
+    idx, score, label, counts = index.search(torch.zeros((0, 768), device="cuda"), 5)
+    assert idx.shape == (0, 5) and label.shape == (0,) and counts.shape == (0, 3)
+    assert v.viterbi_from_probs(emb, np.zeros((0, 3))).shape == (0,)
+    st = v.viterbi_from_counts(emb, torch.zeros((0, 3), dtype=torch.int32, device="cuda"), 25)
+    assert st.shape == (0,)
+    frames = vit_ref.synthetic_frames_u8(65, seed=9)           # max_batch is 64: ragged tail of 1
+    big = emb.embed_frames(frames)
+    assert np.array_equal(emb.embed_frames(frames[64:65]), big[64:65])
+    assert np.array_equal(emb.embed_frames(frames[:1]), big[:1])
+    # k larger than a tiny bank: missing neighbours come back as -1 like an empty Chroma slot
+    tiny = v.BankIndex(emb, rows[:3], labels[:3], 3, metric="cosine", normalise_rows=True)
+    idx, score, label, counts = tiny.search(torch.from_numpy(rows[:2]).cuda(), 5, normalise_queries=True)
+    assert (idx[:, :3] >= 0).all() and (idx[:, 3:] == -1).all() and (counts.sum(1) == 3).all()

@@ -930,6 +930,7 @@ extern "C" int vitk_embed(vitk_handle h, const void* pixels_dev, int pixel_forma
   if (!h) return 1;
   Err& e = h->err;
   if (!h->finalized) { e.set("vitk_embed: weights not finalized"); return 1; }
+  if (n == 0) return 0;  // an empty batch is not an error (empty tensors have null pointers)
   if (!pixels_dev || !emb_f32_dev || n < 0) { e.set("vitk_embed: bad argument"); return 1; }
   if (pixel_format < 0 || pixel_format > 2) { e.set("vitk_embed: bad pixel format"); return 1; }
   CK(e, cudaSetDevice(h->device));
@@ -952,6 +953,7 @@ extern "C" int vitk_embed_host_u8(vitk_handle h, const uint8_t* frames_host, int
   if (!h) return 1;
   Err& e = h->err;
   if (!h->finalized) { e.set("vitk_embed_host_u8: weights not finalized"); return 1; }
+  if (n == 0) return 0;
   if (!frames_host || !emb_host || n < 0) { e.set("vitk_embed_host_u8: bad argument"); return 1; }
   CK(e, cudaSetDevice(h->device));
   cudaStream_t st = h->own_stream;
@@ -1196,6 +1198,7 @@ extern "C" int vitk_knn_vote(vitk_handle h, const float* q_dev, int n, int k, in
   if (!h) return 1;
   Err& e = h->err;
   if (h->bank_m == 0) { e.set("vitk_knn_vote: no bank set"); return 1; }
+  if (n == 0) return 0;
   if (!q_dev || !idx_out || !score_out || n < 0) { e.set("vitk_knn_vote: bad argument"); return 1; }
   if (k < 1 || k > 64) { e.set("vitk_knn_vote: k=%d outside [1,64]", k); return 1; }
   if (metric != METRIC_COSINE && metric != METRIC_L2) { e.set("vitk_knn_vote: bad metric"); return 1; }
@@ -1404,6 +1407,7 @@ extern "C" int vitk_embed_resize_host_u8(vitk_handle h, const uint8_t* frames_ho
   if (!h) return 1;
   Err& e = h->err;
   if (!h->finalized) { e.set("vitk_embed_resize_host_u8: weights not finalized"); return 1; }
+  if (n == 0) return 0;
   if (!frames_host || !emb_host || n < 0 || in_h < 1 || in_w < 1) { e.set("vitk_embed_resize_host_u8: bad argument"); return 1; }
   CK(e, cudaSetDevice(h->device));
   cudaStream_t st = h->own_stream;
@@ -1475,6 +1479,7 @@ extern "C" int vitk_hmm_decode_counts(vitk_handle h, const int32_t* counts_dev, 
                                       int32_t* states_out_dev, double* dp_out_dev, void* stream) {
   if (!h) return 1;
   Err& e = h->err;
+  if (seq_offsets_host && n_seq >= 1 && seq_offsets_host[n_seq] == 0) return 0;  // no frames at all
   if (!counts_dev || !states_out_dev || k < 1 || k > 4096) { e.set("vitk_hmm_decode_counts: bad argument"); return 1; }
   CK(e, cudaSetDevice(h->device));
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
