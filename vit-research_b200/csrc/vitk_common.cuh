@@ -378,54 +378,21 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
 }
-// HF hidden_act="gelu" (exact erf): gelu(x) = x*Phi(x) = max(x,0) - |x| * 0.5*erfc(|x|/sqrt2).
-// 0.5*erfc(a/sqrt2) = 2^q(a) with q a degree-6 minimax fit of log2 on [0,6] (tools/fit_gelu.py):
-// max |error| vs the float64 erf form is 2.5e-7 over [-8,8] (fp32 rounding level), at 11
-// FMA-pipe instructions + one MUFU.EX2 instead of erff's two divergent branches (~25) — the
-// fc1 epilogue was issue-bound on erff (profiles/r01_v1_ncu_gemm.txt: 64 % issue active).
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
-// {2^x0, 2^x1} as packed fp16 (x0 in the low half): ONE MUFU op for two exponentials.
-__device__ __forceinline__ uint32_t ex2_f16x2(float x0, float x1) {
-  uint32_t r;
-  asm("{\n\t.reg .b32 t;\n\t"
-      "cvt.rn.f16x2.f32 t, %2, %1;\n\t"
-      "ex2.approx.f16x2 %0, t;\n\t}\n"
-      : "=r"(r)
-      : "f"(x0), "f"(x1));
-  return r;
-}
-__device__ __forceinline__ float f16x2_sum(uint32_t v) {  // lo + hi in fp32
-  float a, b;
-  asm("{\n\t.reg .b16 l, h;\n\t"
-      "mov.b32 {l, h}, %2;\n\t"
-      "cvt.f32.f16 %0, l;\n\t"
-      "cvt.f32.f16 %1, h;\n\t}\n"
-      : "=f"(a), "=f"(b)
-      : "r"(v));
-  return a + b;
-}
-__device__ __forceinline__ float gelu_erf(float x) {
-  const float a = fminf(fabsf(x), 6.0f);
-  float q = 3.291235043e-05f;
-  q = fmaf(q, a, -7.622243138e-04f);
-  q = fmaf(q, a, 8.038992994e-03f);
-  q = fmaf(q, a, -5.331545696e-02f);
-  q = fmaf(q, a, -4.588715434e-01f);
-  q = fmaf(q, a, -1.151156664e+00f);
-  q = fmaf(q, a, -9.999995828e-01f);
-  return fmaxf(x, 0.0f) - fabsf(x) * ex2_approx(q);
-}
-// Two GELUs per call on Blackwell's packed fp32 pipe (FFMA2: one issue slot, two FMAs).  Same
-// form as gelu_erf with a degree-5 exponent polynomial written in na = -min(|x|, 6) (odd
-// coefficients sign-flipped), so the last step is one packed FMA: max(x,0) + na * 2^q(na).  Max
-// |error| vs the float64 erf form 1.7e-6 (tools/fit_gelu.py 5) — 1/10 of a bf16 half-ulp at the
-// smallest outputs that survive the rounding — at 7.5 issue slots per element instead of 12.5:
-// the fc1 epilogue, not the MMA, paces that GEMM (tools/dev_fc1_probe.py: 1295 TFLOP/s without
-// the epilogue math, 1020 with the scalar form).
+// HF hidden_act="gelu" (exact erf): gelu(x) = x*Phi(x) = max(x,0) - |x| * 0.5*erfc(|x|/sqrt2), with
+// 0.5*erfc(a/sqrt2) = 2^q(a), q a minimax fit of log2 on [0,6] (tools/fit_gelu.py) — FMA-pipe
+// instructions + one MUFU.EX2 instead of erff's two divergent branches (~25 instructions; the fc1
+// epilogue was issue-bound on erff, profiles/r01_v1_ncu_gemm.txt).  Two GELUs per call on
+// Blackwell's packed fp32 pipe (FFMA2: one issue slot, two FMAs): degree-5 q written in
+// na = -min(|x|, 6) (odd coefficients sign-flipped), so the last step is one packed FMA,
+// max(x,0) + na * 2^q(na).  Max |error| vs the float64 erf form 1.7e-6 — 1/10 of a bf16 half-ulp
+// at the smallest outputs that survive the rounding — at 7.5 issue slots per element instead of
+// the 12.5 of the scalar degree-6 form: the fc1 epilogue, not the MMA, paces that GEMM
+// (tools/dev_fc1_probe.py: 1295 TFLOP/s without the epilogue math, 1020 scalar, 1190 packed).
 __device__ __forceinline__ float2 gelu_erf2(float2 x) {
   const float2 na = make_float2(fmaxf(-fabsf(x.x), -6.0f), fmaxf(-fabsf(x.y), -6.0f));
   float2 q = make_float2(3.641535586e-04f, 3.641535586e-04f);
