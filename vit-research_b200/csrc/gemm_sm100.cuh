@@ -398,15 +398,16 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             }
             if (p.xb != nullptr && live && row < p.M) {
               uint4* xp = reinterpret_cast<uint4*>(p.xb + (size_t)row * p.xb_ld + col0);
+              uint4 o[4];
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
-                uint4 o;
-                o.x = pack_bf16x2(v[8 * j + 0], v[8 * j + 1]);
-                o.y = pack_bf16x2(v[8 * j + 2], v[8 * j + 3]);
-                o.z = pack_bf16x2(v[8 * j + 4], v[8 * j + 5]);
-                o.w = pack_bf16x2(v[8 * j + 6], v[8 * j + 7]);
-                xp[j] = o;
+                o[j].x = pack_bf16x2(v[8 * j + 0], v[8 * j + 1]);
+                o[j].y = pack_bf16x2(v[8 * j + 2], v[8 * j + 3]);
+                o[j].z = pack_bf16x2(v[8 * j + 4], v[8 * j + 5]);
+                o[j].w = pack_bf16x2(v[8 * j + 6], v[8 * j + 7]);
               }
+              st_global_256(xp, o[0], o[1]);
+              st_global_256(xp + 2, o[2], o[3]);
             }
           } else if constexpr (EPI == EPI_THRESH_POOL) {
             if (p.pool_l2) {

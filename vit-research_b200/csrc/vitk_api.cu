@@ -208,8 +208,9 @@ int launch_gemm(Err& e, int epi, const CUtensorMap& a, const CUtensorMap& b, con
           GEMM_MAX_STAT_PARTS);
     return 1;
   }
-  if (epi == EPI_BIAS_RESID_F32 && p.xb != nullptr && (p.N % 32 != 0 || p.xb_ld % 8 != 0)) {
-    e.set("gemm: bf16 residual copy needs N %% 32 == 0 and a 16-byte aligned row pitch");
+  if (epi == EPI_BIAS_RESID_F32 && p.xb != nullptr &&
+      (p.N % 32 != 0 || p.xb_ld % 16 != 0 || (reinterpret_cast<uintptr_t>(p.xb) & 31) != 0)) {
+    e.set("gemm: bf16 residual copy needs N %% 32 == 0, a 32-byte aligned base and row pitch");
     return 1;
   }
   switch (epi) {

@@ -412,6 +412,14 @@ __device__ __forceinline__ float gelu_tanh(float x) {  // TF Model Garden activa
 }
 // Order-preserving map float -> uint32 (larger float <=> larger integer); 0 is below every
 // real value and marks "no row".
+// 32-byte global store (sm_100 STG.256): one full sector per lane, so a row-per-lane store of a
+// bf16 tile leaves the SM as whole sectors instead of 16-byte halves
+__device__ __forceinline__ void st_global_256(void* p, uint4 a, uint4 b) {
+  asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(a.x), "r"(a.y),
+               "r"(a.z), "r"(a.w), "r"(b.x), "r"(b.y), "r"(b.z), "r"(b.w)
+               : "memory");
+}
+
 __device__ __forceinline__ uint32_t float_order_bits(float f) {
   const uint32_t u = __float_as_uint(f);
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
