@@ -332,6 +332,9 @@ def test_code_path_variants_agree():
     # single-CTA tcgen05.mma (cta_group::1) vs the CTA pair: same K order, same accumulators
     cg1 = _fingerprint({"VITK_GEMM_CG": "1"})
     assert np.array_equal(base, cg1)
+    # CTA-pair GEMMs with five operand stages / two staging tiles vs six / one: pipeline depth only
+    s5 = _fingerprint({"VITK_GEMM_S6": "0"})
+    assert np.array_equal(base, s5)
     # attention v2 (exact row max, two passes) vs v3 (shift by the first-32 max): the bf16 P tiles
     # are rounded at a different scale, so the two agree to bf16 noise (either one is 0.99996 from
     # the fp32 oracle; measured 0.999988 between them on B200), not bit for bit

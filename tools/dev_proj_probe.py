@@ -38,4 +38,6 @@ for K in (768, 3072):
                 e0.record(); run(); e1.record(); torch.cuda.synchronize()
                 tot += e0.elapsed_time(e1)
             res.append(round(tot / 10 * 1000, 1))
-        print(f"K={K} {name:18s}: us {res}")
+        print(f"XBT={os.environ.get('VITK_GEMM_XBT', 'default')} K={K} {name:18s}: us {res}")
+        if os.environ.get("PROBE_FULL_ONLY"):
+            break

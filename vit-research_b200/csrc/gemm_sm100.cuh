@@ -82,18 +82,20 @@ constexpr int GEMM_MAX_STAT_PARTS = 8;    // LN-fold partial (sum, sumsq) pairs 
 // 256 x BN tile — each CTA stages its own 128 rows of A and only HALF of the W tile, which
 // halves the shared-memory fill + operand-read traffic per FLOP (the 1-CTA kernel is bound by
 // it: 16 KB A + 32 KB W filled and 12 KB read per 128 MMA cycles > 128 B/clk/SM).
-template <int BN, int CG>
+// S6 (CTA pair): six operand stages and a single staging tile per epilogue warp instead of five
+// and two -- for the GEMMs whose mainloop, not epilogue, is the critical path.
+template <int BN, int CG, bool S6 = false>
 struct GemmCfg {
-  static constexpr int kStages = (CG == 2) ? 5 : ((BN == 256) ? 4 : 6);
+  static constexpr int kStages = (CG == 2) ? (S6 ? 6 : 5) : ((BN == 256) ? 4 : 6);
   static constexpr int kABytes = GEMM_BM * GEMM_BK * 2;  // 16 KB
   static constexpr int kBRows = BN / CG;                 // W rows this CTA stages
   static constexpr int kBBytes = kBRows * GEMM_BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   // the CTA pair's smaller W stage leaves room to double-buffer the epilogue staging tiles
-  static constexpr int kStagingBufs = (CG == 2) ? 2 : 1;
+  static constexpr int kStagingBufs = (CG == 2 && !S6) ? 2 : 1;
   static constexpr int kStagingBytes = GEMM_EPI_WARPS * kStagingBufs * GEMM_STAGING_BYTES;
   static constexpr int kVecBytes = 2 * BN * 4;   // c1 | c2 (bias) of the current N tile
-  static constexpr int kBarBytes = 256;          // 2*kStages + 4 + 16 mbarriers + TMEM slot
+  static constexpr int kBarBytes = kStages > 5 ? 320 : 256;  // 2*kStages + 4 + 16 mbarriers + TMEM slot
   static constexpr int kCarveBytes = kStages * kStageBytes + kStagingBytes + kVecBytes + kBarBytes;
   // the carve-up starts at the first 1024-B boundary of the dynamic window; ask for as much
   // alignment slack as the 227 KB limit leaves (the kernel traps if it is ever insufficient)
@@ -117,12 +119,12 @@ __device__ __forceinline__ uint32_t dynamic_smem_size() {
   return v;
 }
 
-template <int BN, int EPI, int CG>
+template <int BN, int EPI, int CG, bool S6 = false>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmR,
                     const GemmParams p) {
-  using Cfg = GemmCfg<BN, CG>;
+  using Cfg = GemmCfg<BN, CG, S6>;
   constexpr int kStages = Cfg::kStages;
   constexpr int CH = EpiTraits<EPI>::kChunkCols;
 
