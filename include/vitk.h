@@ -118,6 +118,18 @@ int vitk_bank_set(vitk_handle h, const float* rows_host, int m, int d, const int
 int vitk_bank_set_device(vitk_handle h, const float* rows_dev, int m, int d,
                          const int32_t* labels_dev, int n_classes, int normalise_rows, void* stream);
 
+/* Mutable bank: write m_new rows at [at_row, at_row + m_new).  at_row == current row count
+ * appends (`collection.upsert(embeddings, ids, metadatas)` of new ids: the confident-upsert loop,
+ * generate_clips_hmm.py:456-470, chroma.py:257-261, generate_clips.py:348-370); a smaller at_row
+ * overwrites (upsert of an existing id).  rows (m_new,d) f32 and labels (m_new) int32 (NULL
+ * exactly when the bank was set without labels) are host pointers, or device pointers when
+ * on_device != 0.  Storage grows geometrically; only the new rows are normalised / cast.
+ * Synchronous on `stream`. */
+int vitk_bank_write(vitk_handle h, int at_row, const float* rows, int m_new, const int32_t* labels,
+                    int on_device, int normalise_rows, void* stream);
+/* Rows currently in the bank (`collection.count()`), -1 for a NULL handle. */
+int vitk_bank_rows(vitk_handle h);
+
 /* Top-k + vote.  Stands behind `collection.query(query_embeddings, n_results=k)`
  * (chroma.py:211-214; 'l2' space = squared L2 ascending) / RattChunkRetriever's
  * `sims = Q @ C.T; argpartition; argsort` (ratt_chunk_retriever.py:123,144-148; cosine
@@ -133,6 +145,13 @@ int vitk_bank_set_device(vitk_handle h, const float* rows_dev, int m, int d,
 int vitk_knn_vote(vitk_handle h, const float* q_dev, int n, int k, int metric,
                   int normalise_queries, int32_t* idx_out, float* score_out, int32_t* label_out,
                   int32_t* counts_out, void* stream);
+/* Same under a metadata filter: `collection.query(..., where={...})` (frame_retriever.py:41-53,
+ * ratt_chunk_retriever.py:98-107).  The host evaluates the where-clause on the metadata and
+ * passes row_mask_dev (bank rows) uint8, 1 = row in play; NULL = no filter.  Filtered rows can
+ * never be returned; a query with fewer than k rows in play pads idx with -1 like vitk_knn_vote. */
+int vitk_knn_vote_masked(vitk_handle h, const float* q_dev, int n, int k, int metric,
+                         int normalise_queries, const uint8_t* row_mask_dev, int32_t* idx_out,
+                         float* score_out, int32_t* label_out, int32_t* counts_out, void* stream);
 
 /* Host-buffer end-to-end call: what a frame-labelling loop does per batch
  * (generate_clips_hmm.py:387-412 — embed, query, vote), on static banks.  H2D of the uint8

@@ -63,6 +63,9 @@ SIGNATURES = {
     "vitk_bank_set": (_i, [_vp, _vp, _i, _i, _vp, _i, _i]),
     "vitk_bank_set_device": (_i, [_vp, _vp, _i, _i, _vp, _i, _i, _vp]),
     "vitk_knn_vote": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
+    "vitk_knn_vote_masked": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "vitk_bank_write": (_i, [_vp, _i, _vp, _i, _vp, _i, _i, _vp]),
+    "vitk_bank_rows": (_i, [_vp]),
     "vitk_hmm_decode_counts": (_i, [_vp, _vp, _i, _vp, _i, _vp, _vp, _vp]),
     "vitk_hmm_decode_probs_host": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
     "vitk_op_gemm": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _i, _vp]),

@@ -65,7 +65,7 @@ struct GemmParams {
   int* pool_n;                            // [M] entries appended (may exceed pool_cap: overflow)
   int pool_cap;
   int col_base;                           // bank row of column 0
-  int pool_l2;                            // 1: squared-L2 key
+  int pool_l2;                            // 1: squared-L2 key 2v - bias[n]; 2: v - bias[n] (row penalty)
   int pool_direct;                        // 1: pools are empty, N <= pool_cap: entry n goes to
                                           //    slot n of its row's pool (no atomics, no filter)
 };
@@ -413,8 +413,9 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             }
           } else if constexpr (EPI == EPI_THRESH_POOL) {
             if (p.pool_l2) {
+              const float sc = p.pool_l2 == 1 ? 2.0f : 1.0f;
 #pragma unroll
-              for (int j = 0; j < 32; ++j) v[j] = fmaf(2.0f, v[j], -sVec[BN + lcol0 + j]);
+              for (int j = 0; j < 32; ++j) v[j] = fmaf(sc, v[j], -sVec[BN + lcol0 + j]);
             }
             if (p.pool_direct) {
               if (row < p.M) {

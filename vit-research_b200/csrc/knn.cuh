@@ -71,6 +71,16 @@ bank_prep_kernel(const float* __restrict__ rows, float* __restrict__ out, __nv_b
   if (lane == 0) sqnorm[warp] = (float)s2;
 }
 
+// Per-call row penalty of a filtered query (Chroma `where=`): the metric's own per-row term for
+// the rows in play, +inf for the others, so their keys sink below every real score.
+__global__ void __launch_bounds__(256)
+knn_penalty_kernel(const uint8_t* __restrict__ row_mask, const float* __restrict__ bank_sqnorm,
+                   float* __restrict__ pen, int m, int metric) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m) return;
+  pen[i] = row_mask[i] ? (metric == METRIC_L2 ? bank_sqnorm[i] : 0.f) : INFINITY;
+}
+
 // Total order used everywhere: larger key first, ties -> smaller index first.
 __device__ __forceinline__ bool key_before(float ka, int ia, float kb, int ib) {
   return ka > kb || (ka == kb && ia < ib);
@@ -97,7 +107,7 @@ template <int KPL>
 __global__ void __launch_bounds__(128)
 knn_candidates_reg_kernel(const float* __restrict__ scores, int ld,
                           const float* __restrict__ bank_sqnorm, int nq, int m, int kc, int metric,
-                          int32_t* __restrict__ cand) {
+                          int32_t* __restrict__ cand, const float* __restrict__ pen = nullptr) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (warp >= nq) return;
@@ -109,7 +119,9 @@ knn_candidates_reg_kernel(const float* __restrict__ scores, int ld,
     float s = -INFINITY;
     if (i < m) {
       s = row[i];
-      if (metric == METRIC_L2) s = 2.0f * s - __ldg(bank_sqnorm + i);
+      // `pen` (masked query): ||b||^2 (L2) or 0 (cosine) for the rows in play, +inf otherwise
+      if (pen != nullptr) s = (metric == METRIC_L2 ? 2.0f * s : s) - __ldg(pen + i);
+      else if (metric == METRIC_L2) s = 2.0f * s - __ldg(bank_sqnorm + i);
     }
     key[j] = i < m ? float_order_bits(s) : 0u;
   }
@@ -290,7 +302,8 @@ knn_rerank_vote_kernel(const float* __restrict__ q, const float* __restrict__ ba
                        const int32_t* __restrict__ labels, const int32_t* __restrict__ cand,
                        int nq, int m, int d, int kc, int k, int metric, int n_classes,
                        int32_t* __restrict__ idx_out, float* __restrict__ score_out,
-                       int32_t* __restrict__ label_out, int32_t* __restrict__ counts_out) {
+                       int32_t* __restrict__ label_out, int32_t* __restrict__ counts_out,
+                       const uint8_t* __restrict__ row_mask = nullptr) {
   extern __shared__ float knn_q_smem[];  // [d] query row
   __shared__ float s_key[KNN_MAX_CAND];
   __shared__ int s_idx[KNN_MAX_CAND];
@@ -309,6 +322,7 @@ knn_rerank_vote_kernel(const float* __restrict__ q, const float* __restrict__ ba
       const int c = c0 + s;
       int b = c < kc ? __ldg(cand + (size_t)qi * kc + c) : -1;
       if (b < 0 || b >= m) b = -1;
+      if (b >= 0 && row_mask != nullptr && !__ldg(row_mask + b)) b = -1;  // filtered out (where=)
       bi[s] = b;
       br[s] = bank + (size_t)(b < 0 ? 0 : b) * d;
       acc[s] = 0.f;

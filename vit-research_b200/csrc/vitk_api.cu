@@ -424,6 +424,10 @@ struct vitk_ctx {
   __nv_bfloat16* bank_bf16 = nullptr;
   int32_t* bank_labels = nullptr;
   int bank_m = 0, bank_d = 0, bank_classes = 0;
+  int bank_cap = 0;                 // rows allocated (vitk_bank_write grows geometrically)
+  float* knn_pen = nullptr;         // [knn_pen_cap] row penalty of a filtered query
+  int knn_pen_cap = 0;
+  const float* knn_pen_cur = nullptr;  // == knn_pen while a filtered query is being launched
   CUtensorMap tm_bank;
   // knn workspace (grown on demand)
   float *knn_q = nullptr, *knn_scores = nullptr;
@@ -509,6 +513,7 @@ void free_ctx(vitk_ctx* c) {
   cudaFree(c->resid); cudaFree(c->emb); cudaFree(c->pix_stage);
   cudaFree(c->xb); cudaFree(c->stats[0]); cudaFree(c->stats[1]);
   cudaFree(c->bank); cudaFree(c->bank_sqnorm); cudaFree(c->bank_bf16); cudaFree(c->bank_labels);
+  cudaFree(c->knn_pen);
   cudaFree(c->res_idx); cudaFree(c->res_label); cudaFree(c->res_counts); cudaFree(c->res_score);
   cudaFree(c->knn_q); cudaFree(c->knn_scores); cudaFree(c->knn_qb); cudaFree(c->knn_cand);
   cudaFree(c->knn_pool); cudaFree(c->knn_pool_n); cudaFree(c->knn_thresh); cudaFree(c->knn_overflow);
@@ -1046,6 +1051,7 @@ extern "C" int vitk_bank_set(vitk_handle h, const float* rows_host, int m, int d
   h->bank_m = m;
   h->bank_d = d;
   h->bank_classes = labels_host ? n_classes : 0;
+  h->bank_cap = m;
   h->knn_cap_m = 0;  // force workspace re-check
   return 0;
 }
@@ -1087,9 +1093,90 @@ extern "C" int vitk_bank_set_device(vitk_handle h, const float* rows_dev, int m,
   h->bank_m = m;
   h->bank_d = d;
   h->bank_classes = labels_dev ? n_classes : 0;
+  h->bank_cap = m;
   h->launches += 1;
   return 0;
 }
+
+// Mutable bank (the confident-upsert loop, generate_clips_hmm.py:456-470 / chroma.py:257-261):
+// rows [at_row, at_row + m_new) are written -- at_row == bank rows appends, smaller overwrites
+// (Chroma upsert of an existing id).  Storage grows geometrically, only the new rows go through
+// the prep kernel, so a 16-row upsert costs microseconds whatever the bank size.
+extern "C" int vitk_bank_write(vitk_handle h, int at_row, const float* rows, int m_new,
+                               const int32_t* labels, int on_device, int normalise_rows,
+                               void* stream) {
+  if (!h) return 1;
+  Err& e = h->err;
+  if (h->bank_m == 0) { e.set("vitk_bank_write: no bank set (call vitk_bank_set first)"); return 1; }
+  if (m_new == 0) return 0;
+  if (!rows || m_new < 0 || at_row < 0 || at_row > h->bank_m) {
+    e.set("vitk_bank_write: bad argument (at_row=%d, m_new=%d, bank rows=%d)", at_row, m_new, h->bank_m);
+    return 1;
+  }
+  if ((labels != nullptr) != (h->bank_classes > 0)) {
+    e.set("vitk_bank_write: labels must be given exactly when the bank has labels");
+    return 1;
+  }
+  CK(e, cudaSetDevice(h->device));
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int d = h->bank_d;
+  const int m_after = at_row + m_new > h->bank_m ? at_row + m_new : h->bank_m;
+  if (m_after > h->bank_cap) {
+    CK(e, cudaDeviceSynchronize());  // nothing may still be reading the old arrays
+    int cap = 2 * h->bank_cap;
+    if (cap < m_after) cap = m_after;
+    cap = (cap + 127) & ~127;
+    float *nb = nullptr, *nsq = nullptr;
+    __nv_bfloat16* nbb = nullptr;
+    int32_t* nl = nullptr;
+    if (dev_alloc(e, &nb, (size_t)cap * d) || dev_alloc(e, &nbb, (size_t)cap * d) ||
+        dev_alloc(e, &nsq, (size_t)cap) || dev_alloc(e, &nl, (size_t)cap)) {
+      cudaFree(nb); cudaFree(nbb); cudaFree(nsq); cudaFree(nl);
+      return 1;
+    }
+    const size_t m0 = (size_t)h->bank_m;
+    CK(e, cudaMemcpy(nb, h->bank, m0 * d * 4, cudaMemcpyDeviceToDevice));
+    CK(e, cudaMemcpy(nbb, h->bank_bf16, m0 * d * 2, cudaMemcpyDeviceToDevice));
+    CK(e, cudaMemcpy(nsq, h->bank_sqnorm, m0 * 4, cudaMemcpyDeviceToDevice));
+    CK(e, cudaMemcpy(nl, h->bank_labels, m0 * 4, cudaMemcpyDeviceToDevice));
+    cudaFree(h->bank); cudaFree(h->bank_bf16); cudaFree(h->bank_sqnorm); cudaFree(h->bank_labels);
+    h->bank = nb; h->bank_bf16 = nbb; h->bank_sqnorm = nsq; h->bank_labels = nl;
+    h->bank_cap = cap;
+  }
+  const float* src = rows;
+  float* tmp = nullptr;
+  int32_t* tmpl = nullptr;
+  if (!on_device) {
+    if (labels) {
+      for (int i = 0; i < m_new; ++i)
+        if (labels[i] < 0 || labels[i] >= h->bank_classes) {
+          e.set("vitk_bank_write: label %d of row %d outside [0,%d)", labels[i], i, h->bank_classes);
+          return 1;
+        }
+    }
+    if (dev_alloc(e, &tmp, (size_t)m_new * d)) return 1;
+    CK(e, cudaMemcpyAsync(tmp, rows, (size_t)m_new * d * 4, cudaMemcpyHostToDevice, st));
+    src = tmp;
+    if (labels)
+      CK(e, cudaMemcpyAsync(h->bank_labels + at_row, labels, (size_t)m_new * 4, cudaMemcpyHostToDevice, st));
+  } else if (labels) {
+    CK(e, cudaMemcpyAsync(h->bank_labels + at_row, labels, (size_t)m_new * 4, cudaMemcpyDeviceToDevice, st));
+  }
+  (void)tmpl;
+  if (!labels) CK(e, cudaMemsetAsync(h->bank_labels + at_row, 0, (size_t)m_new * 4, st));
+  bank_prep_kernel<<<(m_new + 7) / 8, 256, 0, st>>>(src, h->bank + (size_t)at_row * d,
+                                                    h->bank_bf16 + (size_t)at_row * d,
+                                                    h->bank_sqnorm + at_row, m_new, d, normalise_rows);
+  CK(e, cudaGetLastError());
+  CK(e, cudaStreamSynchronize(st));  // host rows / the staging copy may be released on return
+  cudaFree(tmp);
+  if (tmap_operand(e, &h->tm_bank, h->bank_bf16, m_after, d, 128)) return 1;
+  h->bank_m = m_after;
+  h->launches += 1;
+  return 0;
+}
+
+extern "C" int vitk_bank_rows(vitk_handle h) { return h ? h->bank_m : -1; }
 
 namespace {
 int knn_candidates_for(int k, int m) {
@@ -1118,9 +1205,10 @@ int knn_stage(vitk_ctx* h, int n, int kc, int metric, int lo, int hi, int flag, 
     return 1;
   GemmParams gp{};
   gp.M = n; gp.N = hi - lo; gp.K = d;
-  gp.bias = metric == METRIC_L2 ? h->bank_sqnorm + lo : nullptr;
+  gp.bias = h->knn_pen_cur ? h->knn_pen_cur + lo : (metric == METRIC_L2 ? h->bank_sqnorm + lo : nullptr);
   gp.pool_thresh = h->knn_thresh; gp.pool = h->knn_pool; gp.pool_n = h->knn_pool_n;
-  gp.pool_cap = KNN_POOL_CAP; gp.col_base = lo; gp.pool_l2 = metric == METRIC_L2 ? 1 : 0;
+  gp.pool_cap = KNN_POOL_CAP; gp.col_base = lo;
+  gp.pool_l2 = metric == METRIC_L2 ? 1 : (h->knn_pen_cur ? 2 : 0);
   gp.pool_direct = direct ? 1 : 0;
   if (launch_gemm(e, EPI_THRESH_POOL, ta, tb, ta, ta, gp, st)) return 1;
   knn_pool_select_kernel<<<n, 128, 0, st>>>(h->knn_pool, h->knn_pool_n, h->knn_thresh, n,
@@ -1214,6 +1302,14 @@ int knn_large_candidates(vitk_ctx* h, int n, int kc, int metric, cudaStream_t st
 extern "C" int vitk_knn_vote(vitk_handle h, const float* q_dev, int n, int k, int metric,
                              int normalise_queries, int32_t* idx_out, float* score_out,
                              int32_t* label_out, int32_t* counts_out, void* stream) {
+  return vitk_knn_vote_masked(h, q_dev, n, k, metric, normalise_queries, nullptr, idx_out, score_out,
+                              label_out, counts_out, stream);
+}
+
+extern "C" int vitk_knn_vote_masked(vitk_handle h, const float* q_dev, int n, int k, int metric,
+                                    int normalise_queries, const uint8_t* row_mask_dev,
+                                    int32_t* idx_out, float* score_out, int32_t* label_out,
+                                    int32_t* counts_out, void* stream) {
   if (!h) return 1;
   Err& e = h->err;
   if (h->bank_m == 0) { e.set("vitk_knn_vote: no bank set"); return 1; }
@@ -1236,7 +1332,14 @@ extern "C" int vitk_knn_vote(vitk_handle h, const float* q_dev, int n, int k, in
     cudaFree(h->knn_q); cudaFree(h->knn_qb); cudaFree(h->knn_scores); cudaFree(h->knn_cand);
     h->knn_q = nullptr; h->knn_qb = nullptr; h->knn_scores = nullptr; h->knn_cand = nullptr;
     const int cq = n > h->knn_cap_q ? n : h->knn_cap_q;
-    const int cm = ld > h->knn_cap_m ? ld : h->knn_cap_m;
+    // a growing (mutable) bank: leave headroom so that a 16-row upsert does not reallocate
+    int cm = h->knn_cap_m;
+    if (ld > cm) {
+      cm = ld + (ld >> 1);
+      const int top = (KNN_DIRECT_MAX + 3) & ~3;
+      if (cm > top) cm = top;
+      if (cm < ld) cm = ld;
+    }
     h->knn_cap_q = 0;
     if (dev_alloc(e, &h->knn_q, (size_t)cq * d) || dev_alloc(e, &h->knn_qb, (size_t)cq * d) ||
         dev_alloc(e, &h->knn_scores, (size_t)cq * cm) ||
@@ -1250,8 +1353,27 @@ extern "C" int vitk_knn_vote(vitk_handle h, const float* q_dev, int n, int k, in
                                                    normalise_queries);
   CK(e, cudaGetLastError());
   h->launches += 1;
+  const float* pen = nullptr;
+  if (row_mask_dev != nullptr) {
+    if (m > h->knn_pen_cap) {
+      CK(e, cudaStreamSynchronize(st));
+      cudaFree(h->knn_pen);
+      h->knn_pen = nullptr;
+      h->knn_pen_cap = 0;
+      const int cap = (m + (m >> 1) + 127) & ~127;
+      if (dev_alloc(e, &h->knn_pen, (size_t)cap)) return 1;
+      h->knn_pen_cap = cap;
+    }
+    knn_penalty_kernel<<<(m + 255) / 256, 256, 0, st>>>(row_mask_dev, h->bank_sqnorm, h->knn_pen, m, metric);
+    CK(e, cudaGetLastError());
+    h->launches += 1;
+    pen = h->knn_pen;
+  }
   if (large) {
-    if (knn_large_candidates(h, n, kc, metric, st)) return 1;
+    h->knn_pen_cur = pen;
+    const int rc = knn_large_candidates(h, n, kc, metric, st);
+    h->knn_pen_cur = nullptr;
+    if (rc) return 1;
   } else {
     CUtensorMap ta, tc;
     if (tmap_operand(e, &ta, h->knn_qb, n, d, GEMM_BM) ||
@@ -1264,17 +1386,17 @@ extern "C" int vitk_knn_vote(vitk_handle h, const float* q_dev, int n, int k, in
     const float* sc = h->knn_scores;
     const float* sq = h->bank_sqnorm;
     int32_t* cd = h->knn_cand;
-    if (m <= 256) knn_candidates_reg_kernel<8><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd);
-    else if (m <= 512) knn_candidates_reg_kernel<16><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd);
-    else if (m <= 1024) knn_candidates_reg_kernel<32><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd);
-    else if (m <= 1536) knn_candidates_reg_kernel<48><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd);
-    else knn_candidates_reg_kernel<64><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd);
+    if (m <= 256) knn_candidates_reg_kernel<8><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd, pen);
+    else if (m <= 512) knn_candidates_reg_kernel<16><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd, pen);
+    else if (m <= 1024) knn_candidates_reg_kernel<32><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd, pen);
+    else if (m <= 1536) knn_candidates_reg_kernel<48><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd, pen);
+    else knn_candidates_reg_kernel<64><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd, pen);
     CK(e, cudaGetLastError());
     h->launches += 2;
   }
   knn_rerank_vote_kernel<<<n, 128, (size_t)d * sizeof(float), st>>>(
       h->knn_q, h->bank, h->bank_classes ? h->bank_labels : nullptr, h->knn_cand, n, m, d, kc, k,
-      metric, h->bank_classes, idx_out, score_out, label_out, counts_out);
+      metric, h->bank_classes, idx_out, score_out, label_out, counts_out, row_mask_dev);
   CK(e, cudaGetLastError());
   h->launches += 1;
   return 0;
