@@ -23,7 +23,7 @@ def launches(path):
     for row in csv.DictReader(lines):
         if row.get("Metric Name") != "gpu__time_duration.sum":
             continue
-        name = re.sub(r"\(.*", "", row["Kernel Name"])
+        name = re.sub(r"\(.*", "", row["Kernel Name"])  # drop the argument list, keep <...>
         v = float(row["Metric Value"].replace(",", ""))
         v = v / 1e3 if row["Metric Unit"] == "ns" else v * 1e3 if row["Metric Unit"] == "ms" else v
         a = agg.setdefault(name, [0, 0.0])
