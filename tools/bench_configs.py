@@ -1,7 +1,7 @@
 """The other BASELINE.json configs at full size (they are parity-test cases, not bench lines; this
 tool records what they run at).  One JSON line per config, rank 0 prints.
-  python tools/bench_configs.py c3|c4|c5            (1 GPU)
-  torchrun --nproc-per-node N tools/bench_configs.py c3|c4|c5
+  python tools/bench_configs.py c3|c4|c5|c5s        (1 GPU)
+  torchrun --nproc-per-node N tools/bench_configs.py c3|c4|c5|c5s
 c3: ViT-B/16, 108 000-frame stream sharded by contiguous chunk, host uint8 frames through the
     streaming API (H2D/D2H inside), top-25 vote, then the per-video Viterbi on the gathered counts.
 c4: ViT-L/16, batch 512, embedding only (device-resident bf16 pixels).
@@ -139,6 +139,56 @@ def main():
                     "ms_per_step": ms, "frames_per_s": world * B / ms * 1e3, "search_only_ms": ms_s,
                     "search_queries_per_s": world * B / ms_s * 1e3,
                     "redo": int(v.load().vitk_knn_redo_count(emb.handle)), "top1_score_mean": float(r[1][:, 0].mean())})
+    elif which == "c5s":
+        # the same search with the store ROW-SHARDED over the ranks and one exchange step
+        # (all-gather queries -> local top-k -> all-gather (row, score) lists -> merge), checked
+        # against the replicated store on every rank
+        B, steps, k, m = 256, 10, 10, 1_000_000
+        geom = v.ViTGeometry.vit_b16()
+        emb = v.ViTEmbedder(geom, v.random_init_state_dict(geom, 0), device=local, max_batch=B)
+        import dataclasses
+        small = dataclasses.replace(v.ViTGeometry.vit_b16(), layers=1)
+        emb2 = v.ViTEmbedder(small, v.random_init_state_dict(small, 0), device=local, max_batch=8)
+        gd = torch.Generator(device="cuda").manual_seed(99)
+        store = torch.randn((m, 768), generator=gd, device="cuda")
+        full = v.BankIndex(emb, store, None, 0, metric="cosine", normalise_rows=True)
+        lo, hi = v.frame_ranges(m, world)[rank]
+        shard = v.BankIndex(emb2, store[lo:hi].contiguous(), None, 0, metric="cosine", normalise_rows=True)
+        del store
+        gq = torch.Generator().manual_seed(4321 + rank)
+        px = [(torch.randn(B, 3, 224, 224, generator=gq) * 0.5).clamp_(-1, 1).cuda().bfloat16() for _ in range(2)]
+        o = torch.empty((B, 768), device="cuda")
+
+        def step(i):
+            emb.embed(px[i % 2], out=o)
+            return v.shard.search_sharded_store(lambda q, kk: shard.search(q, kk, normalise_queries=True)[:2],
+                                                o, k, lo, world * B)
+
+        for i in range(3):
+            r = step(i)
+        want = full.search(o, k, normalise_queries=True)
+        same = float((r[0] == want[0]).float().mean())
+        score_err = float((r[1] - want[1]).abs().max())
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            r = step(i)
+        e1.record()
+        barrier()
+        ms = sync_max(e0.elapsed_time(e1)) / steps
+        e0.record()
+        for i in range(steps):
+            r = v.shard.search_sharded_store(lambda q, kk: shard.search(q, kk, normalise_queries=True)[:2],
+                                             o, k, lo, world * B)
+        e1.record()
+        barrier()
+        ms_s = sync_max(e0.elapsed_time(e1)) / steps
+        out.update({"workload": "ViT-B/16 embed 256 frames/GPU + cosine top-10 vs a 1M-row store row-sharded over the "
+                                "ranks (NCCL: all-gather queries, local top-10, all-gather lists, merge)",
+                    "ms_per_step": ms, "frames_per_s": world * B / ms * 1e3, "search_only_ms": ms_s,
+                    "search_queries_per_s": world * B / ms_s * 1e3, "rows_per_rank": hi - lo,
+                    "idx_mismatch_fraction_vs_replicated": sync_max(1.0 - same), "score_max_abs_diff": sync_max(score_err)})
     if rank == 0:
         print(json.dumps(out), flush=True)
     if world > 1:
