@@ -228,6 +228,25 @@ int vitk_op_layernorm(const float* x_dev, const float* gamma_dev, const float* b
 /* out[frames,S,heads*64] (bf16) = softmax(q k^T / 8) v from qkv[frames,S,3*heads*64] (bf16). */
 int vitk_op_attention(const void* qkv_bf16_dev, void* out_bf16_dev, int frames, int S, int heads,
                       void* stream);
+/* ---- ChunkEncoder pieces (models/chunk_encoder.py:9-97) ----------------
+ * The temporal transformer over [CLS, frame_1..frame_T] embeddings runs its linear layers on
+ * vitk_op_gemm; these three cover the rest.
+ * Attention over short sequences with any head width (Keras MultiHeadAttention inside
+ * nn_blocks.TransformerEncoderBlock, chunk_encoder.py:17-31: 8 heads of 96):
+ *   out[n_seq,S,heads*d_head] (bf16) = softmax((q / sqrt(d_head)) k^T) v from
+ *   qkv[n_seq,S,3*heads*d_head] (bf16);  S <= 64, d_head a multiple of 32 up to 128;
+ *   probs_out (may be NULL) f32 [n_seq,heads,S,S] = the attention scores the block returns. */
+int vitk_op_attention_small(const void* qkv_bf16_dev, void* out_bf16_dev, float* probs_out_dev,
+                            int n_seq, int S, int heads, int d_head, void* stream);
+/* y f32 [rows,d] = LayerNorm of `rows` f32 rows that sit row_stride floats apart (the CLS row of
+ * every sequence: chunk_encoder.py:83-86). */
+int vitk_op_layernorm_rows_f32(const float* x_dev, const float* gamma_dev, const float* beta_dev,
+                               float* y_dev, int rows, long long row_stride, int d, float eps,
+                               void* stream);
+/* class_head (chunk_encoder.py:34-38): logit[n] = w2 . relu(W1 x + b1) + b2; W1 [hidden,d] f32. */
+int vitk_op_chunk_head(const float* x_dev, const float* w1_dev, const float* b1_dev,
+                       const float* w2_dev, const float* b2_dev, float* logit_dev, int n, int d,
+                       int hidden, void* stream);
 /* im2col + pixel-format conversion: out bf16 [n*(P+1), C*patch*patch] with a zero CLS row. */
 int vitk_op_patchify(const void* pixels_dev, int pixel_format, void* out_bf16_dev, int n, int C,
                      int H, int W, int patch, void* stream);

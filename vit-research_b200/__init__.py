@@ -13,5 +13,6 @@ from .knn import (BankCollection, BankIndex, RattChunkRetriever, determine_class
 from . import hmm as hmm_module  # noqa: F401,E402
 from .hmm import hmm, viterbi_from_counts, viterbi_from_probs  # noqa: F401,E402
 from . import store  # noqa: F401,E402
+from .chunk_encoder import ChunkEncoder  # noqa: F401,E402
 from . import shard  # noqa: F401,E402
 from .shard import frame_ranges, gather_frames, label_frames_sharded  # noqa: F401,E402

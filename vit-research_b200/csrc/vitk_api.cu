@@ -22,6 +22,7 @@
 #include "knn.cuh"
 #include "hmm.cuh"
 #include "preprocess.cuh"
+#include "chunk.cuh"
 
 using namespace vitk;
 
@@ -1788,6 +1789,73 @@ extern "C" int vitk_op_attention(const void* qkv, void* out, int frames, int S, 
        launch_attention(e, tq, tkv, to, frames, S, heads, reinterpret_cast<cudaStream_t>(stream));
   if (rc) g_create_error = e.msg;
   return rc;
+}
+
+// ---- ChunkEncoder pieces (chunk.cuh) ----------------------------------------------------------
+extern "C" int vitk_op_attention_small(const void* qkv, void* out, float* probs_out, int n_seq, int S,
+                                       int heads, int d_head, void* stream) {
+  Err& e = g_op_err;
+  auto fail = [&]() { g_create_error = e.msg; return 1; };
+  if (n_seq == 0) return 0;
+  if (!qkv || !out || n_seq < 0 || S < 1 || S > SATT_MAX_S || heads < 1 || d_head < 32 ||
+      d_head > SATT_MAX_DH || d_head % 32 != 0) {
+    e.set("vitk_op_attention_small: need 1 <= S <= %d and d_head a multiple of 32 in [32,%d] "
+          "(S=%d d_head=%d heads=%d)", SATT_MAX_S, SATT_MAX_DH, S, d_head, heads);
+    return fail();
+  }
+  const size_t smem = ((size_t)S * (d_head + 1) + 2 * (size_t)S * d_head) * sizeof(float);
+  static size_t attr_smem = 48 * 1024;
+  if (smem > attr_smem) {
+    if (cudaFuncSetAttribute(small_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)smem) != cudaSuccess) {
+      e.set("vitk_op_attention_small: cannot reserve %zu B of shared memory", smem);
+      return fail();
+    }
+    attr_smem = smem;
+  }
+  small_attention_kernel<<<n_seq * heads, 128, smem, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const __nv_bfloat16*>(qkv), reinterpret_cast<__nv_bfloat16*>(out), probs_out, S,
+      heads, d_head, 1.0f / sqrtf((float)d_head));
+  if (cudaGetLastError() != cudaSuccess) { e.set("vitk_op_attention_small: launch failed"); return fail(); }
+  return 0;
+}
+
+extern "C" int vitk_op_layernorm_rows_f32(const float* x, const float* gamma, const float* beta, float* y,
+                                          int rows, long long row_stride, int d, float eps, void* stream) {
+  Err& e = g_op_err;
+  if (rows == 0) return 0;
+  if (!x || !gamma || !beta || !y || rows < 0 || d < 1 || row_stride < d) {
+    e.set("vitk_op_layernorm_rows_f32: bad argument");
+    g_create_error = e.msg;
+    return 1;
+  }
+  layernorm_rows_f32_kernel<<<(rows + 7) / 8, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      x, gamma, beta, y, rows, row_stride, d, eps);
+  if (cudaGetLastError() != cudaSuccess) {
+    e.set("vitk_op_layernorm_rows_f32: launch failed");
+    g_create_error = e.msg;
+    return 1;
+  }
+  return 0;
+}
+
+extern "C" int vitk_op_chunk_head(const float* x, const float* w1, const float* b1, const float* w2,
+                                  const float* b2, float* logit, int n, int d, int hidden, void* stream) {
+  Err& e = g_op_err;
+  if (n == 0) return 0;
+  if (!x || !w1 || !b1 || !w2 || !b2 || !logit || n < 0 || d < 1 || d > 8192 || hidden < 1) {
+    e.set("vitk_op_chunk_head: bad argument");
+    g_create_error = e.msg;
+    return 1;
+  }
+  chunk_head_kernel<<<n, 256, (size_t)(d + 8) * sizeof(float), reinterpret_cast<cudaStream_t>(stream)>>>(
+      x, w1, b1, w2, b2, logit, d, hidden);
+  if (cudaGetLastError() != cudaSuccess) {
+    e.set("vitk_op_chunk_head: launch failed");
+    g_create_error = e.msg;
+    return 1;
+  }
+  return 0;
 }
 
 // Developer hook (not in include/vitk.h): device buffer of 2*16*8 int64 clock samples written by
