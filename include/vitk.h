@@ -99,6 +99,13 @@ int vitk_embed_host_u8(vitk_handle h, const uint8_t* frames_host, int n, float* 
  * rescale+normalise happens there).  Asynchronous on `stream`. */
 int vitk_preprocess_resize_u8(vitk_handle h, const uint8_t* frames_dev, int n, int in_h, int in_w,
                               uint8_t* out_dev, void* stream);
+/* The TF path's front-end: cv2.resize(frame, (image_w, image_h), interpolation=cv2.INTER_AREA)
+ * (generate_clips_hmm.py:392, chroma.py:204-205, write_embeddings.py:225-226), shrinking only:
+ * OpenCV's area tables (covered fraction / cell width per source pixel, float accumulation,
+ * round half to even), or the integer box mean when both scale factors are integers.
+ * frames_dev (n,in_h,in_w,C) uint8 -> out_dev (n,image_h,image_w,C) uint8.  Asynchronous. */
+int vitk_preprocess_resize_area_u8(vitk_handle h, const uint8_t* frames_dev, int n, int in_h,
+                                   int in_w, uint8_t* out_dev, void* stream);
 /* hf_vit_embed_batch(frames_np) for host frames of ANY size: H2D of the raw frames, resize,
  * forward in max_batch chunks, D2H of the embeddings; synchronous. */
 int vitk_embed_resize_host_u8(vitk_handle h, const uint8_t* frames_host, int n, int in_h, int in_w,

@@ -103,3 +103,63 @@ def synthetic_frames(name: str, n: int = 1) -> np.ndarray:
         img[h // 4:h // 2, w // 3:w // 2] = rng.integers(0, 256, 3)
         out.append(np.clip(img, 0, 255).astype(np.uint8))
     return np.stack(out)
+
+
+# ---------------------------------------------------------------------------------------------
+# cv2.resize(..., interpolation=cv2.INTER_AREA), shrinking (the TF path's front-end:
+# generate_clips_hmm.py:392, chroma.py:204-205, write_embeddings.py:225-226).
+# PARITY UNPINNED: OpenCV is not in this image (`import cv2` fails) and the reference pins no
+# version; restated from OpenCV's published imgproc/resize.cpp: computeResizeAreaTab,
+# ResizeArea_Invoker (float accumulation, saturate_cast<uchar> = round half to even) and, when
+# both scale factors are integers, ResizeAreaFast (integer box sum * (1.f / area)).
+# ---------------------------------------------------------------------------------------------
+def area_tab(ssize, dsize):
+    """computeResizeAreaTab: list per destination index of (source index, float32 weight)."""
+    scale = ssize / dsize
+    tab = []
+    for dx in range(dsize):
+        fsx1 = dx * scale
+        fsx2 = fsx1 + scale
+        cell = min(scale, ssize - fsx1)
+        sx1, sx2 = int(np.ceil(fsx1)), int(np.floor(fsx2))
+        sx2 = min(sx2, ssize - 1)
+        sx1 = min(sx1, sx2)
+        ent = []
+        if sx1 - fsx1 > 1e-3:
+            ent.append((sx1 - 1, np.float32((sx1 - fsx1) / cell)))
+        for sx in range(sx1, sx2):
+            ent.append((sx, np.float32(1.0 / cell)))
+        if fsx2 - sx2 > 1e-3:
+            ent.append((sx2, np.float32(min(min(fsx2 - sx2, 1.0), cell) / cell)))
+        tab.append(ent)
+    return tab
+
+
+def resize_area_u8(img, out_h, out_w):
+    """img (H,W,C) uint8 -> (out_h,out_w,C) uint8, INTER_AREA shrinking."""
+    img = np.asarray(img, np.uint8)
+    H, W, C = img.shape
+    if H < out_h or W < out_w:
+        raise ValueError("INTER_AREA restatement covers shrinking only")
+    if H % out_h == 0 and W % out_w == 0:
+        sy, sx = H // out_h, W // out_w
+        box = img.reshape(out_h, sy, out_w, sx, C).astype(np.int64).sum((1, 3))
+        val = box.astype(np.float32) * np.float32(1.0 / np.float32(sx * sy))
+        return np.clip(np.rint(val), 0, 255).astype(np.uint8)
+    xt, yt = area_tab(W, out_w), area_tab(H, out_h)
+    src = img.astype(np.float32)
+    # horizontal reduction of every source row: buf = 0; buf += S * alpha (separate mul and add)
+    hbuf = np.zeros((H, out_w, C), np.float32)
+    for dx, ent in enumerate(xt):
+        acc = np.zeros((H, C), np.float32)
+        for sx, a in ent:
+            acc = acc + src[:, sx, :] * a
+        hbuf[:, dx, :] = acc
+    out = np.zeros((out_h, out_w, C), np.uint8)
+    for dy, ent in enumerate(yt):
+        acc = None
+        for sy, b in ent:
+            t = b * hbuf[sy]
+            acc = t if acc is None else acc + t
+        out[dy] = np.clip(np.rint(acc), 0, 255).astype(np.uint8)
+    return out

@@ -83,3 +83,38 @@ def test_build_frame_store_from_image_files(v, model_emb, tmp_path):
     mm, fp, idx = v.store.load_frame_store("t", cache_dir=str(tmp_path / "cache"))
     assert mm.shape == (19, 768) and fp == paths and idx[paths[3]] == 3
     assert np.array_equal(np.asarray(mm), emb.embed_frames(frames))
+
+
+@pytest.mark.parametrize("hw", [(720, 1280), (1080, 1920), (864, 1536), (433, 769), (480, 854), (2160, 3840),
+                                (224, 224), (448, 672), (1000, 225)])
+def test_inter_area_resize_is_bit_exact_against_restatement(v, model_emb, hw):
+    """cv2.resize(frame, (w, h), interpolation=cv2.INTER_AREA) of the TF path (generate_clips_hmm.py:392):
+    the CUDA kernel against the restated OpenCV algorithm, bit for bit (general tables, the integer
+    box-mean form and identity); growing an image is refused."""
+    from oracle import preprocess_ref
+    _, emb = model_emb            # 224 x 224 model: any larger frame shrinks to it
+    n = 2 if hw[0] * hw[1] < 1_000_000 else 1
+    f = np.random.default_rng(hw[0]).integers(0, 256, (n, hw[0], hw[1], 3), dtype=np.uint8)
+    got = emb.resize_frames(torch.from_numpy(f).cuda(), interpolation="area").cpu().numpy()
+    want = np.stack([preprocess_ref.resize_area_u8(x, 224, 224) for x in f])
+    assert np.array_equal(got, want)
+
+
+def test_inter_area_to_the_tf_frame_size_and_errors(v):
+    from oracle import preprocess_ref, vit_ref
+    geom = v.ViTGeometry.tf_432x768()
+    import dataclasses
+    geom = dataclasses.replace(geom, layers=1)
+    emb = v.ViTEmbedder(geom, v.random_init_state_dict(geom, 0), device=0, max_batch=4)
+    try:
+        f = np.random.default_rng(1).integers(0, 256, (2, 720, 1280, 3), dtype=np.uint8)
+        got = emb.resize_frames(torch.from_numpy(f).cuda(), interpolation="area").cpu().numpy()
+        assert got.shape == (2, 432, 768, 3)
+        assert np.array_equal(got, np.stack([preprocess_ref.resize_area_u8(x, 432, 768) for x in f]))
+        small = torch.zeros((1, 200, 300, 3), dtype=torch.uint8, device="cuda")
+        with pytest.raises(v.VitkError):
+            emb.resize_frames(small, interpolation="area")
+        with pytest.raises(v.VitkError):
+            emb.resize_frames(torch.from_numpy(f).cuda(), interpolation="lanczos")
+    finally:
+        emb.close()

@@ -71,6 +71,7 @@ SIGNATURES = {
     "vitk_op_gemm": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _i, _vp]),
     "vitk_op_gemm_fused": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _i, _f, _vp, _vp, _vp, _vp]),
     "vitk_op_rowstats": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
+    "vitk_preprocess_resize_area_u8": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),
     "vitk_op_attention_small": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "vitk_op_layernorm_rows_f32": (_i, [_vp, _vp, _vp, _vp, _i, C.c_longlong, _i, _f, _vp]),
     "vitk_op_chunk_head": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),

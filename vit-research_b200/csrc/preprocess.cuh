@@ -92,4 +92,62 @@ __global__ void __launch_bounds__(256) resize_u8_aa_kernel(const ResizeParams p)
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// cv2.resize(frame, (768, 432), interpolation=cv2.INTER_AREA) -- the TF path's front-end
+// (generate_clips_hmm.py:392, chroma.py:204-205, write_embeddings.py:225-226).  OpenCV [3P]
+// imgproc/resize.cpp, shrinking case: per axis a table of (source index, weight) entries, weight =
+// covered fraction of the source pixel / cell width (computeResizeAreaTab, built on the host in
+// double); per destination row the source rows are reduced horizontally into a float buffer
+// (buf += S * alpha), accumulated vertically (sum = beta * buf, then sum += beta * buf), and
+// written with saturate_cast<uchar> (round half to even).  Multiplies and adds are kept separate
+// (the C++ loop is not FMA-contracted in OpenCV's baseline x86 build).  When both scale factors
+// are integers OpenCV takes ResizeAreaFast instead: integer box sum, then sum * (1.f / area).
+// ---------------------------------------------------------------------------------------------
+struct AreaAxis {
+  const int* off;      // [out + 1] first table entry of each destination index
+  const int* si;       // source index of every entry
+  const float* alpha;  // its weight
+};
+struct AreaParams {
+  const uint8_t* in;   // [n, in_h, in_w, C]
+  uint8_t* out;        // [n, out_h, out_w, C]
+  AreaAxis x, y;
+  int n, C, in_h, in_w, out_h, out_w;
+  int fast_sx, fast_sy;  // > 0: both scales are integers (ResizeAreaFast)
+  float fast_scale;      // 1.f / (fast_sx * fast_sy)
+};
+
+__global__ void __launch_bounds__(256) resize_area_u8_kernel(const AreaParams p) {
+  const int dy = blockIdx.x, f = blockIdx.y;
+  const int C = p.C, row_elems = p.out_w * C;
+  const uint8_t* src = p.in + (size_t)f * p.in_h * p.in_w * C;
+  uint8_t* dst = p.out + ((size_t)f * p.out_h + dy) * row_elems;
+  for (int e = threadIdx.x; e < row_elems; e += blockDim.x) {
+    const int dx = e / C, c = e - dx * C;
+    float sum = 0.f;
+    if (p.fast_sx > 0) {
+      int acc = 0;
+      for (int yy = 0; yy < p.fast_sy; ++yy) {
+        const uint8_t* srow = src + ((size_t)(dy * p.fast_sy + yy) * p.in_w + (size_t)dx * p.fast_sx) * C + c;
+        for (int xx = 0; xx < p.fast_sx; ++xx) acc += srow[xx * C];
+      }
+      sum = __fmul_rn((float)acc, p.fast_scale);
+    } else {
+      bool first = true;
+      for (int yi = p.y.off[dy]; yi < p.y.off[dy + 1]; ++yi) {
+        const uint8_t* srow = src + (size_t)p.y.si[yi] * p.in_w * C + c;
+        float buf = 0.f;
+        for (int xi = p.x.off[dx]; xi < p.x.off[dx + 1]; ++xi)
+          buf = __fadd_rn(buf, __fmul_rn((float)srow[p.x.si[xi] * C], p.x.alpha[xi]));
+        const float t = __fmul_rn(p.y.alpha[yi], buf);
+        sum = first ? t : __fadd_rn(sum, t);
+        first = false;
+      }
+    }
+    int r = __float2int_rn(sum);
+    r = r < 0 ? 0 : (r > 255 ? 255 : r);
+    dst[e] = (uint8_t)r;
+  }
+}
+
 }  // namespace vitk

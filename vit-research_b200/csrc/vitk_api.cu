@@ -453,6 +453,12 @@ struct vitk_ctx {
     size_t smem = 0;
   };
   std::map<std::pair<int, int>, ResizePlan> resize_plans;
+  struct AreaPlan {
+    void* blob = nullptr;
+    AreaAxis x{}, y{};
+    int fast_sx = 0, fast_sy = 0;
+  };
+  std::map<std::pair<int, int>, AreaPlan> area_plans;
   uint8_t* raw_stage = nullptr;   // device staging for raw frames of vitk_embed_resize_host_u8
   size_t raw_stage_bytes = 0;
   // Viterbi workspace (grown on demand)
@@ -521,6 +527,7 @@ void free_ctx(vitk_ctx* c) {
   if (c->knn_overflow_host) cudaFreeHost(c->knn_overflow_host);
   cudaFree(c->hmm_loge); cudaFree(c->hmm_table); cudaFree(c->hmm_bp); cudaFree(c->hmm_offsets);
   for (auto& kv : c->resize_plans) cudaFree(kv.second.blob);
+  for (auto& kv : c->area_plans) cudaFree(kv.second.blob);
   cudaFree(c->raw_stage);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
   for (auto& sl : c->slots) {
@@ -1542,6 +1549,97 @@ extern "C" int vitk_preprocess_resize_u8(vitk_handle h, const uint8_t* frames_de
   if (n > 65535) { e.set("vitk_preprocess_resize_u8: at most 65535 frames per call"); return 1; }
   CK(e, cudaSetDevice(h->device));
   return launch_resize(h, frames_dev, n, in_h, in_w, out_dev, reinterpret_cast<cudaStream_t>(stream));
+}
+
+namespace {
+struct HostAreaAxis {
+  std::vector<int> off, si;
+  std::vector<float> alpha;
+};
+// OpenCV computeResizeAreaTab (imgproc/resize.cpp), scale = ssize / dsize >= 1, in double
+HostAreaAxis build_area_axis(int ssize, int dsize) {
+  HostAreaAxis a;
+  const double scale = (double)ssize / dsize;
+  a.off.push_back(0);
+  for (int dx = 0; dx < dsize; ++dx) {
+    const double fsx1 = dx * scale, fsx2 = fsx1 + scale;
+    const double cell = std::min(scale, ssize - fsx1);
+    int sx1 = (int)std::ceil(fsx1), sx2 = (int)std::floor(fsx2);
+    sx2 = std::min(sx2, ssize - 1);
+    sx1 = std::min(sx1, sx2);
+    if (sx1 - fsx1 > 1e-3) { a.si.push_back(sx1 - 1); a.alpha.push_back((float)((sx1 - fsx1) / cell)); }
+    for (int sx = sx1; sx < sx2; ++sx) { a.si.push_back(sx); a.alpha.push_back((float)(1.0 / cell)); }
+    if (fsx2 - sx2 > 1e-3) {
+      a.si.push_back(sx2);
+      a.alpha.push_back((float)(std::min(std::min(fsx2 - sx2, 1.0), cell) / cell));
+    }
+    a.off.push_back((int)a.si.size());
+  }
+  return a;
+}
+
+int get_area_plan(vitk_ctx* h, int in_h, int in_w, vitk_ctx::AreaPlan** out) {
+  Err& e = h->err;
+  auto key = std::make_pair(in_h, in_w);
+  auto it = h->area_plans.find(key);
+  if (it != h->area_plans.end()) { *out = &it->second; return 0; }
+  const int out_h = h->cfg.image_h, out_w = h->cfg.image_w;
+  vitk_ctx::AreaPlan pl;
+  if (in_w % out_w == 0 && in_h % out_h == 0) {  // both scales integer: ResizeAreaFast
+    pl.fast_sx = in_w / out_w;
+    pl.fast_sy = in_h / out_h;
+  } else {
+    HostAreaAxis ax = build_area_axis(in_w, out_w), ay = build_area_axis(in_h, out_h);
+    const size_t nx = ax.si.size(), ny = ay.si.size();
+    const size_t bytes = 4 * ((out_w + 1) + nx + nx + (out_h + 1) + ny + ny);
+    std::vector<uint8_t> blob(bytes);
+    int* ip = reinterpret_cast<int*>(blob.data());
+    size_t o = 0;
+    memcpy(ip + o, ax.off.data(), 4 * (size_t)(out_w + 1)); const size_t o_xoff = o; o += out_w + 1;
+    memcpy(ip + o, ax.si.data(), 4 * nx); const size_t o_xsi = o; o += nx;
+    memcpy(ip + o, ax.alpha.data(), 4 * nx); const size_t o_xa = o; o += nx;
+    memcpy(ip + o, ay.off.data(), 4 * (size_t)(out_h + 1)); const size_t o_yoff = o; o += out_h + 1;
+    memcpy(ip + o, ay.si.data(), 4 * ny); const size_t o_ysi = o; o += ny;
+    memcpy(ip + o, ay.alpha.data(), 4 * ny); const size_t o_ya = o; o += ny;
+    uint8_t* dev = nullptr;
+    if (dev_alloc(e, &dev, bytes)) return 1;
+    CK(e, cudaMemcpy(dev, blob.data(), bytes, cudaMemcpyHostToDevice));
+    pl.blob = dev;
+    const int* dip = reinterpret_cast<const int*>(dev);
+    const float* dfp = reinterpret_cast<const float*>(dev);
+    pl.x = AreaAxis{dip + o_xoff, dip + o_xsi, dfp + o_xa};
+    pl.y = AreaAxis{dip + o_yoff, dip + o_ysi, dfp + o_ya};
+  }
+  *out = &h->area_plans.emplace(key, pl).first->second;
+  return 0;
+}
+}  // namespace
+
+extern "C" int vitk_preprocess_resize_area_u8(vitk_handle h, const uint8_t* frames_dev, int n, int in_h,
+                                              int in_w, uint8_t* out_dev, void* stream) {
+  if (!h) return 1;
+  Err& e = h->err;
+  if (n == 0) return 0;
+  if (!frames_dev || !out_dev || n < 0 || in_h < 1 || in_w < 1) { e.set("vitk_preprocess_resize_area_u8: bad argument"); return 1; }
+  if (n > 65535) { e.set("vitk_preprocess_resize_area_u8: at most 65535 frames per call"); return 1; }
+  if (in_h < h->cfg.image_h || in_w < h->cfg.image_w) {
+    e.set("vitk_preprocess_resize_area_u8: INTER_AREA is built for shrinking only (%dx%d -> %dx%d)", in_w, in_h,
+          h->cfg.image_w, h->cfg.image_h);
+    return 1;
+  }
+  CK(e, cudaSetDevice(h->device));
+  vitk_ctx::AreaPlan* pl = nullptr;
+  if (get_area_plan(h, in_h, in_w, &pl)) return 1;
+  AreaParams p;
+  p.in = frames_dev; p.out = out_dev; p.x = pl->x; p.y = pl->y;
+  p.n = n; p.C = h->cfg.channels; p.in_h = in_h; p.in_w = in_w;
+  p.out_h = h->cfg.image_h; p.out_w = h->cfg.image_w;
+  p.fast_sx = pl->fast_sx; p.fast_sy = pl->fast_sy;
+  p.fast_scale = pl->fast_sx > 0 ? 1.f / (float)(pl->fast_sx * pl->fast_sy) : 0.f;
+  resize_area_u8_kernel<<<dim3((unsigned)p.out_h, (unsigned)n, 1), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(p);
+  CK(e, cudaGetLastError());
+  h->launches += 1;
+  return 0;
 }
 
 extern "C" int vitk_embed_resize_host_u8(vitk_handle h, const uint8_t* frames_host, int n, int in_h,

@@ -192,9 +192,11 @@ class ViTEmbedder:
                                   int(l2_normalise), stream_ptr(stream)), self.handle, "vitk_embed")
         return out
 
-    def resize_frames(self, frames, out=None, stream=None):
-        """CUDA uint8 (N,H,W,C) frames of any size -> CUDA uint8 (N,image_h,image_w,C): the HF
-        processor's resize (BILINEAR, antialias, on uint8) as one kernel, bit-identical."""
+    def resize_frames(self, frames, out=None, stream=None, interpolation="bilinear_aa"):
+        """CUDA uint8 (N,H,W,C) frames of any size -> CUDA uint8 (N,image_h,image_w,C).
+        interpolation="bilinear_aa": the HF processor's resize (BILINEAR, antialias, on uint8) as
+        one kernel, bit-identical.  interpolation="area": cv2.INTER_AREA shrinking, the TF path's
+        front-end (generate_clips_hmm.py:392)."""
         import torch
 
         g = self.geometry
@@ -205,6 +207,13 @@ class ViTEmbedder:
         n, ih, iw = frames.shape[:3]
         if out is None:
             out = torch.empty((n, g.image_h, g.image_w, g.channels), dtype=torch.uint8, device=frames.device)
+        if interpolation == "area":
+            check(self.lib.vitk_preprocess_resize_area_u8(self.handle, ptr(frames), n, ih, iw, ptr(out),
+                                                          stream_ptr(stream)), self.handle,
+                  "vitk_preprocess_resize_area_u8")
+            return out
+        if interpolation != "bilinear_aa":
+            raise VitkError(f"unknown interpolation {interpolation!r}")
         check(self.lib.vitk_preprocess_resize_u8(self.handle, ptr(frames), n, ih, iw, ptr(out),
                                                  stream_ptr(stream)), self.handle,
               "vitk_preprocess_resize_u8")
