@@ -258,6 +258,12 @@ int vitk_op_chunk_head(const float* x_dev, const float* w1_dev, const float* b1_
 int vitk_op_patchify(const void* pixels_dev, int pixel_format, void* out_bf16_dev, int n, int C,
                      int H, int W, int patch, void* stream);
 
+/* In-step timing of the dominant kernel: while enabled, every fc1 GEMM launch of the forward
+ * (HF modeling_vit.py:287-299; 26 % of the step) is bracketed by a CUDA-event pair on the
+ * launching stream.  vitk_profile_fc1_read waits for them, returns the summed duration and the
+ * number of launches, and clears the list (bench.py's roofline.in_step). */
+int vitk_profile_fc1(vitk_handle h, int enable);
+int vitk_profile_fc1_read(vitk_handle h, double* total_ms, int* launches);
 /* Kernel launches issued by this handle since creation (bench.py's gpu_launches). */
 int64_t vitk_launch_count(vitk_handle h);
 /* Large-store k-NN stages that had to be redone because a candidate pool overflowed (0 on

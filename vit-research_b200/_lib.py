@@ -78,6 +78,8 @@ SIGNATURES = {
     "vitk_op_layernorm": (_i, [_vp, _vp, _vp, _vp, _i, _i, _f, _vp]),
     "vitk_op_attention": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "vitk_op_patchify": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp]),
+    "vitk_profile_fc1": (_i, [_vp, _i]),
+    "vitk_profile_fc1_read": (_i, [_vp, C.POINTER(C.c_double), C.POINTER(_i)]),
     "vitk_launch_count": (C.c_int64, [_vp]),
     "vitk_knn_redo_count": (C.c_int64, [_vp]),
 }

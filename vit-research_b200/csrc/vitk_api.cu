@@ -468,6 +468,9 @@ struct vitk_ctx {
   int hmm_cap_t = 0, hmm_cap_seq = 0, hmm_cap_k = -1;
   cudaStream_t own_stream = nullptr;
   int64_t launches = 0;
+  // vitk_profile_fc1: CUDA-event pairs around every fc1 GEMM launch of the forward
+  bool prof_fc1 = false;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
   // streaming host API (vitk_stream_submit / vitk_stream_wait): two batches in flight
   struct StreamSlot {
     uint8_t* pix = nullptr;
@@ -528,6 +531,7 @@ void free_ctx(vitk_ctx* c) {
   cudaFree(c->hmm_loge); cudaFree(c->hmm_table); cudaFree(c->hmm_bp); cudaFree(c->hmm_offsets);
   for (auto& kv : c->resize_plans) cudaFree(kv.second.blob);
   for (auto& kv : c->area_plans) cudaFree(kv.second.blob);
+  for (auto& pr : c->prof_events) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
   cudaFree(c->raw_stage);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
   for (auto& sl : c->slots) {
@@ -563,6 +567,33 @@ extern "C" const char* vitk_last_error(vitk_handle h) {
 
 extern "C" int64_t vitk_launch_count(vitk_handle h) { return h ? h->launches : 0; }
 extern "C" int64_t vitk_knn_redo_count(vitk_handle h) { return h ? h->knn_redo_stages : 0; }
+
+extern "C" int vitk_profile_fc1(vitk_handle h, int enable) {
+  if (!h) return 1;
+  h->prof_fc1 = enable != 0;
+  return 0;
+}
+
+extern "C" int vitk_profile_fc1_read(vitk_handle h, double* total_ms, int* launches) {
+  if (!h || !total_ms || !launches) return 1;
+  Err& e = h->err;
+  CK(e, cudaSetDevice(h->device));
+  double tot = 0.0;
+  int n = 0;
+  for (auto& pr : h->prof_events) {
+    CK(e, cudaEventSynchronize(pr.second));
+    float ms = 0.f;
+    CK(e, cudaEventElapsedTime(&ms, pr.first, pr.second));
+    tot += ms;
+    ++n;
+    cudaEventDestroy(pr.first);
+    cudaEventDestroy(pr.second);
+  }
+  h->prof_events.clear();
+  *total_ms = tot;
+  *launches = n;
+  return 0;
+}
 
 extern "C" int vitk_create(const vitk_config* cfg, int device, vitk_handle* out) {
   Err e;
@@ -927,7 +958,17 @@ int forward_chunk(vitk_ctx* c, const void* pix, int fmt, int n, float* emb_f32,
     f1.M = M; f1.N = F; f1.K = D; f1.bias = L.b_fc1; f1.c1 = L.c1_fc1;
     f1.stats = c->stats[1]; f1.stats_parts = parts; f1.stats_stride = sstride;
     f1.inv_d = 1.0f / D; f1.eps = cfg.ln_eps;
+    cudaEvent_t pe0 = nullptr, pe1 = nullptr;
+    if (c->prof_fc1) {
+      CK(e, cudaEventCreate(&pe0));
+      CK(e, cudaEventCreate(&pe1));
+      CK(e, cudaEventRecord(pe0, st));
+    }
     if (launch_gemm(e, epi_fc1, mp->a_xb, L.tm_fc1, mp->c_h, mp->c_h, f1, st)) return 1;
+    if (c->prof_fc1) {
+      CK(e, cudaEventRecord(pe1, st));
+      c->prof_events.emplace_back(pe0, pe1);
+    }
     GemmParams f2{};
     f2.M = M; f2.N = D; f2.K = F; f2.bias = L.b_fc2;
     if (li + 1 < nl) {  // nobody reads the copy / sums after the last layer
