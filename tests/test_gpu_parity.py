@@ -365,3 +365,27 @@ def test_empty_and_ragged_inputs(v, b16, banks):
     tiny = v.BankIndex(emb, rows[:3], labels[:3], 3, metric="cosine", normalise_rows=True)
     idx, score, label, counts = tiny.search(torch.from_numpy(rows[:2]).cuda(), 5, normalise_queries=True)
     assert (idx[:, :3] >= 0).all() and (idx[:, 3:] == -1).all() and (counts.sum(1) == 3).all()
+
+
+def test_in_step_fc1_timing_hook(v, b16):
+    """vitk_profile_fc1: one CUDA-event pair per fc1 launch of the forward (11 of the 12 layers run
+    the full-width MLP, the last one only its CLS rows), a positive summed duration, list cleared
+    by the read; results are unchanged by the instrumentation."""
+    import ctypes
+    _, emb = b16
+    lib = v.load()
+    px = (torch.randn(8, 3, 224, 224, generator=torch.Generator().manual_seed(3)) * 0.5).clamp_(-1, 1).cuda()
+    want = emb.embed(px).clone()
+    assert lib.vitk_profile_fc1(emb.handle, 1) == 0
+    got = emb.embed(px)
+    got2 = emb.embed(px)
+    tot, cnt = ctypes.c_double(0.0), ctypes.c_int(0)
+    assert lib.vitk_profile_fc1(emb.handle, 0) == 0
+    assert lib.vitk_profile_fc1_read(emb.handle, ctypes.byref(tot), ctypes.byref(cnt)) == 0
+    n_full = emb.geometry.layers - 1
+    assert cnt.value == 2 * n_full and tot.value > 0.0
+    assert torch.equal(got, want) and torch.equal(got2, want)
+    assert lib.vitk_profile_fc1_read(emb.handle, ctypes.byref(tot), ctypes.byref(cnt)) == 0
+    assert cnt.value == 0
+    emb.embed(px)
+    assert lib.vitk_profile_fc1_read(emb.handle, ctypes.byref(tot), ctypes.byref(cnt)) == 0 and cnt.value == 0
