@@ -335,6 +335,10 @@ def test_code_path_variants_agree():
     # CTA-pair GEMMs with five operand stages / two staging tiles vs six / one: pipeline depth only
     s5 = _fingerprint({"VITK_GEMM_S6": "0"})
     assert np.array_equal(base, s5)
+    # every kernel walking its rows upwards vs the "snake" order (each kernel starts on the rows its
+    # producer wrote last): tile order only
+    up = _fingerprint({"VITK_SNAKE": "0"})
+    assert np.array_equal(base, up)
     # attention v2 (exact row max, two passes) vs v3 (shift by the first-32 max): the bf16 P tiles
     # are rounded at a different scale, so the two agree to bf16 noise (either one is 0.99996 from
     # the fp32 oracle; measured 0.999988 between them on B200), not bit for bit

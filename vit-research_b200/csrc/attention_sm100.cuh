@@ -59,6 +59,7 @@ struct AttnParams {
   int frames;
   int q_rows;   // queries per frame that are needed (== S, or fewer: last-layer CLS shortcut)
   int nblk;     // query blocks per (frame, head): 1 if q_rows <= 128 else 2
+  int reverse;  // v3: walk the (frame, head) units from the last to the first ("snake" order)
   float scale_log2e;  // (1/sqrt(d)) * log2(e)
   long long* dbg;     // developer timeline (tools/dev_attn_timeline.py): null in production
 };
@@ -397,7 +398,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       for (int u = blockIdx.x; u < units; u += gridDim.x, ++j) {
         const int st = j & 1;
         const uint32_t ph = (j >> 1) & 1;
-        const int frame = u / p.heads, head = u % p.heads;
+        const int uu = p.reverse ? units - 1 - u : u;
+        const int frame = uu / p.heads, head = uu % p.heads;
         uint8_t* sb = smem + st * L.stage_bytes;
         mbar_wait(&stage_empty[st], ph ^ 1u);
         mbar_arrive_expect_tx(&kv_full[st], 16384 * nblk + SK * 128);
@@ -483,7 +485,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       const int st = j & 1;
       const uint32_t uph = j & 1;
       const int b = g ^ (j & 1);
-      const int frame = u / p.heads, head = u % p.heads;
+      const int uu = p.reverse ? units - 1 - u : u;
+        const int frame = uu / p.heads, head = uu % p.heads;
       const bool blk_active = b < nblk;
       const int rows_valid = blk_active ? min(128, p.q_rows - b * 128) : 0;
       const bool warp_active = wq * 32 < rows_valid;

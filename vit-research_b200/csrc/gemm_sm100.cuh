@@ -45,6 +45,7 @@ enum GemmEpilogue : int {
 
 struct GemmParams {
   int M, N, K;
+  int reverse_m;       // walk the row units from the last to the first ("snake" order, see vitk_api.cu)
   const float* bias;   // [N]   bias, or c2 when stats != null
   const float* c1;     // [N]   LN fold column term (only read when stats != null)
   const float* stats;  // LN fold: per-row partial (sum, sumsq) pairs; null = plain bias epilogue
@@ -161,6 +162,8 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const int n_tiles = (p.N + BN - 1) / BN;
   const int num_tiles = m_units * n_tiles;
   const int num_kb = p.K / GEMM_BK;
+  // row unit of work unit t: ascending, or descending when the caller walks this GEMM backwards
+  auto m_unit_of = [&](int t) { return p.reverse_m ? m_units - 1 - t / n_tiles : t / n_tiles; };
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -196,7 +199,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = first_unit; tile < num_tiles; tile += unit_stride) {
-        const int m_blk = (tile / n_tiles) * CG + (int)rank, n_blk = tile % n_tiles;
+        const int m_blk = m_unit_of(tile) * CG + (int)rank, n_blk = tile % n_tiles;
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1u);
           uint8_t* a_dst = sA + stage * Cfg::kABytes;
@@ -276,7 +279,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     // EPI_BIAS_RESID_F32: lane 0 asks TMA for the residual chunk (tile_, c_) into buffer b_
     auto resid_request = [&](int tile_, int c_, uint32_t b_) {
       if (tile_ >= num_tiles) return;
-      const int r0_ = ((tile_ / n_tiles) * CG + (int)rank) * GEMM_BM + q * 32;
+      const int r0_ = (m_unit_of(tile_) * CG + (int)rank) * GEMM_BM + q * 32;
       const int c0_ = (tile_ % n_tiles) * BN + half * kColsPerWarp + c_ * CH;
       if (c0_ < p.N && r0_ < p.M) {
         mbar_arrive_expect_tx(&rbar[b_], GEMM_STAGING_BYTES);
@@ -287,7 +290,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       if (lane == 0) resid_request(first_unit, 0, 0);
     }
     for (int tile = first_unit; tile < num_tiles; tile += unit_stride) {
-      const int m_blk = (tile / n_tiles) * CG + (int)rank, n_blk = tile % n_tiles;
+      const int m_blk = m_unit_of(tile) * CG + (int)rank, n_blk = tile % n_tiles;
       const int row0 = m_blk * GEMM_BM + q * 32;
       const int row = row0 + lane;
       if constexpr (EpiTraits<EPI>::kUsesVec) {
@@ -333,7 +336,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             if (p.stats != nullptr) prefetch_l1(p.c1 + nn);
           }
           if constexpr (EpiTraits<EPI>::kOutBf16) {
-            const int nrow = ((nt / n_tiles) * CG + (int)rank) * GEMM_BM + q * 32 + lane;
+            const int nrow = (m_unit_of(nt) * CG + (int)rank) * GEMM_BM + q * 32 + lane;
             if (p.stats != nullptr && nrow < p.M) {
               const float* np_ = p.stats + (size_t)nrow * p.stats_stride;
               prefetch_l1(np_);

@@ -249,7 +249,7 @@ long long* g_attn_dbg = nullptr;  // developer timeline buffer (vitk_dev_attn_ti
 
 // q_rows > 0: only the first q_rows queries of every frame are needed (last layer: the CLS row)
 int launch_attention(Err& e, const CUtensorMap& tq, const CUtensorMap& tkv, const CUtensorMap& to,
-                     int frames, int S, int heads, cudaStream_t st, int q_rows = 0) {
+                     int frames, int S, int heads, cudaStream_t st, int q_rows = 0, int reverse = 0) {
   if (S < 1 || S > ATT_MAX_S) {
     e.set("attention: S=%d unsupported (1..%d)", S, ATT_MAX_S);
     return 1;
@@ -265,6 +265,7 @@ int launch_attention(Err& e, const CUtensorMap& tq, const CUtensorMap& tkv, cons
   p.frames = frames;
   p.q_rows = q_rows > 0 && q_rows < S ? q_rows : S;
   p.nblk = (p.q_rows + 127) / 128;
+  p.reverse = reverse;
   p.scale_log2e = 0.125f * 1.4426950408889634f;  // head dim 64 -> 1/sqrt(64)
   p.dbg = g_attn_dbg;
   if (S > 256) {
@@ -912,6 +913,14 @@ int forward_chunk(vitk_ctx* c, const void* pix, int fmt, int n, float* emb_f32,
   c->launches += 3;
   const int epi_fc1 = cfg.gelu_tanh ? EPI_BIAS_GELUT_BF16 : EPI_BIAS_GELU_BF16;
   const size_t nl = c->layers.size();
+  // "Snake" order: every big kernel walks its rows in the direction opposite to the kernel that
+  // produced its input, so it starts on the ~100 MB its producer wrote LAST -- still in the
+  // 126 MB L2 -- instead of on rows that were evicted long ago (each activation is 77-310 MB).
+  // Results do not depend on the order.  VITK_SNAKE=0 keeps every kernel ascending.
+  static int snake = -1;
+  if (snake < 0) { const char* v = getenv("VITK_SNAKE"); snake = (v && atoi(v) == 0) ? 0 : 1; }
+  int dir = snake;  // rowstats_cast wrote xb ascending: the first QKV GEMM goes down
+  auto next_dir = [&]() { const int d = dir; dir ^= snake; return d; };
   for (size_t li = 0; li < nl; ++li) {
     LayerW& L = c->layers[li];
     // (a5.1+a5.2) LN1 folded into the fused QKV GEMM: A = raw residual (bf16), stats[0]
@@ -919,6 +928,7 @@ int forward_chunk(vitk_ctx* c, const void* pix, int fmt, int n, float* emb_f32,
     q.M = M; q.N = 3 * D; q.K = D; q.bias = L.b_qkv; q.c1 = L.c1_qkv;
     q.stats = c->stats[0]; q.stats_parts = parts; q.stats_stride = sstride;
     q.inv_d = 1.0f / D; q.eps = cfg.ln_eps;
+    q.reverse_m = next_dir();
     if (launch_gemm(e, EPI_BIAS_BF16, mp->a_xb, L.tm_qkv, mp->c_qkv, mp->c_qkv, q, st)) return 1;
     // Last layer: the reference reads only last_hidden_state[:,0,:] (ratt_write_clips_to_ragdb.py
     // :148), and after the attention every remaining op is row-wise, so only the CLS query and
@@ -926,7 +936,7 @@ int forward_chunk(vitk_ctx* c, const void* pix, int fmt, int n, float* emb_f32,
     const bool cls_only = (li + 1 == nl) && c->cls_only_last && c->S > 1;
     // (a5.3) attention
     if (launch_attention(e, mp->att_q, mp->att_kv, mp->att_o, n, c->S, cfg.heads, st,
-                         cls_only ? 1 : 0))
+                         cls_only ? 1 : 0, next_dir()))
       return 1;
     if (cls_only) {
       const long long pitch = (long long)c->S;
@@ -951,6 +961,7 @@ int forward_chunk(vitk_ctx* c, const void* pix, int fmt, int n, float* emb_f32,
     GemmParams o{};
     o.M = M; o.N = D; o.K = D; o.bias = L.b_o;
     o.xb = c->xb; o.xb_ld = D; o.stats_out = c->stats[1]; o.stats_out_stride = sstride;
+    o.reverse_m = next_dir();
     if (launch_gemm(e, EPI_BIAS_RESID_F32, mp->a_act, L.tm_o, mp->c_resid, mp->c_resid, o, st))
       return 1;
     // (a5.1+a5.5) LN2 folded into fc1 + GELU, then fc2 + residual (+ next layer's LN1 inputs)
@@ -958,6 +969,7 @@ int forward_chunk(vitk_ctx* c, const void* pix, int fmt, int n, float* emb_f32,
     f1.M = M; f1.N = F; f1.K = D; f1.bias = L.b_fc1; f1.c1 = L.c1_fc1;
     f1.stats = c->stats[1]; f1.stats_parts = parts; f1.stats_stride = sstride;
     f1.inv_d = 1.0f / D; f1.eps = cfg.ln_eps;
+    f1.reverse_m = next_dir();
     cudaEvent_t pe0 = nullptr, pe1 = nullptr;
     if (c->prof_fc1) {
       CK(e, cudaEventCreate(&pe0));
@@ -971,6 +983,7 @@ int forward_chunk(vitk_ctx* c, const void* pix, int fmt, int n, float* emb_f32,
     }
     GemmParams f2{};
     f2.M = M; f2.N = D; f2.K = F; f2.bias = L.b_fc2;
+    f2.reverse_m = next_dir();
     if (li + 1 < nl) {  // nobody reads the copy / sums after the last layer
       f2.xb = c->xb; f2.xb_ld = D; f2.stats_out = c->stats[0]; f2.stats_out_stride = sstride;
     }
