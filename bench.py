@@ -126,6 +126,17 @@ def cpu_reference_time(sample: int, repeats: int, warmup: int):
     return times, cores, torch.get_num_threads()
 
 
+_JSON_FD = None
+
+
+def emit_json(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def run_reference(args, rank):
     if rank != 0:
         return
@@ -147,7 +158,7 @@ def run_reference(args, rank):
         "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit_json(line)
 
 
 # ---------------------------------------------------------------------------------------------
@@ -369,7 +380,7 @@ def run_ours(args, rank, local_rank, world):
                                 "sample": f"32 frames, best of 2 after 1 warm-up; transformers.ViTModel fp32 eager "
                                           f"(the reference's embed path) + numpy k-NN/vote on {cores} host cores"}
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit_json(line)
     emb.close()
     if world > 1:
         dist.destroy_process_group()
@@ -385,6 +396,12 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    # stdout carries the ONE JSON line and nothing else: libraries that write to fd 1 (NCCL prints
+    # "NCCL version ..." there when the box exports NCCL_DEBUG) are sent to stderr instead.
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args, rank)
     else:
