@@ -45,9 +45,14 @@ typedef struct vitk_config {
 
 enum { VITK_PIX_F32_NCHW = 0, VITK_PIX_BF16_NCHW = 1, VITK_PIX_U8_NHWC = 2 };
 enum { VITK_METRIC_COSINE = 0, VITK_METRIC_L2 = 1 };
+/* resize of raw frames to the model resolution: the HF processor's antialiased bilinear
+ * (image_processing_vit.py:20-27), cv2.INTER_AREA (generate_clips_hmm.py:392, loader.py:7) and
+ * cv2's default INTER_LINEAR (smarter_generate_clips.py:81) */
+enum { VITK_RESIZE_BILINEAR_AA = 0, VITK_RESIZE_AREA = 1, VITK_RESIZE_LINEAR = 2 };
 enum {
   VITK_EPI_BIAS_BF16 = 0, VITK_EPI_BIAS_GELU_BF16 = 1, VITK_EPI_BIAS_GELUT_BF16 = 2,
-  VITK_EPI_BIAS_RESID_F32 = 3, VITK_EPI_TABLE_F32 = 4, VITK_EPI_F32 = 5
+  VITK_EPI_BIAS_RESID_F32 = 3, VITK_EPI_TABLE_F32 = 4, VITK_EPI_F32 = 5,
+  VITK_EPI_BIAS_RESID_BF16 = 7   /* 6 is internal (k-NN threshold filter) */
 };
 
 /* Library / build identification (no device needed). */
@@ -102,10 +107,17 @@ int vitk_preprocess_resize_u8(vitk_handle h, const uint8_t* frames_dev, int n, i
 /* The TF path's front-end: cv2.resize(frame, (image_w, image_h), interpolation=cv2.INTER_AREA)
  * (generate_clips_hmm.py:392, chroma.py:204-205, write_embeddings.py:225-226), shrinking only:
  * OpenCV's area tables (covered fraction / cell width per source pixel, float accumulation,
- * round half to even), or the integer box mean when both scale factors are integers.
+ * round half to even), the integer box sum * (1.f / area) when both scale factors are integers,
+ * and (a + b + c + d + 2) >> 2 at exactly 2 x 2 -- byte-identical to cv2 4.13.
  * frames_dev (n,in_h,in_w,C) uint8 -> out_dev (n,image_h,image_w,C) uint8.  Asynchronous. */
 int vitk_preprocess_resize_area_u8(vitk_handle h, const uint8_t* frames_dev, int n, int in_h,
                                    int in_w, uint8_t* out_dev, void* stream);
+/* cv2.resize(im, (image_w, image_h)) with the default interpolation, INTER_LINEAR: the resize
+ * extract_embeddings applies (smarter_generate_clips.py:81).  OpenCV's 8-bit fixed-point bilinear
+ * (11-bit coefficients, no antialiasing), shrinking or growing, byte-identical to cv2 4.13.
+ * frames_dev (n,in_h,in_w,C) uint8 -> out_dev (n,image_h,image_w,C) uint8.  Asynchronous. */
+int vitk_preprocess_resize_linear_u8(vitk_handle h, const uint8_t* frames_dev, int n, int in_h,
+                                     int in_w, uint8_t* out_dev, void* stream);
 /* hf_vit_embed_batch(frames_np) for host frames of ANY size: H2D of the raw frames, resize,
  * forward in max_batch chunks, D2H of the embeddings; synchronous. */
 int vitk_embed_resize_host_u8(vitk_handle h, const uint8_t* frames_host, int n, int in_h, int in_w,
@@ -137,6 +149,17 @@ int vitk_bank_write(vitk_handle h, int at_row, const float* rows, int m_new, con
 /* Rows currently in the bank (`collection.count()`), -1 for a NULL handle. */
 int vitk_bank_rows(vitk_handle h);
 
+/* Several banks on one handle -- the reference keeps several Chroma collections side by side (the
+ * left/right/none label bank, chroma.py:145; the clip / chunk stores, ratt_write_clips_to_ragdb.py:
+ * 302-310).  A handle starts with bank 0 current.  vitk_bank_new parks the current bank and makes
+ * a fresh empty one current (returns its id >= 1, -1 on error); vitk_bank_select switches the
+ * current bank (every vitk_bank_* / vitk_knn_* / vote call works on the current one);
+ * vitk_bank_free releases a bank's device memory (the current one becomes empty). */
+int vitk_bank_new(vitk_handle h);
+int vitk_bank_select(vitk_handle h, int bank_id);
+int vitk_bank_current(vitk_handle h);
+int vitk_bank_free(vitk_handle h, int bank_id);
+
 /* Top-k + vote.  Stands behind `collection.query(query_embeddings, n_results=k)`
  * (chroma.py:211-214; 'l2' space = squared L2 ascending) / RattChunkRetriever's
  * `sims = Q @ C.T; argpartition; argsort` (ratt_chunk_retriever.py:123,144-148; cosine
@@ -144,7 +167,9 @@ int vitk_bank_rows(vitk_handle h);
  *   q_dev (n,d) f32; normalise_queries: q / (||q|| + 1e-8) first.
  *   idx_out (n,k) int32 bank rows in result order; score_out (n,k) f32 (cosine similarity, or
  *   squared L2 distance); label_out (n) int32 (first-max of counts); counts_out (n,n_classes).
- *   Any out pointer except idx_out/score_out may be NULL.  k <= 64.
+ *   Any out pointer except idx_out/score_out may be NULL.  1 <= k <= 1024 (the vote uses 5 / 25 /
+ *   50; the clip-store queries ask for n_results = search_k = 100-750, frame_retriever.py:41-43,
+ *   config.py:10-11).  k <= 64 re-ranks 2k+32 candidates, larger k re-ranks k + k/4 + 32.
  * Banks of up to 2048 rows: fully asynchronous on `stream`.  Larger stores (the 1 M-row clip
  * store of rag_vit / RattChunkRetriever) never materialise the (n,m) score matrix: the
  * similarity GEMM's epilogue filters scores against a running per-query threshold into small
@@ -159,6 +184,31 @@ int vitk_knn_vote(vitk_handle h, const float* q_dev, int n, int k, int metric,
 int vitk_knn_vote_masked(vitk_handle h, const float* q_dev, int n, int k, int metric,
                          int normalise_queries, const uint8_t* row_mask_dev, int32_t* idx_out,
                          float* score_out, int32_t* label_out, int32_t* counts_out, void* stream);
+
+/* Same with a PER-QUERY row predicate evaluated inside the kernels -- RattChunkRetriever's
+ * `valid_mask = (cand_vids != vid) & (cand_tcenters >= q_start) & (cand_tcenters <= q_end)` within
+ * one side (ratt_chunk_retriever.py:85-88,98-107,130-134) and FrameRetriever's
+ * `where={"$and": [{"vid_num": {"$ne": vid}}, {"side": side}, {"t_norm": {"$gte": ..}}, {"t_norm":
+ * {"$lte": ..}}]}` (frame_retriever.py:41-53): no (queries x rows) mask is ever built.
+ * Columns are device arrays indexed by bank row, q_* device arrays indexed by query; a NULL column
+ * switches its clause off.  Row r is in play for query i iff
+ *     ne_col[r] != q_ne[i]  and  eq_col[r] == q_eq[i]  and  q_lo[i] <= x <= q_hi[i]
+ * with x = rng_col[r], rounded to float32 first when rng_round_f32 != 0 (the reference compares
+ * float32 arrays), and -- when q_lo2/q_hi2 are given -- also q_lo2[i] <= rng_col[r] <= q_hi2[i] on
+ * the un-rounded double (the side-wide `collection.get` window).  row_mask_dev (may be NULL)
+ * applies on top, as in vitk_knn_vote_masked.  Queries with fewer than k rows in play pad idx
+ * with -1. */
+typedef struct vitk_row_filter {
+  const int32_t* ne_col; const int32_t* q_ne;
+  const int32_t* eq_col; const int32_t* q_eq;
+  const double* rng_col; const double* q_lo; const double* q_hi;
+  const double* q_lo2;   const double* q_hi2;
+  int32_t rng_round_f32;
+} vitk_row_filter;
+int vitk_knn_vote_filtered(vitk_handle h, const float* q_dev, int n, int k, int metric,
+                           int normalise_queries, const uint8_t* row_mask_dev,
+                           const vitk_row_filter* filter, int32_t* idx_out, float* score_out,
+                           int32_t* label_out, int32_t* counts_out, void* stream);
 
 /* Host-buffer end-to-end call: what a frame-labelling loop does per batch
  * (generate_clips_hmm.py:387-412 — embed, query, vote), on static banks.  H2D of the uint8
@@ -180,6 +230,15 @@ int vitk_stream_submit(vitk_handle h, int slot, const uint8_t* frames_host, int 
                        float* emb_host, int32_t* label_host, int32_t* idx_host, float* score_host,
                        int32_t* counts_host);
 int vitk_stream_wait(vitk_handle h, int slot);
+/* Same for RAW frames of any size -- what build_frame_store feeds (PIL frames at the video's
+ * resolution, ratt_write_clips_to_ragdb.py:197-209) and what extract_embeddings loads: the H2D
+ * copy carries (n,in_h,in_w,C) uint8 frames, the resize (interp = VITK_RESIZE_*) runs on the
+ * slot's stream in front of the forward, so raw frames take the same overlapped path.
+ * l2_normalise: hf_vit_embed_batch normalises (1); Keras pre_logits are raw (0). */
+int vitk_stream_submit_raw(vitk_handle h, int slot, const uint8_t* frames_host, int n, int in_h,
+                           int in_w, int interp, int l2_normalise, int k, int metric,
+                           float* emb_host, int32_t* label_host, int32_t* idx_host,
+                           float* score_host, int32_t* counts_host);
 
 /* ---- vote -> HMM smoothing (the step right after the path) ------------------------------ */
 /* Stands behind class hmm (nba_proj/hmm.py:5-135: add_first, add_col_to_lattice,
@@ -218,6 +277,10 @@ int vitk_op_gemm(const void* a_bf16_dev, const void* w_bf16_dev, void* out_dev, 
  *      out f32 = acc + bias + resid;  xb_out (bf16 copy of out, may be NULL);  stats_out
  *      (may be NULL): per row 2*ceil(N/256) partial (sum, sumsq) pairs of out, pair index
  *      2*(n/256) + (n%256)/128.
+ *    epi = VITK_EPI_BIAS_RESID_BF16 is the form the forward runs by default: resid_dev and
+ *    out_dev are bf16 (pass the bf16 pointer through the float* parameter; they may alias),
+ *      out bf16 = bf16(acc + bias + resid), stats_out from the fp32 value before rounding;
+ *    xb_out is ignored (the output IS the next GEMM's bf16 operand).
  * NULL c1/stats/xb_out/stats_out reduce to vitk_op_gemm. */
 int vitk_op_gemm_fused(const void* a_bf16_dev, const void* w_bf16_dev, void* out_dev, int M, int N,
                        int K, int epi, const float* bias_dev, const float* c1_dev,
@@ -254,6 +317,12 @@ int vitk_op_layernorm_rows_f32(const float* x_dev, const float* gamma_dev, const
 int vitk_op_chunk_head(const float* x_dev, const float* w1_dev, const float* b1_dev,
                        const float* w2_dev, const float* b2_dev, float* logit_dev, int n, int d,
                        int hidden, void* stream);
+/* Merge of per-shard top-k lists (the row-sharded clip store's exchange step): idx_in / score_in
+ * [n, c] with GLOBAL row ids (-1 = empty slot), c <= 4096 -> the k best per query, better score
+ * first (descending != 0: larger is better), ties to the lower row id -- the kernels' own total
+ * order; missing entries come back as (-1, 0). */
+int vitk_op_merge_topk(const int32_t* idx_in_dev, const float* score_in_dev, int n, int c, int k,
+                       int descending, int32_t* idx_out_dev, float* score_out_dev, void* stream);
 /* im2col + pixel-format conversion: out bf16 [n*(P+1), C*patch*patch] with a zero CLS row. */
 int vitk_op_patchify(const void* pixels_dev, int pixel_format, void* out_bf16_dev, int n, int C,
                      int H, int W, int patch, void* stream);

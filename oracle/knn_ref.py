@@ -138,3 +138,133 @@ def load_banks(directory):
         rows.append(e)
         labels.append(np.full(len(e), li, np.int32))
     return np.concatenate(rows), np.concatenate(labels)
+
+
+# ---------------------------------------------------------------------------------------------
+# Retrievers as CLASSES (B6): RattChunkRetriever(collection, top_k, search_k)(chunk_embs, metadata)
+# restated from retrieval/ratt_chunk_retriever.py:62-159 and FrameRetriever from
+# retrieval/frame_retriever.py:3-72, over a numpy stand-in for the Chroma collection.
+# PINNED: tools/make_golden_retriever.py imports the reference's OWN two classes from
+# /root/reference (they are pure numpy) and runs them on the seeded cases below through the same
+# stand-in collection; tests/golden/retriever_golden.npz holds their outputs, and
+# tests/test_oracle_cpu.py checks these restatements against them.
+# ---------------------------------------------------------------------------------------------
+class ScalarBox:
+    """Stands in for one tf scalar tensor: `.numpy()` returns the value (bytes for strings)."""
+
+    def __init__(self, v):
+        self.v = v
+
+    def numpy(self):
+        return self.v.encode() if isinstance(self.v, str) else self.v
+
+
+def _match(meta, where):
+    for key, cond in where.items():
+        if key == "$and":
+            if not all(_match(meta, w) for w in cond):
+                return False
+        elif isinstance(cond, dict):
+            for op, val in cond.items():
+                x = meta[key]
+                ok = {"$gte": x >= val, "$lte": x <= val, "$ne": x != val, "$eq": x == val}[op]
+                if not ok:
+                    return False
+        elif meta[key] != cond:
+            return False
+    return True
+
+
+class NumpyCollection:
+    """What the two retrievers need of a chromadb Collection ('cosine' space): get(where, include)
+    and query(query_embeddings, n_results, where, include) by float64 brute force."""
+
+    def __init__(self, rows, metadatas):
+        self.rows = np.asarray(rows, np.float32)
+        self.metadatas = list(metadatas)
+
+    def get(self, where=None, include=()):
+        sel = [i for i, m in enumerate(self.metadatas) if where is None or _match(m, where)]
+        return {"embeddings": self.rows[sel], "metadatas": [self.metadatas[i] for i in sel]}
+
+    def query(self, query_embeddings, n_results=10, where=None, include=()):
+        out = []
+        r64 = self.rows.astype(np.float64)
+        rn = r64 / np.linalg.norm(r64, axis=1, keepdims=True)
+        for q in np.asarray(query_embeddings, np.float64):
+            sel = np.array([i for i, m in enumerate(self.metadatas) if where is None or _match(m, where)], np.int64)
+            if len(sel) == 0:
+                out.append(np.zeros((0, self.rows.shape[1]), np.float32))
+                continue
+            d = 1.0 - (rn[sel] @ (q / np.linalg.norm(q)))
+            order = np.argsort(d, kind="stable")[:n_results]
+            out.append(self.rows[sel[order]])
+        return {"embeddings": out}
+
+
+RETRIEVER_CASES = {   # name -> (rows, d, queries, top_k, seed)
+    "small_d64": (600, 64, 24, 5, 11),
+    "clips_d768": (3000, 768, 32, 10, 12),
+    "sparse_d64": (400, 64, 16, 10, 13),     # narrow windows: most queries find < top_k rows
+}
+
+
+def retriever_case(name):
+    """Seeded store + query batch of one golden case: (rows f32 (m,d), metadatas, queries f32
+    (B,d), metadata dict of ScalarBox lists).  Metadata as db_rebuild_chunk.py writes it: vid_num
+    int, side 'left'/'right', t_center / t_norm floats in [0,1]."""
+    m, d, B, top_k, seed = RETRIEVER_CASES[name]
+    rng = np.random.default_rng(seed)
+    centres = rng.standard_normal((8, d)).astype(np.float32)
+    rows = (centres[rng.integers(0, 8, m)] + 0.9 * rng.standard_normal((m, d))).astype(np.float32)
+    metas = [{"vid_num": int(rng.integers(1, 8)), "side": "left" if rng.random() < 0.5 else "right",
+              "t_center": float(rng.random()), "t_norm": float(rng.random()), "clip": f"c{i}"}
+             for i in range(m)]
+    q = (centres[rng.integers(0, 8, B)] + 0.9 * rng.standard_normal((B, d))).astype(np.float32)
+    width = 0.04 if name.startswith("sparse") else 0.5
+    md = {"vid": [ScalarBox(int(rng.integers(1, 8))) for _ in range(B)],
+          "side": [ScalarBox("left" if rng.random() < 0.5 else "right") for _ in range(B)],
+          "t_center": [ScalarBox(float(rng.random())) for _ in range(B)],
+          "t_width": [ScalarBox(float(width * (0.5 + rng.random()))) for _ in range(B)]}
+    return rows, metas, q, md, top_k
+
+
+def ratt_chunk_retriever_restated(collection, chunk_embs, metadata, top_k=10):
+    """retrieval/ratt_chunk_retriever.py:68-159 -> (out (B,top_k,D) f32, idx (B,top_k) i64 row of
+    the collection or -1, gap (B,) f32: the smallest similarity gap that decided the selection)."""
+    q = np.asarray(chunk_embs, np.float32).copy()
+    q /= (np.linalg.norm(q, axis=1, keepdims=True) + 1e-8)
+    B, D = q.shape
+    out = np.zeros((B, top_k, D), np.float32)
+    idx_out = np.full((B, top_k), -1, np.int64)
+    gap = np.full(B, np.inf, np.float32)
+    vids = np.array([int(metadata["vid"][i].numpy()) for i in range(B)], np.int32)
+    sides = [metadata["side"][i].numpy().decode() for i in range(B)]
+    tc = np.array([float(metadata["t_center"][i].numpy()) for i in range(B)], np.float32)
+    tw = np.array([float(metadata["t_width"][i].numpy()) for i in range(B)], np.float32)
+    for side in sorted(set(sides)):
+        idxs = [i for i in range(B) if sides[i] == side]
+        qs, qe = tc[idxs] - tw[idxs] / 2.0, tc[idxs] + tw[idxs] / 2.0
+        g0, g1 = float(np.min(qs)), float(np.max(qe))
+        sel = [i for i, m in enumerate(collection.metadatas)
+               if m["side"] == side and m["t_center"] >= g0 and m["t_center"] <= g1]
+        if not sel:
+            continue
+        cand = collection.rows[sel].astype(np.float32)
+        cand /= (np.linalg.norm(cand, axis=1, keepdims=True) + 1e-8)
+        cvid = np.array([int(collection.metadatas[i]["vid_num"]) for i in sel], np.int32)
+        ct = np.array([float(collection.metadatas[i]["t_center"]) for i in sel], np.float32)
+        sims = q[idxs] @ cand.T
+        for lj, i in enumerate(idxs):
+            valid = np.where((cvid != vids[i]) & (ct >= tc[i] - tw[i] / 2.0) & (ct <= tc[i] + tw[i] / 2.0))[0]
+            if len(valid) == 0:
+                continue
+            vs = sims[lj, valid]
+            order = np.argsort(-vs, kind="stable")
+            chosen = valid[order[:top_k]]
+            out[i, : len(chosen)] = cand[chosen]
+            idx_out[i, : len(chosen)] = np.array(sel)[chosen]
+            sv = vs[order[: top_k + 1]]
+            if len(sv) > 1:
+                gap[i] = np.min(sv[:-1] - sv[1:])
+    return out, idx_out, gap

@@ -107,11 +107,15 @@ def synthetic_frames(name: str, n: int = 1) -> np.ndarray:
 
 # ---------------------------------------------------------------------------------------------
 # cv2.resize(..., interpolation=cv2.INTER_AREA), shrinking (the TF path's front-end:
-# generate_clips_hmm.py:392, chroma.py:204-205, write_embeddings.py:225-226).
-# PARITY UNPINNED: OpenCV is not in this image (`import cv2` fails) and the reference pins no
-# version; restated from OpenCV's published imgproc/resize.cpp: computeResizeAreaTab,
-# ResizeArea_Invoker (float accumulation, saturate_cast<uchar> = round half to even) and, when
-# both scale factors are integers, ResizeAreaFast (integer box sum * (1.f / area)).
+# generate_clips_hmm.py:392, chroma.py:204-205, write_embeddings.py:225-226, loader.py:7).
+# Restated from OpenCV's imgproc/resize.cpp: computeResizeAreaTab, ResizeArea_Invoker (float
+# accumulation, saturate_cast<uchar> = round half to even); when both scale factors are integers
+# ResizeAreaFast (integer box sum * (1.f / area)); and at exactly 2 x 2 its vector form
+# ResizeAreaFastVec, the INTEGER mean (a + b + c + d + 2) >> 2 (round half up).
+# PINNED: tests/test_oracle_cpu.py compares this restatement byte for byte with the live
+# cv2.resize (opencv-python-headless 4.13.0 in this image; the reference pins no version) on 18
+# geometries, and tests/golden/preprocess_cv2_golden.npz holds cv2-produced bytes
+# (tools/make_golden_preprocess.py) that the CUDA kernels are compared with on the GPU box.
 # ---------------------------------------------------------------------------------------------
 def area_tab(ssize, dsize):
     """computeResizeAreaTab: list per destination index of (source index, float32 weight)."""
@@ -144,6 +148,8 @@ def resize_area_u8(img, out_h, out_w):
     if H % out_h == 0 and W % out_w == 0:
         sy, sx = H // out_h, W // out_w
         box = img.reshape(out_h, sy, out_w, sx, C).astype(np.int64).sum((1, 3))
+        if sy == 2 and sx == 2:     # ResizeAreaFastVec: integer mean, round half up
+            return ((box + 2) >> 2).astype(np.uint8)
         val = box.astype(np.float32) * np.float32(1.0 / np.float32(sx * sy))
         return np.clip(np.rint(val), 0, 255).astype(np.uint8)
     xt, yt = area_tab(W, out_w), area_tab(H, out_h)
@@ -163,3 +169,66 @@ def resize_area_u8(img, out_h, out_w):
             acc = t if acc is None else acc + t
         out[dy] = np.clip(np.rint(acc), 0, 255).astype(np.uint8)
     return out
+
+
+# ---------------------------------------------------------------------------------------------
+# cv2.resize(im, (768, 432)) with the DEFAULT interpolation, INTER_LINEAR -- what
+# extract_embeddings feeds the TF model (smarter_generate_clips.py:81).  OpenCV's 8-bit bilinear
+# path (imgproc/resize.cpp: resizeGeneric_ / HResizeLinear / VResizeLinear<uchar,int,short>):
+# two taps per axis, NO antialiasing when shrinking; coefficients are shorts scaled by 2^11
+# (INTER_RESIZE_COEF_BITS), fx = float((dx + .5) * scale - .5) - floor; along x the fraction is
+# zeroed at the borders, along y the ROWS are clamped instead; the horizontal pass keeps
+# S0 * a0 + S1 * a1 as int, the vertical pass is
+#   ((b0 * (S0 >> 4)) >> 16) + ((b1 * (S1 >> 4)) >> 16) + 2) >> 2.
+# (At exactly 2 x 2 shrinking OpenCV switches INTER_LINEAR to INTER_AREA; the fixed-point form
+# above yields the same bytes there -- checked live in the tests.)
+# PINNED like INTER_AREA: byte for byte against the live cv2.resize, shrinking and growing.
+# ---------------------------------------------------------------------------------------------
+def linear_tab(ssize, dsize, clamp_fraction):
+    """Per destination index: (first source index, (a0, a1) int coefficients scaled by 2048)."""
+    scale = 1.0 / (dsize / ssize)          # OpenCV: inv_scale = dsize/ssize; scale = 1./inv_scale
+    idx = np.zeros(dsize, np.int64)
+    coef = np.zeros((dsize, 2), np.int64)
+    for d in range(dsize):
+        f = np.float32((d + 0.5) * scale - 0.5)
+        s = int(np.floor(f))
+        f = np.float32(f - np.float32(s))
+        if clamp_fraction:
+            if s < 0:
+                f, s = np.float32(0), 0
+            if s >= ssize - 1:
+                f, s = np.float32(0), ssize - 1
+        idx[d] = s
+        coef[d, 0] = int(np.rint(np.float32((np.float32(1.0) - f) * np.float32(2048))))
+        coef[d, 1] = int(np.rint(np.float32(f * np.float32(2048))))
+    return idx, coef
+
+
+def resize_linear_u8(img, out_h, out_w):
+    """img (H,W,C) uint8 -> (out_h,out_w,C) uint8, cv2 INTER_LINEAR (any direction)."""
+    img = np.asarray(img, np.uint8)
+    H, W, _ = img.shape
+    xs, xa = linear_tab(W, out_w, True)
+    ys, ya = linear_tab(H, out_h, False)
+    S = img.astype(np.int64)
+    hb = S[:, xs, :] * xa[:, 0][None, :, None] + S[:, np.minimum(xs + 1, W - 1), :] * xa[:, 1][None, :, None]
+    S0, S1 = hb[np.clip(ys, 0, H - 1)], hb[np.clip(ys + 1, 0, H - 1)]
+    b0, b1 = ya[:, 0][:, None, None], ya[:, 1][:, None, None]
+    out = (((b0 * (S0 >> 4)) >> 16) + ((b1 * (S1 >> 4)) >> 16) + 2) >> 2
+    return np.clip(out, 0, 255).astype(np.uint8)
+
+
+# geometries of the cv2-produced golden file (tests/golden/preprocess_cv2_golden.npz): source
+# (h, w) -> the model resolution used with it; frames come from cv2_case_frame (seeded).
+CV2_GOLDEN_CASES = {
+    "hd1080_to_tf": ((1080, 1920), (432, 768)), "hd720_to_tf": ((720, 1280), (432, 768)),
+    "x2_to_tf": ((864, 1536), (432, 768)), "x3_to_tf": ((1296, 2304), (432, 768)),
+    "x2x1_to_tf": ((432, 1536), (432, 768)), "odd_to_tf": ((433, 769), (432, 768)),
+    "wvga_to_tf": ((480, 854), (432, 768)), "x2_to_224": ((448, 448), (224, 224)),
+    "x5_to_224": ((1120, 1120), (224, 224)), "odd_to_224": ((1000, 225), (224, 224)),
+}
+
+
+def cv2_case_frame(name):
+    (h, w), _ = CV2_GOLDEN_CASES[name]
+    return np.random.default_rng(sum(map(ord, name)) + 17).integers(0, 256, (h, w, 3), dtype=np.uint8)

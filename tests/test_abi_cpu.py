@@ -69,8 +69,61 @@ def test_load_label_banks_accepts_reference_layout(golden_dir):
     assert ids[0].startswith("left:") and ids[-1].startswith("none:")
 
 
-def test_vote_helpers_follow_reference():
-    assert v.determine_class_pass2([10, 10, 5])["dir"] == "left"
-    assert v.determine_class_pass1([19, 4, 2])["dir"] == "pass2"
-    r = v.determine_class_pass1([21, 2, 2])
+def test_vote_helpers_follow_reference(golden_dir):
+    """determine_class_pass1 / pass2 keep the reference's call (ids, metadatas, distances) and
+    return what the reference's OWN functions returned (chroma.py:36-71,102-134 cut out with ast
+    and executed: tools/make_golden_determine_class.py), literal threshold 20 included."""
+    import json
+    z = json.load(open(os.path.join(golden_dir, "determine_class_pass12_golden.json")))
+    assert len(z["cases"]) == 96
+    for c in z["cases"]:
+        metas = [{"label": lab} for lab in c["labels"]]
+        ids = [f"id{j}" for j in range(len(metas))]
+        for fn, key in ((v.determine_class_pass1, "pass1"), (v.determine_class_pass2, "pass2")):
+            got = fn(ids, metas, c["distances"])
+            assert got["dir"] == c[key]["dir"]
+            assert ("probs" in got) == ("probs" in c[key])
+            if "probs" in got:
+                assert np.array_equal(np.asarray(got["probs"]), np.asarray(c[key]["probs"]))
+    assert v.vote_from_counts([10, 10, 5])["dir"] == "left"            # first max wins
+    assert v.vote_from_counts([19, 4, 2], threshold=20)["dir"] == "pass2"
+    r = v.vote_from_counts([21, 2, 2], threshold=20)
     assert r["dir"] == "left" and abs(r["probs"].sum() - 1) < 1e-12
+
+
+def test_collection_where_clauses_vectorised_equal_the_per_row_form():
+    """BankCollection.where_mask (columnar, what query(where=...) uploads) against match_where
+    row by row, on the clause shapes the reference sends (frame_retriever.py:44-51,
+    ratt_chunk_retriever.py:99-105, db_rebuild.py:121) -- host logic, no GPU."""
+    rng = np.random.default_rng(3)
+    metas = []
+    for i in range(500):
+        m = {"vid_num": int(rng.integers(1, 6)), "side": "left" if rng.random() < 0.5 else "right",
+             "t_norm": float(rng.random()), "label": ["left", "right", "none"][i % 3]}
+        if i % 11 == 0:
+            del m["t_norm"]                      # a missing key never matches
+        if i % 13 == 0:
+            m["video"] = f"vid{i % 4}"
+        metas.append(m)
+    col = object.__new__(v.BankCollection)
+    col.metadatas, col._n, col._cols, col._codes = metas, len(metas), {}, {}
+    clauses = [
+        {"side": "left"},
+        {"vid_num": {"$ne": 3}},
+        {"$and": [{"vid_num": {"$ne": 2}}, {"side": "right"}, {"t_norm": {"$gte": 0.25}}, {"t_norm": {"$lte": 0.75}}]},
+        {"$or": [{"vid_num": 1}, {"t_norm": {"$lt": 0.1}}]},
+        {"video": "vid1"},
+        {"vid_num": {"$in": [1, 4]}},
+        {"label": {"$nin": ["none"]}},
+        {"$and": [{"side": "left"}, {"$or": [{"vid_num": {"$gt": 3}}, {"t_norm": {"$gte": 0.9}}]}]},
+    ]
+    for w in clauses:
+        want = np.array([v.match_where(m, w) for m in metas], np.uint8)
+        assert np.array_equal(col.where_mask(w), want), w
+    assert col.where_mask(None) is None
+    assert col.code("side", "left") != col.code("side", "right") and col.code("vid_num", 7) == 7
+
+
+def test_knn_limits_are_stated_not_silent():
+    from vit_research_b200 import _lib
+    assert _lib.KNN_MAX_K == 1024 and _lib.STREAM_MAX_K == 64

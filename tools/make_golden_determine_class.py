@@ -54,5 +54,39 @@ def main():
     print("wrote", path, len(out), "cases;", sum(len(o["result"]) == 3 for o in out), "confident")
 
 
+def main_pass12():
+    """determine_class_pass1 / determine_class_pass2 (chroma.py:36-71,102-134) cut out of the
+    reference script the same way and run on seeded neighbour lists (k = 25 like chroma.py:27 and
+    a few other k): the dir and the temp_smax probabilities they return."""
+    src = "/root/reference/nba_proj/chroma.py"
+    tree = ast.parse(open(src).read())
+    want = {"softmax", "temp_smax", "determine_class_pass1", "determine_class_pass2"}
+    fns = [n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name in want]
+    g = {"np": np}
+    exec(compile(ast.Module(body=fns, type_ignores=[]), src, "exec"), g)
+    rng = np.random.default_rng(2025)
+    cases = []
+    for c in range(96):
+        k = [25, 25, 25, 5, 50, 30][c % 6]
+        p = rng.dirichlet([0.4, 0.4, 0.25])
+        if c % 5 == 0:
+            p = np.array([0.5, 0.5, 0.0]) if c % 10 == 0 else np.array([0.0, 0.5, 0.5])   # ties
+        labs = [["left", "right", "none", "weird"][min(int(x), 3)] for x in rng.choice(3, k, p=p)]
+        if c % 7 == 0:
+            labs[0] = "weird"          # any other label counts as none
+        metas = [{"label": lab} for lab in labs]
+        ids = [f"id{j}" for j in range(k)]
+        dist = [float(x) for x in np.sort(rng.random(k) * 100)]
+        with contextlib.redirect_stdout(io.StringIO()):
+            r1 = g["determine_class_pass1"](ids, metas, dist)
+            r2 = g["determine_class_pass2"](ids, metas, dist)
+        enc = lambda r: {"dir": r["dir"], **({"probs": [float(x) for x in r["probs"]]} if "probs" in r else {})}
+        cases.append({"labels": labs, "distances": dist, "pass1": enc(r1), "pass2": enc(r2)})
+    path = os.path.join(ROOT, "tests", "golden", "determine_class_pass12_golden.json")
+    json.dump({"source": "chroma.py:28-71,102-134 executed as written", "cases": cases}, open(path, "w"))
+    print("wrote", path, len(cases), "cases;", sum(c["pass1"]["dir"] == "pass2" for c in cases), "deferred by pass 1")
+
+
 if __name__ == "__main__":
     main()
+    main_pass12()

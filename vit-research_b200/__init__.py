@@ -7,9 +7,10 @@ from ._lib import VitkError, build, load  # noqa: F401
 from .embed import (ViTEmbedder, ViTGeometry, extract_embeddings, hf_vit_embed_batch,  # noqa: F401
                     install, random_init_state_dict)
 from . import knn  # noqa: F401
-from .knn import (BankCollection, BankIndex, RattChunkRetriever, determine_class_pass1,  # noqa: F401
-                  determine_class_pass2, load_label_banks, temp_smax, LABEL_NAMES,
-                  determine_class, classify_stream_with_upserts, match_where, one_hot_metadata)
+from .knn import (BankClient, BankCollection, BankIndex, FrameRetriever, RattChunkRetriever,  # noqa: F401
+                  determine_class_pass1, determine_class_pass2, load_label_banks, temp_smax,
+                  LABEL_NAMES, determine_class, classify_stream_with_upserts, match_where,
+                  one_hot_metadata, vote_from_counts)
 from . import hmm as hmm_module  # noqa: F401,E402
 from .hmm import hmm, viterbi_from_counts, viterbi_from_probs  # noqa: F401,E402
 from . import store  # noqa: F401,E402

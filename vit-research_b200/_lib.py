@@ -38,10 +38,23 @@ class VitkConfig(C.Structure):
     ]
 
 
+class VitkRowFilter(C.Structure):
+    """vitk_row_filter (include/vitk.h): per-query row predicate of vitk_knn_vote_filtered."""
+    _fields_ = [
+        ("ne_col", C.c_void_p), ("q_ne", C.c_void_p), ("eq_col", C.c_void_p), ("q_eq", C.c_void_p),
+        ("rng_col", C.c_void_p), ("q_lo", C.c_void_p), ("q_hi", C.c_void_p),
+        ("q_lo2", C.c_void_p), ("q_hi2", C.c_void_p), ("rng_round_f32", C.c_int32),
+    ]
+
+
 PIX_F32_NCHW, PIX_BF16_NCHW, PIX_U8_NHWC = 0, 1, 2
 METRIC_COSINE, METRIC_L2 = 0, 1
+RESIZE_BILINEAR_AA, RESIZE_AREA, RESIZE_LINEAR = 0, 1, 2
 EPI_BIAS_BF16, EPI_BIAS_GELU_BF16, EPI_BIAS_GELUT_BF16 = 0, 1, 2
 EPI_BIAS_RESID_F32, EPI_TABLE_F32, EPI_F32 = 3, 4, 5
+EPI_BIAS_RESID_BF16 = 7
+KNN_MAX_K = 1024          # vitk_knn_vote*: 1 <= k <= 1024
+STREAM_MAX_K = 64         # vitk_stream_submit* / vitk_embed_vote_host_u8 (the vote: k = 5 / 25 / 50)
 
 # name -> (restype, argtypes); every symbol include/vitk.h declares
 _vp, _i, _f = C.c_void_p, C.c_int, C.c_float
@@ -58,6 +71,14 @@ SIGNATURES = {
     "vitk_embed_vote_host_u8": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "vitk_stream_submit": (_i, [_vp, _i, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "vitk_stream_wait": (_i, [_vp, _i]),
+    "vitk_stream_submit_raw": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
+    "vitk_preprocess_resize_linear_u8": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),
+    "vitk_knn_vote_filtered": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, C.POINTER(VitkRowFilter), _vp, _vp, _vp, _vp, _vp]),
+    "vitk_bank_new": (_i, [_vp]),
+    "vitk_bank_select": (_i, [_vp, _i]),
+    "vitk_bank_current": (_i, [_vp]),
+    "vitk_bank_free": (_i, [_vp, _i]),
+    "vitk_op_merge_topk": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp]),
     "vitk_preprocess_resize_u8": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),
     "vitk_embed_resize_host_u8": (_i, [_vp, _vp, _i, _i, _i, _vp, _i]),
     "vitk_bank_set": (_i, [_vp, _vp, _i, _i, _vp, _i, _i]),

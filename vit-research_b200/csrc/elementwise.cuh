@@ -146,19 +146,25 @@ rowstats_cast_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ xb
 // The other 196 rows of the final LayerNorm are never read by the reference and are skipped.
 template <int VEC>
 __global__ void __launch_bounds__(128)
-cls_tail_kernel(const float* __restrict__ resid, const float* __restrict__ gamma,
+cls_tail_kernel(const float* __restrict__ resid, const __nv_bfloat16* __restrict__ resid_bf16,
+                const float* __restrict__ gamma,
                 const float* __restrict__ beta, float* __restrict__ out_f32,
                 __nv_bfloat16* __restrict__ out_bf16, int n, int tokens, float eps, int l2norm) {
   constexpr int D = 128 * VEC;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (warp >= n) return;
-  const float4* xr = reinterpret_cast<const float4*>(resid + (size_t)warp * tokens * D);
   float4 v[VEC];
   float s = 0.f;
 #pragma unroll
   for (int j = 0; j < VEC; ++j) {
-    v[j] = xr[lane + 32 * j];
+    if (resid_bf16 != nullptr) {  // bf16 residual stream (the default): 4 elements = 8 bytes
+      const uint2 u = reinterpret_cast<const uint2*>(resid_bf16 + (size_t)warp * tokens * D)[lane + 32 * j];
+      v[j] = make_float4(__uint_as_float(u.x << 16), __uint_as_float(u.x & 0xffff0000u),
+                         __uint_as_float(u.y << 16), __uint_as_float(u.y & 0xffff0000u));
+    } else {
+      v[j] = reinterpret_cast<const float4*>(resid + (size_t)warp * tokens * D)[lane + 32 * j];
+    }
     s += (v[j].x + v[j].y) + (v[j].z + v[j].w);
   }
   const float mean = warp_sum(s) * (1.0f / D);

@@ -41,7 +41,35 @@ enum GemmEpilogue : int {
   EPI_THRESH_POOL = 6,     // no matrix out: (key, column) of every score that beats its row's
                            //   running threshold is appended to that row's candidate pool
                            //   (large-store top-k: the score matrix never exists — knn.cuh)
+  EPI_BIAS_RESID_BF16 = 7, // out bf16 = acc + bias[n] + resid[m,n], resid bf16 (normally aliasing
+                           //   out: the residual stream IS the next GEMM's A operand); optional
+                           //   per-row partial (sum, sumsq) of the fp32 value before rounding
 };
+
+// Per-query row predicate of a filtered k-NN query (the reference filters candidates per query:
+// ratt_chunk_retriever.py:130-134 `(cand_vids != vid) & (t_center in [q_start, q_end])`,
+// frame_retriever.py:44-51 `where={$and: [vid_num $ne, side, t_norm $gte/$lte]}`).  Columns are
+// indexed by bank row, q_* by query; a null column switches its clause off.
+struct KnnFilter {
+  const int32_t* ne_col; const int32_t* q_ne;   // pass iff ne_col[row] != q_ne[query]
+  const int32_t* eq_col; const int32_t* q_eq;   // pass iff eq_col[row] == q_eq[query]
+  const double* rng_col;                        // pass iff q_lo <= x <= q_hi, x = rng_col[row],
+  const double* q_lo; const double* q_hi;       //   rounded to float first when rng_f32 != 0
+  const double* q_lo2; const double* q_hi2;     // optional second window on the un-rounded value
+  int rng_f32;
+  int active;
+};
+__device__ __forceinline__ bool knn_filter_pass(const KnnFilter& f, int query, int row) {
+  if (f.ne_col != nullptr && __ldg(f.ne_col + row) == __ldg(f.q_ne + query)) return false;
+  if (f.eq_col != nullptr && __ldg(f.eq_col + row) != __ldg(f.q_eq + query)) return false;
+  if (f.rng_col != nullptr) {
+    const double raw = __ldg(f.rng_col + row);
+    const double x = f.rng_f32 ? (double)(float)raw : raw;
+    if (!(x >= __ldg(f.q_lo + query) && x <= __ldg(f.q_hi + query))) return false;
+    if (f.q_lo2 != nullptr && !(raw >= __ldg(f.q_lo2 + query) && raw <= __ldg(f.q_hi2 + query))) return false;
+  }
+  return true;
+}
 
 struct GemmParams {
   int M, N, K;
@@ -69,6 +97,7 @@ struct GemmParams {
   int pool_l2;                            // 1: squared-L2 key 2v - bias[n]; 2: v - bias[n] (row penalty)
   int pool_direct;                        // 1: pools are empty, N <= pool_cap: entry n goes to
                                           //    slot n of its row's pool (no atomics, no filter)
+  KnnFilter filt;                         // EPI_THRESH_POOL: per-query row predicate (active != 0)
 };
 
 constexpr int GEMM_BM = 128;
@@ -110,8 +139,9 @@ template <int EPI>
 struct EpiTraits {
   static constexpr bool kOutBf16 = (EPI == EPI_BIAS_BF16 || EPI == EPI_BIAS_GELU_BF16 ||
                                     EPI == EPI_BIAS_GELUT_BF16);
-  static constexpr bool kUsesVec = kOutBf16 || EPI == EPI_BIAS_RESID_F32 || EPI == EPI_THRESH_POOL;
-  static constexpr int kChunkCols = kOutBf16 ? 64 : 32;  // 128 B of output per row per chunk
+  static constexpr bool kResid = (EPI == EPI_BIAS_RESID_F32 || EPI == EPI_BIAS_RESID_BF16);
+  static constexpr bool kUsesVec = kOutBf16 || kResid || EPI == EPI_THRESH_POOL;
+  static constexpr int kChunkCols = (kOutBf16 || EPI == EPI_BIAS_RESID_BF16) ? 64 : 32;  // 128 B of output per row per chunk
 };
 
 __device__ __forceinline__ uint32_t dynamic_smem_size() {
@@ -169,7 +199,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     tma_prefetch_desc(&tmC);
-    if constexpr (EPI == EPI_BIAS_RESID_F32) tma_prefetch_desc(&tmR);
+    if constexpr (EpiTraits<EPI>::kResid) tma_prefetch_desc(&tmR);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < kStages; ++i) {
@@ -286,7 +316,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         tma_load_2d(swarp + b_ * GEMM_STAGING_BYTES, &tmR, &rbar[b_], c0_, r0_);
       }
     };
-    if constexpr (EPI == EPI_BIAS_RESID_F32) {
+    if constexpr (EpiTraits<EPI>::kResid) {
       if (lane == 0) resid_request(first_unit, 0, 0);
     }
     for (int tile = first_unit; tile < num_tiles; tile += unit_stride) {
@@ -424,9 +454,12 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               if (row < p.M) {
 #pragma unroll
                 for (int j = 0; j < 32; ++j)
-                  if (col0 + j < p.N && col0 + j < p.pool_cap)
+                  if (col0 + j < p.N && col0 + j < p.pool_cap) {
+                    // a row the query's predicate rejects leaves an EMPTY slot (key bits 0)
+                    const bool ok = !p.filt.active || knn_filter_pass(p.filt, row, p.col_base + col0 + j);
                     p.pool[(size_t)row * p.pool_cap + col0 + j] = make_uint2(
-                        static_cast<uint32_t>(p.col_base + col0 + j), float_order_bits(v[j]));
+                        static_cast<uint32_t>(p.col_base + col0 + j), ok ? float_order_bits(v[j]) : 0u);
+                  }
               }
             } else {
               // branch-free common case: one float compare per score against the key part of
@@ -441,7 +474,8 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     const uint32_t kb = float_order_bits(v[j]);
                     const uint32_t bi = static_cast<uint32_t>(p.col_base + col0 + j);
                     const unsigned long long comp = (static_cast<unsigned long long>(kb) << 32) | (~bi);
-                    if (comp > pool_t) {
+                    // the predicate runs only for the rare score that beats the threshold
+                    if (comp > pool_t && (!p.filt.active || knn_filter_pass(p.filt, row, (int)bi))) {
                       const int pos = atomicAdd(p.pool_n + row, 1);
                       if (pos < p.pool_cap) p.pool[(size_t)row * p.pool_cap + pos] = make_uint2(bi, kb);
                     }
@@ -474,6 +508,55 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               float4 o = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
               *reinterpret_cast<float4*>(sbuf + lane * 128 + ((j ^ (lane & 7)) << 4)) = o;
             }
+          }
+        } else if constexpr (EPI == EPI_BIAS_RESID_BF16) {
+          // bf16 residual stream: TMA-load the 32 x 64 bf16 residual tile into the staging buffer,
+          // add accumulator + bias in fp32, round once, store back in place and TMA-store it.  The
+          // output IS the next GEMM's A operand, so no separate bf16 copy is written (the copy
+          // was the expensive part of the fp32 form, tools/dev_proj_probe.py).
+          if constexpr (NBUF == 2) {
+            if (lane == 0) {
+              tma_store_wait_read<0>();
+              if (c + 1 < kChunks) resid_request(tile, c + 1, b ^ 1u);
+              else resid_request(tile + unit_stride, 0, b ^ 1u);
+            }
+          }
+          uint32_t r0[32], r1[32];
+          tmem_ld_32x32b_x32(t_row + c * CH, r0);
+          tmem_ld_32x32b_x32(t_row + c * CH + 32, r1);
+          tmem_ld_wait();
+          if (live) {
+            mbar_wait(&rbar[b], (rphase >> b) & 1u);
+            rphase ^= 1u << b;
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t* acc8 = j < 4 ? r0 + 8 * j : r1 + 8 * (j - 4);
+            const float4 b0 = *reinterpret_cast<const float4*>(sVec + BN + lcol0 + 8 * j);
+            const float4 b1 = *reinterpret_cast<const float4*>(sVec + BN + lcol0 + 8 * j + 4);
+            uint4* cell = reinterpret_cast<uint4*>(sbuf + lane * 128 + ((j ^ (lane & 7)) << 4));
+            uint4 x = make_uint4(0u, 0u, 0u, 0u);
+            if (live) x = *cell;
+            float y[8];
+            y[0] = __uint_as_float(acc8[0]) + (__uint_as_float(x.x << 16) + b0.x);
+            y[1] = __uint_as_float(acc8[1]) + (__uint_as_float(x.x & 0xffff0000u) + b0.y);
+            y[2] = __uint_as_float(acc8[2]) + (__uint_as_float(x.y << 16) + b0.z);
+            y[3] = __uint_as_float(acc8[3]) + (__uint_as_float(x.y & 0xffff0000u) + b0.w);
+            y[4] = __uint_as_float(acc8[4]) + (__uint_as_float(x.z << 16) + b1.x);
+            y[5] = __uint_as_float(acc8[5]) + (__uint_as_float(x.z & 0xffff0000u) + b1.y);
+            y[6] = __uint_as_float(acc8[6]) + (__uint_as_float(x.w << 16) + b1.z);
+            y[7] = __uint_as_float(acc8[7]) + (__uint_as_float(x.w & 0xffff0000u) + b1.w);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              st_s += y[i];
+              st_ss = fmaf(y[i], y[i], st_ss);
+            }
+            uint4 o;
+            o.x = pack_bf16x2(y[0], y[1]);
+            o.y = pack_bf16x2(y[2], y[3]);
+            o.z = pack_bf16x2(y[4], y[5]);
+            o.w = pack_bf16x2(y[6], y[7]);
+            *cell = o;
           }
         } else {
           uint32_t r0[32], r1[32];
@@ -534,7 +617,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         if (lane == 0) {
           if (live) tma_store_2d(&tmC, sbuf, col0, row0);
           tma_store_commit();
-          if constexpr (EPI == EPI_BIAS_RESID_F32 && NBUF == 1) {
+          if constexpr (EpiTraits<EPI>::kResid && NBUF == 1) {
             // single staging tile: the next residual chunk can only be requested once this
             // store has drained it
             tma_store_wait_read<0>();
@@ -543,7 +626,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           }
         }
       }
-      if constexpr (EPI == EPI_BIAS_RESID_F32) {
+      if constexpr (EpiTraits<EPI>::kResid) {
         if (p.stats_out != nullptr && row < p.M) {
           float2* so = reinterpret_cast<float2*>(p.stats_out + (size_t)row * p.stats_out_stride);
           so[2 * n_blk + half] = make_float2(st_s, st_ss);

@@ -11,12 +11,15 @@
 // bf16 similarities alone permute near-ties (SURVEY.md §7 "Top-k index exactness").
 #pragma once
 #include "vitk_common.cuh"
+#include "gemm_sm100.cuh"  // KnnFilter
 
 namespace vitk {
 
 enum KnnMetric : int { METRIC_COSINE = 0, METRIC_L2 = 1 };
 
-constexpr int KNN_MAX_CAND = 128;   // kc <= 128 (4 per lane)
+constexpr int KNN_MAX_CAND = 128;   // kc <= 128 (4 per lane): warp-extraction re-rank
+constexpr int KNN_MAX_K = 1024;     // n_results of the clip-store queries reach 750 (config.py:10-11)
+constexpr int KNN_SORT_MAX_CAND = 2048;  // kc of the sort-based re-rank (k + k/4 + 32 <= 1312)
 constexpr int KNN_MAX_CLASSES = 8;
 
 // f32 rows -> bf16 rows (+ optional x / (||x|| + 1e-8), the reference's query normalisation,
@@ -107,7 +110,7 @@ template <int KPL>
 __global__ void __launch_bounds__(128)
 knn_candidates_reg_kernel(const float* __restrict__ scores, int ld,
                           const float* __restrict__ bank_sqnorm, int nq, int m, int kc, int metric,
-                          int32_t* __restrict__ cand, const float* __restrict__ pen = nullptr) {
+                          int32_t* __restrict__ cand, const float* __restrict__ pen, const KnnFilter filt) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (warp >= nq) return;
@@ -122,6 +125,8 @@ knn_candidates_reg_kernel(const float* __restrict__ scores, int ld,
       // `pen` (masked query): ||b||^2 (L2) or 0 (cosine) for the rows in play, +inf otherwise
       if (pen != nullptr) s = (metric == METRIC_L2 ? 2.0f * s : s) - __ldg(pen + i);
       else if (metric == METRIC_L2) s = 2.0f * s - __ldg(bank_sqnorm + i);
+      // per-query predicate (ratt_chunk_retriever.py:130-134): a rejected row sinks to the bottom
+      if (filt.active && !knn_filter_pass(filt, warp, i)) s = -INFINITY;
     }
     key[j] = i < m ? float_order_bits(s) : 0u;
   }
@@ -168,18 +173,24 @@ knn_candidates_reg_kernel(const float* __restrict__ scores, int ld,
 // how the atomics interleave.  A pool that overflows is detected on the host after the last
 // stage and that stage is redone in quarters (a stage of <= cap - kc rows cannot overflow).
 // ---------------------------------------------------------------------------------------------
-constexpr int KNN_POOL_CAP = 2048;  // pool entries per query (64 per lane)
+constexpr int KNN_POOL_KPL = 16;     // pool entries per thread of the select kernel
+constexpr int KNN_POOL_CAP = 2048;   // pool entries per query, kc <= 448 (128 select threads)
+constexpr int KNN_POOL_CAP_BIG = 8192;  // larger k (n_results 100-750): 512 select threads
 
-// Sum over the 128 threads of a CTA (4 warps); `buf` = 4 ints of shared memory that no thread
-// still reads from an earlier call (callers alternate two buffers).
-__device__ __forceinline__ int block4_sum(int v, int* buf) {
+// Sum over the NW warps of a CTA; `buf` = NW ints of shared memory that no thread still reads
+// from an earlier call (callers alternate two buffers).
+template <int NW>
+__device__ __forceinline__ int block_sum(int v, int* buf) {
   v = __reduce_add_sync(0xffffffffu, v);
   if ((threadIdx.x & 31) == 0) buf[threadIdx.x >> 5] = v;
   __syncthreads();
-  return (buf[0] + buf[1]) + (buf[2] + buf[3]);
+  int t = 0;
+#pragma unroll
+  for (int i = 0; i < NW; ++i) t += buf[i];
+  return t;
 }
 
-// One CTA (4 warps) per query.  Loads the pool into registers (16 entries per thread), finds
+// One CTA (THREADS / 32 warps) per query; pool capacity = 16 * THREADS.  Loads the pool into registers (16 entries per thread), finds
 // the kc-th largest composite — a 32-step bitwise binary search on the key bits (compare +
 // block-wide count), and only when several rows share the kc-th key a second search on ~row
 // among them — compacts the winners to the front of the pool, publishes the new threshold and,
@@ -187,31 +198,34 @@ __device__ __forceinline__ int block4_sum(int v, int* buf) {
 // pool was filled positionally by the first stage (entry i = row i of the stage) and holds
 // exactly that many entries.  Rows in [ex_lo, ex_hi) are dropped first (a stage being redone
 // after an overflow).  overflow[0] is set when a pool had been truncated.
-__global__ void __launch_bounds__(128)
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS)
 knn_pool_select_kernel(uint2* __restrict__ pool, int* __restrict__ pool_n,
                        unsigned long long* __restrict__ thresh, int nq, int kc, int direct_rows,
                        int ex_lo, int ex_hi, int32_t* __restrict__ cand, int* __restrict__ overflow) {
-  constexpr int KPL = KNN_POOL_CAP / 128;
-  __shared__ int s_buf[2][4];
-  __shared__ uint32_t s_min[4];
+  constexpr int KPL = KNN_POOL_KPL;
+  constexpr int NW = THREADS / 32;
+  constexpr int CAP = KPL * THREADS;
+  __shared__ int s_buf[2][NW];
+  __shared__ uint32_t s_min[NW];
   const int qi = blockIdx.x;
   const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
   int count = direct_rows >= 0 ? direct_rows : pool_n[qi];
-  if (count > KNN_POOL_CAP) {
+  if (count > CAP) {
     if (tid == 0) atomicExch(overflow, 1);
-    count = KNN_POOL_CAP;
+    count = CAP;
   }
-  uint2* row = pool + (size_t)qi * KNN_POOL_CAP;
+  uint2* row = pool + (size_t)qi * CAP;
   uint32_t hi[KPL], lo[KPL];  // key bits | ~row; hi == 0 marks an empty slot
 #pragma unroll
   for (int j = 0; j < KPL; ++j) {
-    const int i = tid + 128 * j;
+    const int i = tid + THREADS * j;
     hi[j] = 0u;
     lo[j] = 0u;
     if (i < count) {
       const uint2 e = row[i];
       const bool excluded = (int)e.x >= ex_lo && (int)e.x < ex_hi;
-      if (!excluded) { hi[j] = e.y; lo[j] = ~e.x; }
+      if (!excluded && e.y != 0u) { hi[j] = e.y; lo[j] = ~e.x; }
     }
   }
   uint32_t t = 0u;
@@ -222,7 +236,7 @@ knn_pool_select_kernel(uint2* __restrict__ pool, int* __restrict__ pool_n,
     int c = 0;
 #pragma unroll
     for (int j = 0; j < KPL; ++j) c += hi[j] >= tt ? 1 : 0;
-    if (block4_sum(c, s_buf[flip]) >= kc) t = tt;
+    if (block_sum<NW>(c, s_buf[flip]) >= kc) t = tt;
   }
   // t == the kc-th largest key (with multiplicity), or 0 when fewer than kc entries exist
   uint32_t t_lo = 0u;
@@ -234,14 +248,16 @@ knn_pool_select_kernel(uint2* __restrict__ pool, int* __restrict__ pool_n,
       gt += hi[j] > t ? 1 : 0;
       if (hi[j] == t) { ++eq; lo_min = min(lo_min, lo[j]); }
     }
-    gt = block4_sum(gt, s_buf[flip]); flip ^= 1;
-    eq = block4_sum(eq, s_buf[flip]); flip ^= 1;
+    gt = block_sum<NW>(gt, s_buf[flip]); flip ^= 1;
+    eq = block_sum<NW>(eq, s_buf[flip]); flip ^= 1;
     const int need = kc - gt;  // >= 1 rows with key == t are wanted, lowest rows first
     if (eq == need) {
       lo_min = __reduce_min_sync(0xffffffffu, lo_min);
       if (lane == 0) s_min[w] = lo_min;
       __syncthreads();
-      t_lo = min(min(s_min[0], s_min[1]), min(s_min[2], s_min[3]));
+      t_lo = s_min[0];
+#pragma unroll
+      for (int i = 1; i < NW; ++i) t_lo = min(t_lo, s_min[i]);
     } else {
 #pragma unroll 1
       for (int bit = 31; bit >= 0; --bit, flip ^= 1) {
@@ -249,7 +265,7 @@ knn_pool_select_kernel(uint2* __restrict__ pool, int* __restrict__ pool_n,
         int c = 0;
 #pragma unroll
         for (int j = 0; j < KPL; ++j) c += (hi[j] == t && lo[j] >= tt) ? 1 : 0;
-        if (block4_sum(c, s_buf[flip]) >= need) t_lo = tt;
+        if (block_sum<NW>(c, s_buf[flip]) >= need) t_lo = tt;
       }
     }
   }
@@ -259,7 +275,7 @@ knn_pool_select_kernel(uint2* __restrict__ pool, int* __restrict__ pool_n,
 #pragma unroll
   for (int j = 0; j < KPL; ++j)
     mine += (hi[j] != 0u && (hi[j] > t || (hi[j] == t && lo[j] >= t_lo))) ? 1 : 0;
-  const int total = block4_sum(mine, s_buf[flip]);
+  const int total = block_sum<NW>(mine, s_buf[flip]);
   int base = 0;
   for (int i = 0; i < w; ++i) base += s_buf[flip][i];
   const uint32_t lt_mask = (1u << lane) - 1u;
@@ -276,7 +292,7 @@ knn_pool_select_kernel(uint2* __restrict__ pool, int* __restrict__ pool_n,
     base += __popc(b);
   }
   if (cand != nullptr)
-    for (int i = total + tid; i < kc; i += 128) cand[(size_t)qi * kc + i] = -1;
+    for (int i = total + tid; i < kc; i += THREADS) cand[(size_t)qi * kc + i] = -1;
   if (tid == 0) {
     pool_n[qi] = total;
     // the old threshold may be the composite of a row that was just excluded: step below it so
@@ -288,47 +304,37 @@ knn_pool_select_kernel(uint2* __restrict__ pool, int* __restrict__ pool_n,
   }
 }
 
-// Exact fp32 re-rank of the kc candidates, ordered top-k, vote.  One CTA (4 warps) per query.
+// Exact fp32 score of candidates [0, kc) of one query -> s_key / s_idx (key: larger == better;
+// dropped candidates get (-inf, INT_MAX)).
 //   cosine: score = <q, b>            (rows unit-normalised upstream), descending
 //   L2    : score = sum (q-b)^2       (Chroma 'l2' space returns squared L2), ascending
-// Each warp takes every 4th candidate, four at a time: the 32 lanes read the bank row coalesced
-// (float4 per lane per 128 columns), multiply against the query staged in shared memory and
-// reduce with xor-shuffles (every lane ends with the same, order-deterministic sum).  Warp 0
-// then extracts the k best in (score, row) order and votes.
-// Outputs: idx[nq,k], score[nq,k] in result order; counts[nq,n_classes]; label = first argmax
-// of counts (np.argmax semantics, chroma.py:128: ties -> left > right > none).
-__global__ void __launch_bounds__(128)
-knn_rerank_vote_kernel(const float* __restrict__ q, const float* __restrict__ bank,
-                       const int32_t* __restrict__ labels, const int32_t* __restrict__ cand,
-                       int nq, int m, int d, int kc, int k, int metric, int n_classes,
-                       int32_t* __restrict__ idx_out, float* __restrict__ score_out,
-                       int32_t* __restrict__ label_out, int32_t* __restrict__ counts_out,
-                       const uint8_t* __restrict__ row_mask = nullptr) {
-  extern __shared__ float knn_q_smem[];  // [d] query row
-  __shared__ float s_key[KNN_MAX_CAND];
-  __shared__ int s_idx[KNN_MAX_CAND];
-  const int qi = blockIdx.x;
+// Each warp takes every NWARPS-th group of four candidates: the 32 lanes read the bank rows
+// coalesced (float4 per lane per 128 columns), multiply against the query staged in shared memory
+// and reduce with xor-shuffles (every lane ends with the same, order-deterministic sum).  Rows a
+// `where=` mask or the per-query predicate rejects are dropped here, so they can never be returned.
+template <int NWARPS>
+__device__ __forceinline__ void knn_score_candidates(const float* q_smem, const float* __restrict__ bank,
+                                                     const int32_t* __restrict__ cand_row, int qi, int m, int d,
+                                                     int kc, int metric, const uint8_t* __restrict__ row_mask,
+                                                     const KnnFilter& filt, float* s_key, int* s_idx) {
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (qi >= nq) return;
-  for (int i = threadIdx.x * 4; i < d; i += 128 * 4)
-    *reinterpret_cast<float4*>(knn_q_smem + i) = *reinterpret_cast<const float4*>(q + (size_t)qi * d + i);
-  __syncthreads();
-  for (int c0 = w * 4; c0 < kc; c0 += 16) {
+  for (int c0 = w * 4; c0 < kc; c0 += 4 * NWARPS) {
     const float* br[4];
     int bi[4];
     float acc[4];
 #pragma unroll
     for (int s = 0; s < 4; ++s) {
       const int c = c0 + s;
-      int b = c < kc ? __ldg(cand + (size_t)qi * kc + c) : -1;
+      int b = c < kc ? __ldg(cand_row + c) : -1;
       if (b < 0 || b >= m) b = -1;
       if (b >= 0 && row_mask != nullptr && !__ldg(row_mask + b)) b = -1;  // filtered out (where=)
+      if (b >= 0 && filt.active && !knn_filter_pass(filt, qi, b)) b = -1;  // per-query predicate
       bi[s] = b;
       br[s] = bank + (size_t)(b < 0 ? 0 : b) * d;
       acc[s] = 0.f;
     }
     for (int i = lane * 4; i < d; i += 128) {
-      const float4 a = *reinterpret_cast<const float4*>(knn_q_smem + i);
+      const float4 a = *reinterpret_cast<const float4*>(q_smem + i);
 #pragma unroll
       for (int s = 0; s < 4; ++s) {
         const float4 b = __ldg(reinterpret_cast<const float4*>(br[s] + i));
@@ -349,6 +355,31 @@ knn_rerank_vote_kernel(const float* __restrict__ q, const float* __restrict__ ba
       }
     }
   }
+}
+
+// Exact fp32 re-rank of kc <= 128 candidates, ordered top-k, vote.  One CTA (4 warps) per query:
+// the four warps score the candidates, warp 0 then extracts the k best in (score, row) order and
+// votes.
+// Outputs: idx[nq,k], score[nq,k] in result order; counts[nq,n_classes]; label = first argmax
+// of counts (np.argmax semantics, chroma.py:128: ties -> left > right > none).
+__global__ void __launch_bounds__(128)
+knn_rerank_vote_kernel(const float* __restrict__ q, const float* __restrict__ bank,
+                       const int32_t* __restrict__ labels, const int32_t* __restrict__ cand,
+                       int nq, int m, int d, int kc, int k, int metric, int n_classes,
+                       int32_t* __restrict__ idx_out, float* __restrict__ score_out,
+                       int32_t* __restrict__ label_out, int32_t* __restrict__ counts_out,
+                       const uint8_t* __restrict__ row_mask, const KnnFilter filt) {
+  extern __shared__ float knn_q_smem[];  // [d] query row
+  __shared__ float s_key[KNN_MAX_CAND];
+  __shared__ int s_idx[KNN_MAX_CAND];
+  const int qi = blockIdx.x;
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (qi >= nq) return;
+  for (int i = threadIdx.x * 4; i < d; i += 128 * 4)
+    *reinterpret_cast<float4*>(knn_q_smem + i) = *reinterpret_cast<const float4*>(q + (size_t)qi * d + i);
+  __syncthreads();
+  knn_score_candidates<4>(knn_q_smem, bank, cand + (size_t)qi * kc, qi, m, d, kc, metric, row_mask, filt,
+                          s_key, s_idx);
   __syncthreads();
   if (w != 0) return;
   float ck[KNN_MAX_CAND / 32];   // key (larger == better) of candidate slot lane + 32*s
@@ -396,6 +427,114 @@ knn_rerank_vote_kernel(const float* __restrict__ q, const float* __restrict__ ba
       if (cnt[j] > cnt[best]) best = j;
     }
     if (label_out) label_out[qi] = best;
+  }
+}
+
+// In-place bitonic sort of n2 (a power of two) (key, row) pairs in shared memory into the
+// (key descending, row ascending) order; all T threads of the CTA take part.
+template <int T>
+__device__ __forceinline__ void knn_bitonic_sort(float* s_key, int* s_idx, int n2) {
+  for (int k2 = 2; k2 <= n2; k2 <<= 1) {
+    for (int j = k2 >> 1; j > 0; j >>= 1) {
+      for (int i = threadIdx.x; i < n2; i += T) {
+        const int l = i ^ j;
+        if (l > i) {
+          const float ka = s_key[i], kb = s_key[l];
+          const int ia = s_idx[i], ib = s_idx[l];
+          const bool up = (i & k2) == 0;  // this run is sorted best-first
+          const bool swap = up ? key_before(kb, ib, ka, ia) : key_before(ka, ia, kb, ib);
+          if (swap) { s_key[i] = kb; s_key[l] = ka; s_idx[i] = ib; s_idx[l] = ia; }
+        }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+// The same re-rank for the larger n_results of the clip-store queries (100-750: config.py:10-11,
+// frame_retriever.py:41-43): kc up to KNN_SORT_MAX_CAND candidates are scored by the same code and
+// ordered by a bitonic sort in shared memory.  One CTA (8 warps) per query.
+__global__ void __launch_bounds__(256)
+knn_rerank_sort_kernel(const float* __restrict__ q, const float* __restrict__ bank,
+                       const int32_t* __restrict__ labels, const int32_t* __restrict__ cand,
+                       int nq, int m, int d, int kc, int k, int metric, int n_classes,
+                       int32_t* __restrict__ idx_out, float* __restrict__ score_out,
+                       int32_t* __restrict__ label_out, int32_t* __restrict__ counts_out,
+                       const uint8_t* __restrict__ row_mask, const KnnFilter filt) {
+  extern __shared__ float knn_q_smem[];  // [d] query row
+  __shared__ float s_key[KNN_SORT_MAX_CAND];
+  __shared__ int s_idx[KNN_SORT_MAX_CAND];
+  __shared__ int s_cnt[KNN_MAX_CLASSES];
+  const int qi = blockIdx.x;
+  if (qi >= nq) return;
+  for (int i = threadIdx.x * 4; i < d; i += 256 * 4)
+    *reinterpret_cast<float4*>(knn_q_smem + i) = *reinterpret_cast<const float4*>(q + (size_t)qi * d + i);
+  if (threadIdx.x < KNN_MAX_CLASSES) s_cnt[threadIdx.x] = 0;
+  int n2 = 32;
+  while (n2 < kc) n2 <<= 1;
+  for (int i = kc + threadIdx.x; i < n2; i += 256) { s_key[i] = -INFINITY; s_idx[i] = 0x7fffffff; }
+  __syncthreads();
+  knn_score_candidates<8>(knn_q_smem, bank, cand + (size_t)qi * kc, qi, m, d, kc, metric, row_mask, filt,
+                          s_key, s_idx);
+  __syncthreads();
+  knn_bitonic_sort<256>(s_key, s_idx, n2);
+  for (int r = threadIdx.x; r < k; r += 256) {
+    const int wi = r < n2 ? s_idx[r] : 0x7fffffff;
+    if (wi == 0x7fffffff) {  // fewer than k rows in play: pad like an empty Chroma slot
+      idx_out[(size_t)qi * k + r] = -1;
+      score_out[(size_t)qi * k + r] = 0.f;
+    } else {
+      idx_out[(size_t)qi * k + r] = wi;
+      score_out[(size_t)qi * k + r] = metric == METRIC_L2 ? -s_key[r] : s_key[r];
+      if (labels != nullptr && n_classes > 0) atomicAdd(&s_cnt[__ldg(labels + wi)], 1);
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int best = 0;
+    for (int j = 0; j < n_classes; ++j) {
+      if (counts_out) counts_out[(size_t)qi * n_classes + j] = s_cnt[j];
+      if (s_cnt[j] > s_cnt[best]) best = j;
+    }
+    if (label_out) label_out[qi] = best;
+  }
+}
+
+// Merge of per-shard result lists (the row-sharded clip store's exchange step):
+// idx / score [nq, c] with GLOBAL row ids (-1 = empty slot) -> the k best per query in the
+// kernels' total order (better score first, then the lower row id).  One CTA per query, bitonic
+// sort in shared memory; c <= 4096.
+__global__ void __launch_bounds__(256)
+knn_merge_topk_kernel(const int32_t* __restrict__ idx_in, const float* __restrict__ score_in, int nq,
+                      int c, int k, int descending, int32_t* __restrict__ idx_out,
+                      float* __restrict__ score_out) {
+  extern __shared__ float knn_merge_smem[];  // [n2] keys | [n2] rows
+  const int qi = blockIdx.x;
+  if (qi >= nq) return;
+  int n2 = 32;
+  while (n2 < c) n2 <<= 1;
+  float* s_key = knn_merge_smem;
+  int* s_idx = reinterpret_cast<int*>(knn_merge_smem + n2);
+  for (int i = threadIdx.x; i < n2; i += 256) {
+    int row = 0x7fffffff;
+    float key = -INFINITY;
+    if (i < c) {
+      const int r = __ldg(idx_in + (size_t)qi * c + i);
+      if (r >= 0) {
+        row = r;
+        const float sc = __ldg(score_in + (size_t)qi * c + i);
+        key = descending ? sc : -sc;
+      }
+    }
+    s_key[i] = key;
+    s_idx[i] = row;
+  }
+  __syncthreads();
+  knn_bitonic_sort<256>(s_key, s_idx, n2);
+  for (int r = threadIdx.x; r < k; r += 256) {
+    const int wi = r < n2 ? s_idx[r] : 0x7fffffff;
+    idx_out[(size_t)qi * k + r] = wi == 0x7fffffff ? -1 : wi;
+    score_out[(size_t)qi * k + r] = wi == 0x7fffffff ? 0.f : (descending ? s_key[r] : -s_key[r]);
   }
 }
 

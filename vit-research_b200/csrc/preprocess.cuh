@@ -101,7 +101,9 @@ __global__ void __launch_bounds__(256) resize_u8_aa_kernel(const ResizeParams p)
 // (buf += S * alpha), accumulated vertically (sum = beta * buf, then sum += beta * buf), and
 // written with saturate_cast<uchar> (round half to even).  Multiplies and adds are kept separate
 // (the C++ loop is not FMA-contracted in OpenCV's baseline x86 build).  When both scale factors
-// are integers OpenCV takes ResizeAreaFast instead: integer box sum, then sum * (1.f / area).
+// are integers OpenCV takes ResizeAreaFast instead: integer box sum, then sum * (1.f / area) --
+// except at exactly 2 x 2, where its vector form computes (a + b + c + d + 2) >> 2.
+// Pinned byte for byte against cv2 4.13 (tests/golden/preprocess_cv2_golden.npz).
 // ---------------------------------------------------------------------------------------------
 struct AreaAxis {
   const int* off;      // [out + 1] first table entry of each destination index
@@ -131,6 +133,11 @@ __global__ void __launch_bounds__(256) resize_area_u8_kernel(const AreaParams p)
         const uint8_t* srow = src + ((size_t)(dy * p.fast_sy + yy) * p.in_w + (size_t)dx * p.fast_sx) * C + c;
         for (int xx = 0; xx < p.fast_sx; ++xx) acc += srow[xx * C];
       }
+      if (p.fast_sx == 2 && p.fast_sy == 2) {
+        // OpenCV's ResizeAreaFastVec: exactly 2 x 2 is the INTEGER mean, round half up
+        dst[e] = (uint8_t)((acc + 2) >> 2);
+        continue;
+      }
       sum = __fmul_rn((float)acc, p.fast_scale);
     } else {
       bool first = true;
@@ -147,6 +154,47 @@ __global__ void __launch_bounds__(256) resize_area_u8_kernel(const AreaParams p)
     int r = __float2int_rn(sum);
     r = r < 0 ? 0 : (r > 255 ? 255 : r);
     dst[e] = (uint8_t)r;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// cv2.resize(im, (768, 432)) with the default interpolation, INTER_LINEAR -- the resize
+// extract_embeddings applies before the TF model (smarter_generate_clips.py:81).  OpenCV's 8-bit
+// bilinear path: two taps per axis (no antialiasing), short coefficients scaled by 2^11 built on
+// the host exactly as OpenCV builds them (float arithmetic, cvRound), horizontal pass in int,
+// vertical pass ((b0 * (S0 >> 4)) >> 16) + ((b1 * (S1 >> 4)) >> 16) + 2) >> 2.  HBM-bound byte work:
+// one CTA per destination row, a thread per destination byte gathers its 2 x 2 source bytes (the
+// two source rows of a destination row are read once per CTA and stay in L1).
+// ---------------------------------------------------------------------------------------------
+struct LinearParams {
+  const uint8_t* in;   // [n, in_h, in_w, C]
+  uint8_t* out;        // [n, out_h, out_w, C]
+  const int* xs;       // [out_w] first source column (fraction already zeroed at the borders)
+  const int* xa;       // [out_w][2] coefficients
+  const int* ys;       // [out_h] first source row (may be -1 / in_h - 1: rows are clamped)
+  const int* ya;       // [out_h][2]
+  int n, C, in_h, in_w, out_h, out_w;
+};
+
+__global__ void __launch_bounds__(256) resize_linear_u8_kernel(const LinearParams p) {
+  const int dy = blockIdx.x, f = blockIdx.y;
+  const int C = p.C, row_elems = p.out_w * C;
+  const uint8_t* src = p.in + (size_t)f * p.in_h * p.in_w * C;
+  uint8_t* dst = p.out + ((size_t)f * p.out_h + dy) * row_elems;
+  const int sy = p.ys[dy];
+  const int y0 = min(max(sy, 0), p.in_h - 1), y1 = min(max(sy + 1, 0), p.in_h - 1);
+  const int b0 = p.ya[2 * dy], b1 = p.ya[2 * dy + 1];
+  const uint8_t* r0 = src + (size_t)y0 * p.in_w * C;
+  const uint8_t* r1 = src + (size_t)y1 * p.in_w * C;
+  for (int e = threadIdx.x; e < row_elems; e += blockDim.x) {
+    const int dx = e / C, c = e - dx * C;
+    const int x0 = p.xs[dx], x1 = min(x0 + 1, p.in_w - 1);
+    const int a0 = p.xa[2 * dx], a1 = p.xa[2 * dx + 1];
+    const int s0 = (int)r0[x0 * C + c] * a0 + (int)r0[x1 * C + c] * a1;
+    const int s1 = (int)r1[x0 * C + c] * a0 + (int)r1[x1 * C + c] * a1;
+    int v = (((b0 * (s0 >> 4)) >> 16) + ((b1 * (s1 >> 4)) >> 16) + 2) >> 2;
+    v = v < 0 ? 0 : (v > 255 ? 255 : v);
+    dst[e] = (uint8_t)v;
   }
 }
 

@@ -42,6 +42,8 @@ struct Err {
   }
 };
 
+thread_local Err g_op_err;
+
 #define CK(e, call)                                                                        \
   do {                                                                                     \
     cudaError_t _s = (call);                                                               \
@@ -205,8 +207,10 @@ int gemm_s6_mask() {
 template <int EPI>
 int launch_gemm_e(Err& e, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& c,
                   const CUtensorMap& r, const GemmParams& p, cudaStream_t st) {
-  if constexpr (EPI == EPI_BIAS_BF16 || EPI == EPI_BIAS_GELU_BF16 || EPI == EPI_BIAS_RESID_F32) {
-    const int want = EPI == EPI_BIAS_RESID_F32 ? ((gemm_s6_mask() & 2) && p.K > 1024) : (gemm_s6_mask() & 1);
+  if constexpr (EPI == EPI_BIAS_BF16 || EPI == EPI_BIAS_GELU_BF16 || EPI == EPI_BIAS_RESID_F32 ||
+                EPI == EPI_BIAS_RESID_BF16) {
+    const int want = (EPI == EPI_BIAS_RESID_F32 || EPI == EPI_BIAS_RESID_BF16)
+                         ? ((gemm_s6_mask() & 2) && p.K > 1024) : (gemm_s6_mask() & 1);
     if (want && gemm_cta_group(p.M) == 2) return launch_gemm_t<256, EPI, 2, true>(e, a, b, c, r, p, st);
   }
   return gemm_cta_group(p.M) == 2 ? launch_gemm_t<256, EPI, 2>(e, a, b, c, r, p, st)
@@ -240,6 +244,7 @@ int launch_gemm(Err& e, int epi, const CUtensorMap& a, const CUtensorMap& b, con
     case EPI_TABLE_F32: return launch_gemm_e<EPI_TABLE_F32>(e, a, b, c, r, p, st);
     case EPI_F32: return launch_gemm_e<EPI_F32>(e, a, b, c, r, p, st);
     case EPI_THRESH_POOL: return launch_gemm_e<EPI_THRESH_POOL>(e, a, b, c, r, p, st);
+    case EPI_BIAS_RESID_BF16: return launch_gemm_e<EPI_BIAS_RESID_BF16>(e, a, b, c, r, p, st);
   }
   e.set("gemm: unknown epilogue %d", epi);
   return 1;
@@ -398,6 +403,9 @@ struct BatchMaps {  // tensor maps that depend on the number of frames in the ca
   CUtensorMap att_q, att_kv, att_o;         // attention
   // last layer, CLS rows only (row f of these maps = token 0 of frame f: pitch S*D)
   CUtensorMap a_act_cls, a_xb_cls, a_h_cls, c_resid_cls, c_h_cls;
+  // bf16 residual stream (default): the residual GEMMs update xb in place
+  CUtensorMap c_xb, c_xb_cls;
+  CUtensorMap c_patch;                      // fp32 patch-embedding output (scratch in hbuf)
 };
 
 struct vitk_ctx {
@@ -418,6 +426,7 @@ struct vitk_ctx {
   float *stats[2] = {nullptr, nullptr};  // per-row LayerNorm partial sums, ping-pong
   int stat_parts = 0;                 // 2 * hidden / 256
   bool cls_only_last = true;          // VITK_FULL_LAST_LAYER=1 computes all tokens in the last layer
+  bool resid_f32 = false;             // VITK_RESID_F32=1: fp32 master residual stream + bf16 copy (round-1 form)
   float *resid = nullptr, *emb = nullptr;
   uint8_t* pix_stage = nullptr;  // device staging for vitk_embed_host_u8
   std::map<int, BatchMaps> maps;
@@ -435,14 +444,14 @@ struct vitk_ctx {
   float *knn_q = nullptr, *knn_scores = nullptr;
   __nv_bfloat16* knn_qb = nullptr;
   int32_t* knn_cand = nullptr;
-  int knn_cap_q = 0, knn_cap_m = 0;
+  int knn_cap_q = 0, knn_cap_m = 0, knn_cap_kc = 0;
   // large-store path (bank_m > KNN_DIRECT_MAX): per-query candidate pools instead of scores
   uint2* knn_pool = nullptr;
   int* knn_pool_n = nullptr;
   unsigned long long* knn_thresh = nullptr;
   int* knn_overflow = nullptr;      // device, KNN_MAX_STAGES flags
   int* knn_overflow_host = nullptr; // pinned
-  int knn_pool_cap_q = 0;
+  int knn_pool_cap_q = 0, knn_pool_cap_e = 0;   // queries / entries per query the pools hold
   int64_t knn_redo_stages = 0;      // stages redone after a pool overflow (diagnostic)
   int32_t *res_idx = nullptr, *res_label = nullptr, *res_counts = nullptr;
   float* res_score = nullptr;
@@ -460,6 +469,11 @@ struct vitk_ctx {
     int fast_sx = 0, fast_sy = 0;
   };
   std::map<std::pair<int, int>, AreaPlan> area_plans;
+  struct LinearPlan {
+    void* blob = nullptr;
+    const int *xs = nullptr, *xa = nullptr, *ys = nullptr, *ya = nullptr;
+  };
+  std::map<std::pair<int, int>, LinearPlan> linear_plans;
   uint8_t* raw_stage = nullptr;   // device staging for raw frames of vitk_embed_resize_host_u8
   size_t raw_stage_bytes = 0;
   // Viterbi workspace (grown on demand)
@@ -467,7 +481,22 @@ struct vitk_ctx {
   int8_t* hmm_bp = nullptr;
   int* hmm_offsets = nullptr;
   int hmm_cap_t = 0, hmm_cap_seq = 0, hmm_cap_k = -1;
+  // several banks per handle (vitk_bank_new / vitk_bank_select): the fields above are the
+  // CURRENT bank, the others are parked here
+  struct BankState {
+    float *bank = nullptr, *sqnorm = nullptr;
+    __nv_bfloat16* bf16 = nullptr;
+    int32_t* labels = nullptr;
+    int m = 0, d = 0, classes = 0, cap = 0;
+    CUtensorMap tm;
+  };
+  std::map<int, BankState> parked;
+  int bank_id = 0, next_bank_id = 1;
   cudaStream_t own_stream = nullptr;
+  // ordering between the caller's streams and own_stream (both work on the same workspace)
+  cudaEvent_t ev_own = nullptr, ev_user = nullptr;
+  bool own_pending = false, user_pending = false;
+  cudaStream_t last_user = nullptr;
   int64_t launches = 0;
   // vitk_profile_fc1: CUDA-event pairs around every fc1 GEMM launch of the forward
   bool prof_fc1 = false;
@@ -475,6 +504,8 @@ struct vitk_ctx {
   // streaming host API (vitk_stream_submit / vitk_stream_wait): two batches in flight
   struct StreamSlot {
     uint8_t* pix = nullptr;
+    uint8_t* raw = nullptr;     // raw-size frames of vitk_stream_submit_raw (grown on demand)
+    size_t raw_bytes = 0;
     float *emb = nullptr, *score = nullptr;
     int32_t *idx = nullptr, *label = nullptr, *counts = nullptr;
     cudaEvent_t ev_h2d = nullptr, ev_done = nullptr, ev_out = nullptr;
@@ -490,6 +521,49 @@ template <typename T>
 int dev_alloc(Err& e, T** p, size_t count) {
   CK(e, cudaMalloc(reinterpret_cast<void**>(p), count * sizeof(T)));
   return 0;
+}
+
+// Every entry point works on the handle's one workspace (activations, k-NN buffers), some on the
+// caller's stream, the host-buffer / streaming ones on own_stream.  order_enter makes the stream
+// about to be used wait for the work last queued on the other side; order_leave marks the work
+// just queued.  Calls on one stream need nothing; calls that alternate streams are serialised on
+// the device instead of racing.
+int order_enter(vitk_ctx* h, cudaStream_t st) {
+  Err& e = h->err;
+  CK(e, cudaSetDevice(h->device));
+  if (st == h->own_stream) {
+    if (h->user_pending) CK(e, cudaStreamWaitEvent(st, h->ev_user, 0));
+  } else {
+    if (h->own_pending) CK(e, cudaStreamWaitEvent(st, h->ev_own, 0));
+    if (h->user_pending && h->last_user != st) CK(e, cudaStreamWaitEvent(st, h->ev_user, 0));
+  }
+  return 0;
+}
+int order_leave(vitk_ctx* h, cudaStream_t st) {
+  Err& e = h->err;
+  if (st == h->own_stream) {
+    CK(e, cudaEventRecord(h->ev_own, st));
+    h->own_pending = true;
+  } else {
+    CK(e, cudaEventRecord(h->ev_user, st));
+    h->user_pending = true;
+    h->last_user = st;
+  }
+  return 0;
+}
+
+void bank_park(vitk_ctx* h) {
+  vitk_ctx::BankState b;
+  b.bank = h->bank; b.sqnorm = h->bank_sqnorm; b.bf16 = h->bank_bf16; b.labels = h->bank_labels;
+  b.m = h->bank_m; b.d = h->bank_d; b.classes = h->bank_classes; b.cap = h->bank_cap; b.tm = h->tm_bank;
+  h->parked[h->bank_id] = b;
+}
+void bank_unpark(vitk_ctx* h, int id) {
+  vitk_ctx::BankState b = h->parked[id];
+  h->parked.erase(id);
+  h->bank = b.bank; h->bank_sqnorm = b.sqnorm; h->bank_bf16 = b.bf16; h->bank_labels = b.labels;
+  h->bank_m = b.m; h->bank_d = b.d; h->bank_classes = b.classes; h->bank_cap = b.cap; h->tm_bank = b.tm;
+  h->bank_id = id;
 }
 
 int upload_bf16(Err& e, __nv_bfloat16* dst, const float* src, size_t count) {
@@ -524,6 +598,11 @@ void free_ctx(vitk_ctx* c) {
   cudaFree(c->resid); cudaFree(c->emb); cudaFree(c->pix_stage);
   cudaFree(c->xb); cudaFree(c->stats[0]); cudaFree(c->stats[1]);
   cudaFree(c->bank); cudaFree(c->bank_sqnorm); cudaFree(c->bank_bf16); cudaFree(c->bank_labels);
+  for (auto& kv : c->parked) {
+    cudaFree(kv.second.bank); cudaFree(kv.second.sqnorm); cudaFree(kv.second.bf16); cudaFree(kv.second.labels);
+  }
+  if (c->ev_own) cudaEventDestroy(c->ev_own);
+  if (c->ev_user) cudaEventDestroy(c->ev_user);
   cudaFree(c->knn_pen);
   cudaFree(c->res_idx); cudaFree(c->res_label); cudaFree(c->res_counts); cudaFree(c->res_score);
   cudaFree(c->knn_q); cudaFree(c->knn_scores); cudaFree(c->knn_qb); cudaFree(c->knn_cand);
@@ -532,11 +611,12 @@ void free_ctx(vitk_ctx* c) {
   cudaFree(c->hmm_loge); cudaFree(c->hmm_table); cudaFree(c->hmm_bp); cudaFree(c->hmm_offsets);
   for (auto& kv : c->resize_plans) cudaFree(kv.second.blob);
   for (auto& kv : c->area_plans) cudaFree(kv.second.blob);
+  for (auto& kv : c->linear_plans) cudaFree(kv.second.blob);
   for (auto& pr : c->prof_events) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
   cudaFree(c->raw_stage);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
   for (auto& sl : c->slots) {
-    cudaFree(sl.pix); cudaFree(sl.emb); cudaFree(sl.score); cudaFree(sl.idx); cudaFree(sl.label);
+    cudaFree(sl.pix); cudaFree(sl.raw); cudaFree(sl.emb); cudaFree(sl.score); cudaFree(sl.idx); cudaFree(sl.label);
     cudaFree(sl.counts);
     if (sl.ev_h2d) cudaEventDestroy(sl.ev_h2d);
     if (sl.ev_done) cudaEventDestroy(sl.ev_done);
@@ -633,6 +713,10 @@ extern "C" int vitk_create(const vitk_config* cfg, int device, vitk_handle* out)
     const char* v = getenv("VITK_FULL_LAST_LAYER");
     c->cls_only_last = !(v && atoi(v) == 1);
   }
+  {
+    const char* v = getenv("VITK_RESID_F32");
+    c->resid_f32 = v && atoi(v) == 1;
+  }
   if (c->S > ATT_MAX_S) { e.set("tokens per frame %d > %d unsupported by the attention kernel", c->S, ATT_MAX_S); return fail(c); }
   if (c->Kp % 64) { e.set("channels*patch^2 must be a multiple of 64"); return fail(c); }
   if (cudaSetDevice(device) != cudaSuccess) { e.set("cudaSetDevice failed"); return fail(c); }
@@ -656,7 +740,7 @@ extern "C" int vitk_create(const vitk_config* cfg, int device, vitk_handle* out)
   rc |= dev_alloc(e, &c->w_patch, D * Kp) | dev_alloc(e, &c->posb, (size_t)c->S * D) |
         dev_alloc(e, &c->lnf_g, D) | dev_alloc(e, &c->lnf_b, D) | dev_alloc(e, &c->act, M * actw) |
         dev_alloc(e, &c->qkv, M * 3 * D) | dev_alloc(e, &c->hbuf, M * F) |
-        dev_alloc(e, &c->resid, M * D) | dev_alloc(e, &c->xb, M * D) |
+        ((c->resid_f32 || F < 2 * D) ? dev_alloc(e, &c->resid, M * D) : 0) | dev_alloc(e, &c->xb, M * D) |
         dev_alloc(e, &c->stats[0], M * 2 * (2 * D / 256)) |
         dev_alloc(e, &c->stats[1], M * 2 * (2 * D / 256)) |
         dev_alloc(e, &c->emb, (size_t)cfg->max_batch * D) |
@@ -670,8 +754,10 @@ extern "C" int vitk_create(const vitk_config* cfg, int device, vitk_handle* out)
         dev_alloc(e, &c->res_counts, (size_t)cfg->max_batch * KNN_MAX_CLASSES);
   if (rc) return fail(c);
   if (tmap_operand(e, &c->tm_patch, c->w_patch, D, Kp, 128)) return fail(c);
-  if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess) {
-    e.set("cudaStreamCreate failed");
+  if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreateWithFlags(&c->ev_own, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&c->ev_user, cudaEventDisableTiming) != cudaSuccess) {
+    e.set("cudaStreamCreate / cudaEventCreate failed");
     return fail(c);
   }
   *out = c;
@@ -873,7 +959,10 @@ int get_maps(vitk_ctx* c, int n, BatchMaps** out) {
            tmap_operand(e, &m.a_act, c->act, M, D, GEMM_BM) |
            tmap_operand(e, &m.a_h, c->hbuf, M, F, GEMM_BM) |
            tmap_operand(e, &m.a_xb, c->xb, M, D, GEMM_BM) |
-           tmap_output(e, &m.c_resid, c->resid, M, D, false) |
+           (c->resid_f32 ? tmap_output(e, &m.c_resid, c->resid, M, D, false) : 0) |
+           tmap_output(e, &m.c_patch, c->resid ? (void*)c->resid : (void*)c->hbuf, M, D, false) |
+           tmap_output(e, &m.c_xb, c->xb, M, D, true) |
+           tmap_output(e, &m.c_xb_cls, c->xb, n, D, true, (long long)c->S * D) |
            tmap_output(e, &m.c_qkv, c->qkv, M, 3 * D, true) |
            tmap_output(e, &m.c_h, c->hbuf, M, F, true) |
            tmap_tokens(e, &m.att_q, c->qkv, n, c->S, 3 * D, 128) |
@@ -882,7 +971,7 @@ int get_maps(vitk_ctx* c, int n, BatchMaps** out) {
            tmap_operand(e, &m.a_act_cls, c->act, n, D, GEMM_BM, (long long)c->S * D) |
            tmap_operand(e, &m.a_xb_cls, c->xb, n, D, GEMM_BM, (long long)c->S * D) |
            tmap_operand(e, &m.a_h_cls, c->hbuf, n, F, GEMM_BM) |
-           tmap_output(e, &m.c_resid_cls, c->resid, n, D, false, (long long)c->S * D) |
+           (c->resid_f32 ? tmap_output(e, &m.c_resid_cls, c->resid, n, D, false, (long long)c->S * D) : 0) |
            tmap_output(e, &m.c_h_cls, c->hbuf, n, F, true);
   if (rc) return 1;
   *out = &c->maps.emplace(n, m).first->second;
@@ -904,12 +993,22 @@ int forward_chunk(vitk_ctx* c, const void* pix, int fmt, int n, float* emb_f32,
   GemmParams gp{};
   gp.M = M; gp.N = D; gp.K = c->Kp;
   gp.table = c->posb; gp.table_rows = c->S;
-  if (launch_gemm(e, EPI_TABLE_F32, mp->a_patch, c->tm_patch, mp->c_resid, mp->c_resid, gp, st))
+  // The embedded tokens land in fp32 scratch (the fp32 residual buffer, or -- bf16 residual
+  // stream -- the not yet used MLP buffer) ...
+  const float* patch_out = c->resid ? c->resid : reinterpret_cast<const float*>(c->hbuf);
+  if (launch_gemm(e, EPI_TABLE_F32, mp->a_patch, c->tm_patch, mp->c_patch, mp->c_patch, gp, st))
     return 1;
-  // bf16 copy + row statistics of the embedded tokens: inputs of layer 0's folded LayerNorm
+  // ... and one pass produces the bf16 residual stream / copy + the row statistics that feed
+  // layer 0's folded LayerNorm
   const int parts = c->stat_parts;
   const long long sstride = 2LL * parts;
-  if (launch_rowstats(e, c->resid, c->xb, c->stats[0], M, D, parts, st)) return 1;
+  if (launch_rowstats(e, patch_out, c->xb, c->stats[0], M, D, parts, st)) return 1;
+  // Residual stream: bf16 in place in `xb` (default; the residual GEMMs read and write the tile
+  // their own epilogue owns) or the round-1 form, an fp32 master copy + a bf16 copy (VITK_RESID_F32=1).
+  const bool rf32 = c->resid_f32;
+  const int epi_res = rf32 ? EPI_BIAS_RESID_F32 : EPI_BIAS_RESID_BF16;
+  const CUtensorMap& c_res = rf32 ? mp->c_resid : mp->c_xb;
+  const CUtensorMap& c_res_cls = rf32 ? mp->c_resid_cls : mp->c_xb_cls;
   c->launches += 3;
   const int epi_fc1 = cfg.gelu_tanh ? EPI_BIAS_GELUT_BF16 : EPI_BIAS_GELU_BF16;
   const size_t nl = c->layers.size();
@@ -942,8 +1041,9 @@ int forward_chunk(vitk_ctx* c, const void* pix, int fmt, int n, float* emb_f32,
       const long long pitch = (long long)c->S;
       GemmParams o{};
       o.M = n; o.N = D; o.K = D; o.bias = L.b_o;
-      o.xb = c->xb; o.xb_ld = pitch * D; o.stats_out = c->stats[1]; o.stats_out_stride = pitch * sstride;
-      if (launch_gemm(e, EPI_BIAS_RESID_F32, mp->a_act_cls, L.tm_o, mp->c_resid_cls, mp->c_resid_cls, o, st))
+      if (rf32) { o.xb = c->xb; o.xb_ld = pitch * D; }
+      o.stats_out = c->stats[1]; o.stats_out_stride = pitch * sstride;
+      if (launch_gemm(e, epi_res, mp->a_act_cls, L.tm_o, c_res_cls, c_res_cls, o, st))
         return 1;
       GemmParams f1{};
       f1.M = n; f1.N = F; f1.K = D; f1.bias = L.b_fc1; f1.c1 = L.c1_fc1;
@@ -952,7 +1052,7 @@ int forward_chunk(vitk_ctx* c, const void* pix, int fmt, int n, float* emb_f32,
       if (launch_gemm(e, epi_fc1, mp->a_xb_cls, L.tm_fc1, mp->c_h_cls, mp->c_h_cls, f1, st)) return 1;
       GemmParams f2{};
       f2.M = n; f2.N = D; f2.K = F; f2.bias = L.b_fc2;
-      if (launch_gemm(e, EPI_BIAS_RESID_F32, mp->a_h_cls, L.tm_fc2, mp->c_resid_cls, mp->c_resid_cls, f2, st))
+      if (launch_gemm(e, epi_res, mp->a_h_cls, L.tm_fc2, c_res_cls, c_res_cls, f2, st))
         return 1;
       c->launches += 5;
       continue;
@@ -960,9 +1060,10 @@ int forward_chunk(vitk_ctx* c, const void* pix, int fmt, int n, float* emb_f32,
     // (a5.4) out-proj + residual; epilogue also emits the bf16 copy and LN2's row sums
     GemmParams o{};
     o.M = M; o.N = D; o.K = D; o.bias = L.b_o;
-    o.xb = c->xb; o.xb_ld = D; o.stats_out = c->stats[1]; o.stats_out_stride = sstride;
+    if (rf32) { o.xb = c->xb; o.xb_ld = D; }
+    o.stats_out = c->stats[1]; o.stats_out_stride = sstride;
     o.reverse_m = next_dir();
-    if (launch_gemm(e, EPI_BIAS_RESID_F32, mp->a_act, L.tm_o, mp->c_resid, mp->c_resid, o, st))
+    if (launch_gemm(e, epi_res, mp->a_act, L.tm_o, c_res, c_res, o, st))
       return 1;
     // (a5.1+a5.5) LN2 folded into fc1 + GELU, then fc2 + residual (+ next layer's LN1 inputs)
     GemmParams f1{};
@@ -985,19 +1086,22 @@ int forward_chunk(vitk_ctx* c, const void* pix, int fmt, int n, float* emb_f32,
     f2.M = M; f2.N = D; f2.K = F; f2.bias = L.b_fc2;
     f2.reverse_m = next_dir();
     if (li + 1 < nl) {  // nobody reads the copy / sums after the last layer
-      f2.xb = c->xb; f2.xb_ld = D; f2.stats_out = c->stats[0]; f2.stats_out_stride = sstride;
+      if (rf32) { f2.xb = c->xb; f2.xb_ld = D; }
+      f2.stats_out = c->stats[0]; f2.stats_out_stride = sstride;
     }
-    if (launch_gemm(e, EPI_BIAS_RESID_F32, mp->a_h, L.tm_fc2, mp->c_resid, mp->c_resid, f2, st))
+    if (launch_gemm(e, epi_res, mp->a_h, L.tm_fc2, c_res, c_res, f2, st))
       return 1;
     c->launches += 5;
   }
   // (a6) final LN on the CLS rows only, (a7) row normalisation
   const int blocks = (n + 3) / 4;
+  const float* rs_f32 = rf32 ? c->resid : nullptr;
+  const __nv_bfloat16* rs_bf16 = rf32 ? nullptr : c->xb;
   if (D == 768)
-    cls_tail_kernel<6><<<blocks, 128, 0, st>>>(c->resid, c->lnf_g, c->lnf_b, emb_f32, emb_bf16, n,
+    cls_tail_kernel<6><<<blocks, 128, 0, st>>>(rs_f32, rs_bf16, c->lnf_g, c->lnf_b, emb_f32, emb_bf16, n,
                                                c->S, cfg.ln_eps, l2norm);
   else
-    cls_tail_kernel<8><<<blocks, 128, 0, st>>>(c->resid, c->lnf_g, c->lnf_b, emb_f32, emb_bf16, n,
+    cls_tail_kernel<8><<<blocks, 128, 0, st>>>(rs_f32, rs_bf16, c->lnf_g, c->lnf_b, emb_f32, emb_bf16, n,
                                                c->S, cfg.ln_eps, l2norm);
   CK(e, cudaGetLastError());
   c->launches += 1;
@@ -1021,6 +1125,7 @@ extern "C" int vitk_embed(vitk_handle h, const void* pixels_dev, int pixel_forma
   if (pixel_format < 0 || pixel_format > 2) { e.set("vitk_embed: bad pixel format"); return 1; }
   CK(e, cudaSetDevice(h->device));
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (order_enter(h, st)) return 1;
   const size_t fb = pixel_bytes_per_frame(h->cfg, pixel_format);
   for (int off = 0; off < n; off += h->cfg.max_batch) {
     const int cn = n - off < h->cfg.max_batch ? n - off : h->cfg.max_batch;
@@ -1031,6 +1136,7 @@ extern "C" int vitk_embed(vitk_handle h, const void* pixels_dev, int pixel_forma
                       pixel_format, cn, emb_f32_dev + (size_t)off * h->D, eb, l2_normalise, st))
       return 1;
   }
+  if (order_leave(h, st)) return 1;
   return 0;
 }
 
@@ -1043,6 +1149,7 @@ extern "C" int vitk_embed_host_u8(vitk_handle h, const uint8_t* frames_host, int
   if (!frames_host || !emb_host || n < 0) { e.set("vitk_embed_host_u8: bad argument"); return 1; }
   CK(e, cudaSetDevice(h->device));
   cudaStream_t st = h->own_stream;
+  if (order_enter(h, st)) return 1;
   const size_t fb = pixel_bytes_per_frame(h->cfg, PIX_U8_NHWC);
   for (int off = 0; off < n; off += h->cfg.max_batch) {
     const int cn = n - off < h->cfg.max_batch ? n - off : h->cfg.max_batch;
@@ -1052,6 +1159,7 @@ extern "C" int vitk_embed_host_u8(vitk_handle h, const uint8_t* frames_host, int
     CK(e, cudaMemcpyAsync(emb_host + (size_t)off * h->D, h->emb, (size_t)cn * h->D * 4,
                           cudaMemcpyDeviceToHost, st));
   }
+  if (order_leave(h, st)) return 1;
   CK(e, cudaStreamSynchronize(st));
   return 0;
 }
@@ -1137,6 +1245,7 @@ extern "C" int vitk_bank_set_device(vitk_handle h, const float* rows_dev, int m,
   CK(e, cudaSetDevice(h->device));
   CK(e, cudaDeviceSynchronize());
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (order_enter(h, st)) return 1;
   cudaFree(h->bank); cudaFree(h->bank_sqnorm); cudaFree(h->bank_bf16); cudaFree(h->bank_labels);
   h->bank = nullptr; h->bank_sqnorm = nullptr; h->bank_bf16 = nullptr; h->bank_labels = nullptr;
   h->bank_m = 0;
@@ -1181,6 +1290,7 @@ extern "C" int vitk_bank_write(vitk_handle h, int at_row, const float* rows, int
   }
   CK(e, cudaSetDevice(h->device));
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (order_enter(h, st)) return 1;
   const int d = h->bank_d;
   const int m_after = at_row + m_new > h->bank_m ? at_row + m_new : h->bank_m;
   if (m_after > h->bank_cap) {
@@ -1207,7 +1317,6 @@ extern "C" int vitk_bank_write(vitk_handle h, int at_row, const float* rows, int
   }
   const float* src = rows;
   float* tmp = nullptr;
-  int32_t* tmpl = nullptr;
   if (!on_device) {
     if (labels) {
       for (int i = 0; i < m_new; ++i)
@@ -1217,21 +1326,28 @@ extern "C" int vitk_bank_write(vitk_handle h, int at_row, const float* rows, int
         }
     }
     if (dev_alloc(e, &tmp, (size_t)m_new * d)) return 1;
-    CK(e, cudaMemcpyAsync(tmp, rows, (size_t)m_new * d * 4, cudaMemcpyHostToDevice, st));
     src = tmp;
-    if (labels)
-      CK(e, cudaMemcpyAsync(h->bank_labels + at_row, labels, (size_t)m_new * 4, cudaMemcpyHostToDevice, st));
-  } else if (labels) {
-    CK(e, cudaMemcpyAsync(h->bank_labels + at_row, labels, (size_t)m_new * 4, cudaMemcpyDeviceToDevice, st));
   }
-  (void)tmpl;
-  if (!labels) CK(e, cudaMemsetAsync(h->bank_labels + at_row, 0, (size_t)m_new * 4, st));
-  bank_prep_kernel<<<(m_new + 7) / 8, 256, 0, st>>>(src, h->bank + (size_t)at_row * d,
-                                                    h->bank_bf16 + (size_t)at_row * d,
-                                                    h->bank_sqnorm + at_row, m_new, d, normalise_rows);
-  CK(e, cudaGetLastError());
-  CK(e, cudaStreamSynchronize(st));  // host rows / the staging copy may be released on return
+  // every CUDA call below reports through `st_err` so that the staging copy is released on any path
+  cudaError_t st_err = cudaSuccess;
+  auto ok = [&](cudaError_t r) { if (st_err == cudaSuccess) st_err = r; return st_err == cudaSuccess; };
+  if (!on_device) ok(cudaMemcpyAsync(tmp, rows, (size_t)m_new * d * 4, cudaMemcpyHostToDevice, st));
+  if (labels && st_err == cudaSuccess)
+    ok(cudaMemcpyAsync(h->bank_labels + at_row, labels, (size_t)m_new * 4,
+                       on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+  if (!labels && st_err == cudaSuccess) ok(cudaMemsetAsync(h->bank_labels + at_row, 0, (size_t)m_new * 4, st));
+  if (st_err == cudaSuccess) {
+    bank_prep_kernel<<<(m_new + 7) / 8, 256, 0, st>>>(src, h->bank + (size_t)at_row * d,
+                                                      h->bank_bf16 + (size_t)at_row * d,
+                                                      h->bank_sqnorm + at_row, m_new, d, normalise_rows);
+    ok(cudaGetLastError());
+  }
+  ok(cudaStreamSynchronize(st));  // host rows / the staging copy may be released on return
   cudaFree(tmp);
+  if (st_err != cudaSuccess) {
+    e.set("vitk_bank_write: CUDA error: %s", cudaGetErrorString(st_err));
+    return 1;
+  }
   if (tmap_operand(e, &h->tm_bank, h->bank_bf16, m_after, d, 128)) return 1;
   h->bank_m = m_after;
   h->launches += 1;
@@ -1240,12 +1356,63 @@ extern "C" int vitk_bank_write(vitk_handle h, int at_row, const float* rows, int
 
 extern "C" int vitk_bank_rows(vitk_handle h) { return h ? h->bank_m : -1; }
 
+extern "C" int vitk_bank_new(vitk_handle h) {
+  if (!h) return -1;
+  bank_park(h);
+  h->bank = nullptr; h->bank_sqnorm = nullptr; h->bank_bf16 = nullptr; h->bank_labels = nullptr;
+  h->bank_m = 0; h->bank_d = 0; h->bank_classes = 0; h->bank_cap = 0;
+  h->bank_id = h->next_bank_id++;
+  return h->bank_id;
+}
+
+extern "C" int vitk_bank_current(vitk_handle h) { return h ? h->bank_id : -1; }
+
+extern "C" int vitk_bank_select(vitk_handle h, int bank_id) {
+  if (!h) return 1;
+  if (bank_id == h->bank_id) return 0;
+  if (h->parked.find(bank_id) == h->parked.end()) {
+    h->err.set("vitk_bank_select: no bank %d on this handle", bank_id);
+    return 1;
+  }
+  bank_park(h);
+  bank_unpark(h, bank_id);
+  return 0;
+}
+
+extern "C" int vitk_bank_free(vitk_handle h, int bank_id) {
+  if (!h) return 1;
+  Err& e = h->err;
+  CK(e, cudaSetDevice(h->device));
+  if (bank_id == h->bank_id) {
+    CK(e, cudaDeviceSynchronize());
+    cudaFree(h->bank); cudaFree(h->bank_sqnorm); cudaFree(h->bank_bf16); cudaFree(h->bank_labels);
+    h->bank = nullptr; h->bank_sqnorm = nullptr; h->bank_bf16 = nullptr; h->bank_labels = nullptr;
+    h->bank_m = 0; h->bank_d = 0; h->bank_classes = 0; h->bank_cap = 0;
+    return 0;
+  }
+  auto it = h->parked.find(bank_id);
+  if (it == h->parked.end()) return 0;   // already gone
+  CK(e, cudaDeviceSynchronize());
+  cudaFree(it->second.bank); cudaFree(it->second.sqnorm); cudaFree(it->second.bf16); cudaFree(it->second.labels);
+  h->parked.erase(it);
+  return 0;
+}
+
 namespace {
 int knn_candidates_for(int k, int m) {
   // bf16 similarity error on unit vectors is ~1e-4..1e-3; the slack keeps every true top-k
-  // row inside the candidate set so the fp32 re-rank can restore the exact order.
-  int kc = 2 * k + 32;
-  if (kc > KNN_MAX_CAND) kc = KNN_MAX_CAND;
+  // row inside the candidate set so the fp32 re-rank can restore the exact order.  Small k (the
+  // vote: 5 / 25 / 50): 2k + 32, at most 128 (warp-extraction re-rank).  Larger k (the clip-store
+  // queries, n_results 100-750): k + k/4 + 32 -- at rank 750 of a 1 M-row store of unit vectors
+  // about 140 rows lie within 1e-3 of the k-th score, 28 within 2e-4.
+  int kc;
+  if (k <= 64) {
+    kc = 2 * k + 32;
+    if (kc > KNN_MAX_CAND) kc = KNN_MAX_CAND;
+  } else {
+    kc = (k + k / 4 + 32 + 31) & ~31;
+    if (kc < KNN_MAX_CAND) kc = KNN_MAX_CAND;
+  }
   if (kc > m) kc = m;
   if (kc < k) kc = k < m ? k : m;
   return kc;
@@ -1254,11 +1421,26 @@ int knn_candidates_for(int k, int m) {
 constexpr int KNN_DIRECT_MAX = 2048;  // banks up to this many rows: score matrix + register select
 constexpr int KNN_MAX_STAGES = 32;
 
+int knn_pool_cap_for(int kc) { return kc <= 448 ? KNN_POOL_CAP : KNN_POOL_CAP_BIG; }
+
+int launch_pool_select(vitk_ctx* h, int cap, int n, int kc, int direct_rows, int ex_lo, int ex_hi,
+                       int32_t* cand, int* overflow, cudaStream_t st) {
+  Err& e = h->err;
+  if (cap == KNN_POOL_CAP)
+    knn_pool_select_kernel<KNN_POOL_CAP / KNN_POOL_KPL><<<n, KNN_POOL_CAP / KNN_POOL_KPL, 0, st>>>(
+        h->knn_pool, h->knn_pool_n, h->knn_thresh, n, kc, direct_rows, ex_lo, ex_hi, cand, overflow);
+  else
+    knn_pool_select_kernel<KNN_POOL_CAP_BIG / KNN_POOL_KPL><<<n, KNN_POOL_CAP_BIG / KNN_POOL_KPL, 0, st>>>(
+        h->knn_pool, h->knn_pool_n, h->knn_thresh, n, kc, direct_rows, ex_lo, ex_hi, cand, overflow);
+  CK(e, cudaGetLastError());
+  h->launches += 1;
+  return 0;
+}
+
 // One stage of the large-store walk: bank rows [lo, hi) through the threshold-filter GEMM, then
-// the pool select (flag = overflow slot; ex_* = rows to drop from the pools first; cand != null
-// on the final select).
-int knn_stage(vitk_ctx* h, int n, int kc, int metric, int lo, int hi, int flag, bool direct,
-              cudaStream_t st) {
+// the pool select (flag = overflow slot).
+int knn_stage(vitk_ctx* h, int n, int kc, int cap, int metric, int lo, int hi, int flag, bool direct,
+              const KnnFilter& filt, cudaStream_t st) {
   Err& e = h->err;
   const int d = h->bank_d;
   CUtensorMap ta, tb;
@@ -1269,48 +1451,50 @@ int knn_stage(vitk_ctx* h, int n, int kc, int metric, int lo, int hi, int flag, 
   gp.M = n; gp.N = hi - lo; gp.K = d;
   gp.bias = h->knn_pen_cur ? h->knn_pen_cur + lo : (metric == METRIC_L2 ? h->bank_sqnorm + lo : nullptr);
   gp.pool_thresh = h->knn_thresh; gp.pool = h->knn_pool; gp.pool_n = h->knn_pool_n;
-  gp.pool_cap = KNN_POOL_CAP; gp.col_base = lo;
+  gp.pool_cap = cap; gp.col_base = lo;
   gp.pool_l2 = metric == METRIC_L2 ? 1 : (h->knn_pen_cur ? 2 : 0);
   gp.pool_direct = direct ? 1 : 0;
+  gp.filt = filt;
   if (launch_gemm(e, EPI_THRESH_POOL, ta, tb, ta, ta, gp, st)) return 1;
-  knn_pool_select_kernel<<<n, 128, 0, st>>>(h->knn_pool, h->knn_pool_n, h->knn_thresh, n,
-                                                      kc, direct ? hi - lo : -1, 0, 0, nullptr,
-                                                      h->knn_overflow + flag);
-  CK(e, cudaGetLastError());
-  h->launches += 2;
-  return 0;
+  h->launches += 1;
+  return launch_pool_select(h, cap, n, kc, direct ? hi - lo : -1, 0, 0, nullptr, h->knn_overflow + flag, st);
 }
 
 // Candidate rows (h->knn_cand [n, kc]) for a bank of more than KNN_DIRECT_MAX rows.  All stages
 // are launched back to back; ONE stream synchronisation at the end reads the overflow flags.  A
 // flagged stage (its pool was truncated; thresholds stay valid lower bounds, so later stages are
 // unaffected) is redone in quarters with the final thresholds.
-int knn_large_candidates(vitk_ctx* h, int n, int kc, int metric, cudaStream_t st) {
+int knn_large_candidates(vitk_ctx* h, int n, int kc, int metric, const KnnFilter& filt, cudaStream_t st) {
   Err& e = h->err;
   const int m = h->bank_m;
-  if (n > h->knn_pool_cap_q) {
+  const int cap = knn_pool_cap_for(kc);
+  if (n > h->knn_pool_cap_q || cap > h->knn_pool_cap_e) {
     CK(e, cudaStreamSynchronize(st));
     cudaFree(h->knn_pool); cudaFree(h->knn_pool_n); cudaFree(h->knn_thresh);
     h->knn_pool = nullptr; h->knn_pool_n = nullptr; h->knn_thresh = nullptr;
+    const int cq = n > h->knn_pool_cap_q ? n : h->knn_pool_cap_q;
+    const int ce = cap > h->knn_pool_cap_e ? cap : h->knn_pool_cap_e;
     h->knn_pool_cap_q = 0;
-    if (dev_alloc(e, &h->knn_pool, (size_t)n * KNN_POOL_CAP) || dev_alloc(e, &h->knn_pool_n, (size_t)n) ||
-        dev_alloc(e, &h->knn_thresh, (size_t)n))
+    h->knn_pool_cap_e = 0;
+    if (dev_alloc(e, &h->knn_pool, (size_t)cq * ce) || dev_alloc(e, &h->knn_pool_n, (size_t)cq) ||
+        dev_alloc(e, &h->knn_thresh, (size_t)cq))
       return 1;
     if (!h->knn_overflow && dev_alloc(e, &h->knn_overflow, (size_t)KNN_MAX_STAGES)) return 1;
     if (!h->knn_overflow_host)
       CK(e, cudaMallocHost(reinterpret_cast<void**>(&h->knn_overflow_host), KNN_MAX_STAGES * sizeof(int)));
-    h->knn_pool_cap_q = n;
+    h->knn_pool_cap_q = cq;
+    h->knn_pool_cap_e = ce;
   }
   CK(e, cudaMemsetAsync(h->knn_pool_n, 0, (size_t)n * sizeof(int), st));
   CK(e, cudaMemsetAsync(h->knn_thresh, 0, (size_t)n * sizeof(unsigned long long), st));
   // stage sizes: the first fills the empty pools (threshold 0: everything is appended), later
   // ones grow by g, chosen so the EXPECTED survivors per pool (kc * g on exchangeable rows) stay
   // 4x below the pool capacity
-  int g = (KNN_POOL_CAP - kc) / (4 * kc);
+  int g = (cap - kc) / (4 * kc);
   g = g < 2 ? 2 : g > 8 ? 8 : g;
   struct Stage { int lo, hi; };
   std::vector<Stage> todo;
-  for (int lo = 0, step = KNN_POOL_CAP; lo < m;) {
+  for (int lo = 0, step = cap; lo < m;) {
     const long long want = (long long)lo + step;
     const int hi = want < m ? (int)want : m;
     todo.push_back({lo, hi});
@@ -1325,8 +1509,8 @@ int knn_large_candidates(vitk_ctx* h, int n, int kc, int metric, cudaStream_t st
       const size_t cnt = todo.size() - base < (size_t)KNN_MAX_STAGES ? todo.size() - base : KNN_MAX_STAGES;
       CK(e, cudaMemsetAsync(h->knn_overflow, 0, KNN_MAX_STAGES * sizeof(int), st));
       for (size_t i = 0; i < cnt; ++i)
-        if (knn_stage(h, n, kc, metric, todo[base + i].lo, todo[base + i].hi, (int)i,
-                      first_pass && base + i == 0, st))
+        if (knn_stage(h, n, kc, cap, metric, todo[base + i].lo, todo[base + i].hi, (int)i,
+                      first_pass && base + i == 0, filt, st))
           return 1;
       CK(e, cudaMemcpyAsync(h->knn_overflow_host, h->knn_overflow, KNN_MAX_STAGES * sizeof(int),
                             cudaMemcpyDeviceToHost, st));
@@ -1335,16 +1519,13 @@ int knn_large_candidates(vitk_ctx* h, int n, int kc, int metric, cudaStream_t st
         if (!h->knn_overflow_host[i]) continue;
         const Stage s = todo[base + i];
         const int rows = s.hi - s.lo;
-        if (rows <= KNN_POOL_CAP - kc) {
+        if (rows <= cap - kc) {
           e.set("vitk_knn_vote: candidate pool overflow in a %d-row stage (internal error)", rows);
           return 1;
         }
         h->knn_redo_stages += 1;
         // forget whatever the truncated stage left in the pools, keep the thresholds
-        knn_pool_select_kernel<<<n, 128, 0, st>>>(h->knn_pool, h->knn_pool_n, h->knn_thresh,
-                                                            n, kc, -1, s.lo, s.hi, nullptr, h->knn_overflow);
-        CK(e, cudaGetLastError());
-        h->launches += 1;
+        if (launch_pool_select(h, cap, n, kc, -1, s.lo, s.hi, nullptr, h->knn_overflow, st)) return 1;
         const int q4 = (rows + 3) / 4;
         for (int lo = s.lo; lo < s.hi; lo += q4) next.push_back({lo, lo + q4 < s.hi ? lo + q4 : s.hi});
       }
@@ -1353,43 +1534,40 @@ int knn_large_candidates(vitk_ctx* h, int n, int kc, int metric, cudaStream_t st
     first_pass = false;
   }
   // final select: candidates for the fp32 re-rank
-  knn_pool_select_kernel<<<n, 128, 0, st>>>(h->knn_pool, h->knn_pool_n, h->knn_thresh, n, kc,
-                                                      -1, 0, 0, h->knn_cand, h->knn_overflow);
-  CK(e, cudaGetLastError());
-  h->launches += 1;
-  return 0;
-}
-}  // namespace
-
-extern "C" int vitk_knn_vote(vitk_handle h, const float* q_dev, int n, int k, int metric,
-                             int normalise_queries, int32_t* idx_out, float* score_out,
-                             int32_t* label_out, int32_t* counts_out, void* stream) {
-  return vitk_knn_vote_masked(h, q_dev, n, k, metric, normalise_queries, nullptr, idx_out, score_out,
-                              label_out, counts_out, stream);
+  return launch_pool_select(h, cap, n, kc, -1, 0, 0, h->knn_cand, h->knn_overflow, st);
 }
 
-extern "C" int vitk_knn_vote_masked(vitk_handle h, const float* q_dev, int n, int k, int metric,
-                                    int normalise_queries, const uint8_t* row_mask_dev,
-                                    int32_t* idx_out, float* score_out, int32_t* label_out,
-                                    int32_t* counts_out, void* stream) {
-  if (!h) return 1;
+int knn_vote_impl(vitk_ctx* h, const float* q_dev, int n, int k, int metric, int normalise_queries,
+                  const uint8_t* row_mask_dev, const vitk_row_filter* rf, int32_t* idx_out,
+                  float* score_out, int32_t* label_out, int32_t* counts_out, cudaStream_t st) {
   Err& e = h->err;
   if (h->bank_m == 0) { e.set("vitk_knn_vote: no bank set"); return 1; }
   if (n == 0) return 0;
   if (!q_dev || !idx_out || !score_out || n < 0) { e.set("vitk_knn_vote: bad argument"); return 1; }
-  if (k < 1 || k > 64) { e.set("vitk_knn_vote: k=%d outside [1,64]", k); return 1; }
+  if (k < 1 || k > KNN_MAX_K) { e.set("vitk_knn_vote: k=%d outside [1,%d]", k, KNN_MAX_K); return 1; }
   if (metric != METRIC_COSINE && metric != METRIC_L2) { e.set("vitk_knn_vote: bad metric"); return 1; }
-  if (n == 0) return 0;
+  KnnFilter filt{};
+  if (rf != nullptr) {
+    if ((rf->ne_col && !rf->q_ne) || (rf->eq_col && !rf->q_eq) || (rf->rng_col && (!rf->q_lo || !rf->q_hi)) ||
+        ((rf->q_lo2 != nullptr) != (rf->q_hi2 != nullptr)) || (rf->q_lo2 && !rf->rng_col)) {
+      e.set("vitk_knn_vote_filtered: every column needs its per-query operand(s)");
+      return 1;
+    }
+    filt.ne_col = rf->ne_col; filt.q_ne = rf->q_ne; filt.eq_col = rf->eq_col; filt.q_eq = rf->q_eq;
+    filt.rng_col = rf->rng_col; filt.q_lo = rf->q_lo; filt.q_hi = rf->q_hi;
+    filt.q_lo2 = rf->q_lo2; filt.q_hi2 = rf->q_hi2; filt.rng_f32 = rf->rng_round_f32;
+    filt.active = (rf->ne_col || rf->eq_col || rf->rng_col) ? 1 : 0;
+  }
   CK(e, cudaSetDevice(h->device));
-  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const int m = h->bank_m, d = h->bank_d;
-  if (d % 4 != 0 || (size_t)d * sizeof(float) > 40 * 1024) {
-    e.set("vitk_knn_vote: d=%d must be a multiple of 4 and at most 10240", d);
+  if (d % 4 != 0 || (size_t)d * sizeof(float) > 28 * 1024) {
+    e.set("vitk_knn_vote: d=%d must be a multiple of 4 and at most 7168", d);
     return 1;
   }
   const bool large = m > KNN_DIRECT_MAX;
   const int ld = large ? 4 : (m + 3) & ~3;  // TMA row pitch must be a multiple of 16 B
-  if (n > h->knn_cap_q || ld > h->knn_cap_m) {
+  const int kc = knn_candidates_for(k, m);
+  if (n > h->knn_cap_q || ld > h->knn_cap_m || kc > h->knn_cap_kc) {
     CK(e, cudaStreamSynchronize(st));
     cudaFree(h->knn_q); cudaFree(h->knn_qb); cudaFree(h->knn_scores); cudaFree(h->knn_cand);
     h->knn_q = nullptr; h->knn_qb = nullptr; h->knn_scores = nullptr; h->knn_cand = nullptr;
@@ -1402,15 +1580,17 @@ extern "C" int vitk_knn_vote_masked(vitk_handle h, const float* q_dev, int n, in
       if (cm > top) cm = top;
       if (cm < ld) cm = ld;
     }
+    int ckc = h->knn_cap_kc > KNN_MAX_CAND ? h->knn_cap_kc : KNN_MAX_CAND;
+    if (kc > ckc) ckc = kc;
     h->knn_cap_q = 0;
     if (dev_alloc(e, &h->knn_q, (size_t)cq * d) || dev_alloc(e, &h->knn_qb, (size_t)cq * d) ||
         dev_alloc(e, &h->knn_scores, (size_t)cq * cm) ||
-        dev_alloc(e, &h->knn_cand, (size_t)cq * KNN_MAX_CAND))
+        dev_alloc(e, &h->knn_cand, (size_t)cq * ckc))
       return 1;
     h->knn_cap_q = cq;
     h->knn_cap_m = cm;
+    h->knn_cap_kc = ckc;
   }
-  const int kc = knn_candidates_for(k, m);
   prep_queries_kernel<<<(n + 7) / 8, 256, 0, st>>>(q_dev, h->knn_q, h->knn_qb, n, d,
                                                    normalise_queries);
   CK(e, cudaGetLastError());
@@ -1433,7 +1613,7 @@ extern "C" int vitk_knn_vote_masked(vitk_handle h, const float* q_dev, int n, in
   }
   if (large) {
     h->knn_pen_cur = pen;
-    const int rc = knn_large_candidates(h, n, kc, metric, st);
+    const int rc = knn_large_candidates(h, n, kc, metric, filt, st);
     h->knn_pen_cur = nullptr;
     if (rc) return 1;
   } else {
@@ -1448,19 +1628,71 @@ extern "C" int vitk_knn_vote_masked(vitk_handle h, const float* q_dev, int n, in
     const float* sc = h->knn_scores;
     const float* sq = h->bank_sqnorm;
     int32_t* cd = h->knn_cand;
-    if (m <= 256) knn_candidates_reg_kernel<8><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd, pen);
-    else if (m <= 512) knn_candidates_reg_kernel<16><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd, pen);
-    else if (m <= 1024) knn_candidates_reg_kernel<32><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd, pen);
-    else if (m <= 1536) knn_candidates_reg_kernel<48><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd, pen);
-    else knn_candidates_reg_kernel<64><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd, pen);
+    if (m <= 256) knn_candidates_reg_kernel<8><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd, pen, filt);
+    else if (m <= 512) knn_candidates_reg_kernel<16><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd, pen, filt);
+    else if (m <= 1024) knn_candidates_reg_kernel<32><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd, pen, filt);
+    else if (m <= 1536) knn_candidates_reg_kernel<48><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd, pen, filt);
+    else knn_candidates_reg_kernel<64><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd, pen, filt);
     CK(e, cudaGetLastError());
     h->launches += 2;
   }
-  knn_rerank_vote_kernel<<<n, 128, (size_t)d * sizeof(float), st>>>(
-      h->knn_q, h->bank, h->bank_classes ? h->bank_labels : nullptr, h->knn_cand, n, m, d, kc, k,
-      metric, h->bank_classes, idx_out, score_out, label_out, counts_out, row_mask_dev);
+  const int32_t* lab = h->bank_classes ? h->bank_labels : nullptr;
+  if (kc <= KNN_MAX_CAND)
+    knn_rerank_vote_kernel<<<n, 128, (size_t)d * sizeof(float), st>>>(
+        h->knn_q, h->bank, lab, h->knn_cand, n, m, d, kc, k, metric, h->bank_classes, idx_out,
+        score_out, label_out, counts_out, row_mask_dev, filt);
+  else
+    knn_rerank_sort_kernel<<<n, 256, (size_t)d * sizeof(float), st>>>(
+        h->knn_q, h->bank, lab, h->knn_cand, n, m, d, kc, k, metric, h->bank_classes, idx_out,
+        score_out, label_out, counts_out, row_mask_dev, filt);
   CK(e, cudaGetLastError());
   h->launches += 1;
+  return 0;
+}
+}  // namespace
+
+extern "C" int vitk_knn_vote(vitk_handle h, const float* q_dev, int n, int k, int metric,
+                             int normalise_queries, int32_t* idx_out, float* score_out,
+                             int32_t* label_out, int32_t* counts_out, void* stream) {
+  return vitk_knn_vote_filtered(h, q_dev, n, k, metric, normalise_queries, nullptr, nullptr, idx_out,
+                                score_out, label_out, counts_out, stream);
+}
+
+extern "C" int vitk_knn_vote_masked(vitk_handle h, const float* q_dev, int n, int k, int metric,
+                                    int normalise_queries, const uint8_t* row_mask_dev,
+                                    int32_t* idx_out, float* score_out, int32_t* label_out,
+                                    int32_t* counts_out, void* stream) {
+  return vitk_knn_vote_filtered(h, q_dev, n, k, metric, normalise_queries, row_mask_dev, nullptr,
+                                idx_out, score_out, label_out, counts_out, stream);
+}
+
+extern "C" int vitk_knn_vote_filtered(vitk_handle h, const float* q_dev, int n, int k, int metric,
+                                      int normalise_queries, const uint8_t* row_mask_dev,
+                                      const vitk_row_filter* filter, int32_t* idx_out, float* score_out,
+                                      int32_t* label_out, int32_t* counts_out, void* stream) {
+  if (!h) return 1;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (order_enter(h, st)) return 1;
+  if (knn_vote_impl(h, q_dev, n, k, metric, normalise_queries, row_mask_dev, filter, idx_out, score_out,
+                    label_out, counts_out, st))
+    return 1;
+  return order_leave(h, st);
+}
+
+extern "C" int vitk_op_merge_topk(const int32_t* idx_in_dev, const float* score_in_dev, int n, int c, int k,
+                                  int descending, int32_t* idx_out_dev, float* score_out_dev, void* stream) {
+  Err& e = g_op_err;
+  auto fail = [&]() { g_create_error = e.msg; return 1; };
+  if (n == 0) return 0;
+  if (!idx_in_dev || !score_in_dev || !idx_out_dev || !score_out_dev || n < 0 || c < 1 || c > 4096 || k < 1) {
+    e.set("vitk_op_merge_topk: need 1 <= c <= 4096 candidates per query and k >= 1 (c=%d k=%d)", c, k);
+    return fail();
+  }
+  int n2 = 32;
+  while (n2 < c) n2 <<= 1;
+  knn_merge_topk_kernel<<<n, 256, (size_t)n2 * 8, reinterpret_cast<cudaStream_t>(stream)>>>(
+      idx_in_dev, score_in_dev, n, c, k, descending, idx_out_dev, score_out_dev);
+  if (cudaGetLastError() != cudaSuccess) { e.set("vitk_op_merge_topk: launch failed"); return fail(); }
   return 0;
 }
 
@@ -1669,19 +1901,15 @@ int get_area_plan(vitk_ctx* h, int in_h, int in_w, vitk_ctx::AreaPlan** out) {
 }
 }  // namespace
 
-extern "C" int vitk_preprocess_resize_area_u8(vitk_handle h, const uint8_t* frames_dev, int n, int in_h,
-                                              int in_w, uint8_t* out_dev, void* stream) {
-  if (!h) return 1;
+namespace {
+int launch_resize_area(vitk_ctx* h, const uint8_t* frames_dev, int n, int in_h, int in_w, uint8_t* out_dev,
+                       cudaStream_t st) {
   Err& e = h->err;
-  if (n == 0) return 0;
-  if (!frames_dev || !out_dev || n < 0 || in_h < 1 || in_w < 1) { e.set("vitk_preprocess_resize_area_u8: bad argument"); return 1; }
-  if (n > 65535) { e.set("vitk_preprocess_resize_area_u8: at most 65535 frames per call"); return 1; }
   if (in_h < h->cfg.image_h || in_w < h->cfg.image_w) {
     e.set("vitk_preprocess_resize_area_u8: INTER_AREA is built for shrinking only (%dx%d -> %dx%d)", in_w, in_h,
           h->cfg.image_w, h->cfg.image_h);
     return 1;
   }
-  CK(e, cudaSetDevice(h->device));
   vitk_ctx::AreaPlan* pl = nullptr;
   if (get_area_plan(h, in_h, in_w, &pl)) return 1;
   AreaParams p;
@@ -1690,10 +1918,98 @@ extern "C" int vitk_preprocess_resize_area_u8(vitk_handle h, const uint8_t* fram
   p.out_h = h->cfg.image_h; p.out_w = h->cfg.image_w;
   p.fast_sx = pl->fast_sx; p.fast_sy = pl->fast_sy;
   p.fast_scale = pl->fast_sx > 0 ? 1.f / (float)(pl->fast_sx * pl->fast_sy) : 0.f;
-  resize_area_u8_kernel<<<dim3((unsigned)p.out_h, (unsigned)n, 1), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(p);
+  resize_area_u8_kernel<<<dim3((unsigned)p.out_h, (unsigned)n, 1), 256, 0, st>>>(p);
   CK(e, cudaGetLastError());
   h->launches += 1;
   return 0;
+}
+
+// OpenCV resizeGeneric_ coefficient tables for INTER_LINEAR on 8-bit data (float arithmetic and
+// cvRound exactly as OpenCV; oracle/preprocess_ref.linear_tab is the numpy twin)
+void build_linear_axis(int ssize, int dsize, bool clamp_fraction, std::vector<int>& idx, std::vector<int>& coef) {
+  const double scale = 1.0 / ((double)dsize / (double)ssize);
+  idx.resize(dsize);
+  coef.resize(2 * (size_t)dsize);
+  for (int d = 0; d < dsize; ++d) {
+    float f = (float)((d + 0.5) * scale - 0.5);
+    int sx = (int)std::floor(f);
+    f -= (float)sx;
+    if (clamp_fraction) {
+      if (sx < 0) { f = 0.f; sx = 0; }
+      if (sx >= ssize - 1) { f = 0.f; sx = ssize - 1; }
+    }
+    idx[d] = sx;
+    coef[2 * d] = (int)lrintf((1.f - f) * 2048.f);
+    coef[2 * d + 1] = (int)lrintf(f * 2048.f);
+  }
+}
+
+int launch_resize_linear(vitk_ctx* h, const uint8_t* frames_dev, int n, int in_h, int in_w, uint8_t* out_dev,
+                         cudaStream_t st) {
+  Err& e = h->err;
+  const int out_h = h->cfg.image_h, out_w = h->cfg.image_w;
+  auto key = std::make_pair(in_h, in_w);
+  auto it = h->linear_plans.find(key);
+  if (it == h->linear_plans.end()) {
+    std::vector<int> xs, xa, ys, ya;
+    build_linear_axis(in_w, out_w, true, xs, xa);    // x: fraction zeroed at the borders
+    build_linear_axis(in_h, out_h, false, ys, ya);   // y: rows are clamped instead
+    std::vector<int> blob;
+    blob.insert(blob.end(), xs.begin(), xs.end());
+    blob.insert(blob.end(), xa.begin(), xa.end());
+    blob.insert(blob.end(), ys.begin(), ys.end());
+    blob.insert(blob.end(), ya.begin(), ya.end());
+    int* dev = nullptr;
+    if (dev_alloc(e, &dev, blob.size())) return 1;
+    CK(e, cudaMemcpy(dev, blob.data(), blob.size() * sizeof(int), cudaMemcpyHostToDevice));
+    vitk_ctx::LinearPlan pl;
+    pl.blob = dev;
+    pl.xs = dev; pl.xa = dev + out_w; pl.ys = dev + 3 * (size_t)out_w; pl.ya = dev + 3 * (size_t)out_w + out_h;
+    it = h->linear_plans.emplace(key, pl).first;
+  }
+  LinearParams p;
+  p.in = frames_dev; p.out = out_dev;
+  p.xs = it->second.xs; p.xa = it->second.xa; p.ys = it->second.ys; p.ya = it->second.ya;
+  p.n = n; p.C = h->cfg.channels; p.in_h = in_h; p.in_w = in_w; p.out_h = out_h; p.out_w = out_w;
+  resize_linear_u8_kernel<<<dim3((unsigned)out_h, (unsigned)n, 1), 256, 0, st>>>(p);
+  CK(e, cudaGetLastError());
+  h->launches += 1;
+  return 0;
+}
+
+// interp: VITK_RESIZE_BILINEAR_AA (the HF processor), VITK_RESIZE_AREA, VITK_RESIZE_LINEAR (cv2)
+int launch_resize_interp(vitk_ctx* h, int interp, const uint8_t* in_dev, int n, int in_h, int in_w,
+                         uint8_t* out_dev, cudaStream_t st) {
+  switch (interp) {
+    case VITK_RESIZE_BILINEAR_AA: return launch_resize(h, in_dev, n, in_h, in_w, out_dev, st);
+    case VITK_RESIZE_AREA: return launch_resize_area(h, in_dev, n, in_h, in_w, out_dev, st);
+    case VITK_RESIZE_LINEAR: return launch_resize_linear(h, in_dev, n, in_h, in_w, out_dev, st);
+  }
+  h->err.set("unknown resize interpolation %d", interp);
+  return 1;
+}
+}  // namespace
+
+extern "C" int vitk_preprocess_resize_area_u8(vitk_handle h, const uint8_t* frames_dev, int n, int in_h,
+                                              int in_w, uint8_t* out_dev, void* stream) {
+  if (!h) return 1;
+  Err& e = h->err;
+  if (n == 0) return 0;
+  if (!frames_dev || !out_dev || n < 0 || in_h < 1 || in_w < 1) { e.set("vitk_preprocess_resize_area_u8: bad argument"); return 1; }
+  if (n > 65535) { e.set("vitk_preprocess_resize_area_u8: at most 65535 frames per call"); return 1; }
+  CK(e, cudaSetDevice(h->device));
+  return launch_resize_area(h, frames_dev, n, in_h, in_w, out_dev, reinterpret_cast<cudaStream_t>(stream));
+}
+
+extern "C" int vitk_preprocess_resize_linear_u8(vitk_handle h, const uint8_t* frames_dev, int n, int in_h,
+                                                int in_w, uint8_t* out_dev, void* stream) {
+  if (!h) return 1;
+  Err& e = h->err;
+  if (n == 0) return 0;
+  if (!frames_dev || !out_dev || n < 0 || in_h < 1 || in_w < 1) { e.set("vitk_preprocess_resize_linear_u8: bad argument"); return 1; }
+  if (n > 65535) { e.set("vitk_preprocess_resize_linear_u8: at most 65535 frames per call"); return 1; }
+  CK(e, cudaSetDevice(h->device));
+  return launch_resize_linear(h, frames_dev, n, in_h, in_w, out_dev, reinterpret_cast<cudaStream_t>(stream));
 }
 
 extern "C" int vitk_embed_resize_host_u8(vitk_handle h, const uint8_t* frames_host, int n, int in_h,
@@ -1705,6 +2021,7 @@ extern "C" int vitk_embed_resize_host_u8(vitk_handle h, const uint8_t* frames_ho
   if (!frames_host || !emb_host || n < 0 || in_h < 1 || in_w < 1) { e.set("vitk_embed_resize_host_u8: bad argument"); return 1; }
   CK(e, cudaSetDevice(h->device));
   cudaStream_t st = h->own_stream;
+  if (order_enter(h, st)) return 1;
   const size_t fb = (size_t)in_h * in_w * h->cfg.channels;
   const int mb = h->cfg.max_batch;
   if (h->raw_stage_bytes < fb * mb) {
@@ -1724,6 +2041,7 @@ extern "C" int vitk_embed_resize_host_u8(vitk_handle h, const uint8_t* frames_ho
     CK(e, cudaMemcpyAsync(emb_host + (size_t)off * h->D, h->emb, (size_t)cn * h->D * 4,
                           cudaMemcpyDeviceToHost, st));
   }
+  if (order_leave(h, st)) return 1;
   CK(e, cudaStreamSynchronize(st));
   return 0;
 }
@@ -1777,6 +2095,7 @@ extern "C" int vitk_hmm_decode_counts(vitk_handle h, const int32_t* counts_dev, 
   if (!counts_dev || !states_out_dev || k < 1 || k > 4096) { e.set("vitk_hmm_decode_counts: bad argument"); return 1; }
   CK(e, cudaSetDevice(h->device));
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (order_enter(h, st)) return 1;
   int T = 0;
   if (hmm_prepare(h, seq_offsets_host, n_seq, &T, st)) return 1;
   if (T == 0) return 0;
@@ -1801,6 +2120,7 @@ extern "C" int vitk_hmm_decode_counts(vitk_handle h, const int32_t* counts_dev, 
   hmm_viterbi_kernel<<<n_seq, 32, 0, st>>>(h->hmm_loge, h->hmm_offsets, n_seq, hmm_params(), h->hmm_bp,
                                            states_out_dev, dp_out_dev);
   CK(e, cudaGetLastError());
+  if (order_leave(h, st)) return 1;
   h->launches += 2;
   return 0;
 }
@@ -1850,9 +2170,6 @@ extern "C" int vitk_hmm_decode_probs_host(vitk_handle h, const double* probs_hos
 // ------------------------------------------------------------------------------------------
 // operator-level entry points
 // ------------------------------------------------------------------------------------------
-namespace {
-thread_local Err g_op_err;
-}
 
 namespace {
 int op_gemm_common(const void* a, const void* w, void* out, int M, int N, int K, int epi,
@@ -1866,10 +2183,13 @@ int op_gemm_common(const void* a, const void* w, void* out, int M, int N, int K,
     return fail();
   }
   if (M < 1 || N < 4 || N % 4) { e.set("vitk_op_gemm: bad shape M=%d N=%d", M, N); return fail(); }
-  const bool bf16_out = epi == EPI_BIAS_BF16 || epi == EPI_BIAS_GELU_BF16 || epi == EPI_BIAS_GELUT_BF16;
+  const bool is_resid = epi == EPI_BIAS_RESID_F32 || epi == EPI_BIAS_RESID_BF16;
+  const bool bf16_out = epi == EPI_BIAS_BF16 || epi == EPI_BIAS_GELU_BF16 || epi == EPI_BIAS_GELUT_BF16 ||
+                        epi == EPI_BIAS_RESID_BF16;
+  if (epi == EPI_THRESH_POOL) { e.set("vitk_op_gemm: epilogue %d is internal to the k-NN path", epi); return fail(); }
   if (bf16_out && N % 8) { e.set("vitk_op_gemm: bf16 output needs N %% 8 == 0"); return fail(); }
-  if ((bf16_out || epi == EPI_BIAS_RESID_F32) && !bias) { e.set("vitk_op_gemm: bias required"); return fail(); }
-  if (epi == EPI_BIAS_RESID_F32 && !resid) { e.set("vitk_op_gemm: resid required"); return fail(); }
+  if ((bf16_out || is_resid) && !bias) { e.set("vitk_op_gemm: bias required"); return fail(); }
+  if (is_resid && !resid) { e.set("vitk_op_gemm: resid required"); return fail(); }
   CUtensorMap ta, tb, tc, tr;
   GemmParams p{};
   p.M = M; p.N = N; p.K = K; p.bias = bias; p.table = table;
@@ -1878,15 +2198,15 @@ int op_gemm_common(const void* a, const void* w, void* out, int M, int N, int K,
     p.c1 = c1; p.stats = stats; p.stats_parts = stats_parts; p.stats_stride = 2LL * stats_parts;
     p.inv_d = 1.0f / K; p.eps = ln_eps;
   }
-  if (epi == EPI_BIAS_RESID_F32) {
-    p.xb = reinterpret_cast<__nv_bfloat16*>(xb_out); p.xb_ld = N;
+  if (is_resid) {
+    if (epi == EPI_BIAS_RESID_F32) { p.xb = reinterpret_cast<__nv_bfloat16*>(xb_out); p.xb_ld = N; }
     p.stats_out = stats_out; p.stats_out_stride = 2LL * (2 * ((N + 255) / 256));
   }
   int rc = tmap_operand(e, &ta, a, M, K, GEMM_BM) || tmap_operand(e, &tb, w, N, K, 128) ||
            tmap_output(e, &tc, out, M, N, bf16_out);
   if (!rc) {
-    if (epi == EPI_BIAS_RESID_F32 && resid != out)
-      rc = tmap_output(e, &tr, const_cast<float*>(resid), M, N, false);
+    if (is_resid && static_cast<const void*>(resid) != out)
+      rc = tmap_output(e, &tr, const_cast<float*>(resid), M, N, epi == EPI_BIAS_RESID_BF16);
     else
       tr = tc;
   }
@@ -2044,6 +2364,7 @@ extern "C" int vitk_embed_vote_host_u8(vitk_handle h, const uint8_t* frames_host
   if (h->bank_d != h->D) { e.set("bank width %d != hidden %d", h->bank_d, h->D); return 1; }
   CK(e, cudaSetDevice(h->device));
   cudaStream_t st = h->own_stream;
+  if (order_enter(h, st)) return 1;
   const size_t fb = pixel_bytes_per_frame(h->cfg, PIX_U8_NHWC);
   const int nc = h->bank_classes > 0 ? h->bank_classes : 1;
   for (int off = 0; off < n; off += h->cfg.max_batch) {
@@ -2069,6 +2390,7 @@ extern "C" int vitk_embed_vote_host_u8(vitk_handle h, const uint8_t* frames_host
       CK(e, cudaMemcpyAsync(counts_host + (size_t)off * nc, h->res_counts, (size_t)cn * nc * 4,
                             cudaMemcpyDeviceToHost, st));
   }
+  if (order_leave(h, st)) return 1;
   CK(e, cudaStreamSynchronize(st));
   return 0;
 }
@@ -2099,10 +2421,12 @@ int stream_init(vitk_ctx* h) {
 }
 }  // namespace
 
-extern "C" int vitk_stream_submit(vitk_handle h, int slot, const uint8_t* frames_host, int n, int k,
-                                  int metric, float* emb_host, int32_t* label_host,
-                                  int32_t* idx_host, float* score_host, int32_t* counts_host) {
-  if (!h) return 1;
+namespace {
+// in_h == 0: frames are already at the model's resolution; otherwise raw (n,in_h,in_w,C) frames
+// are uploaded into the slot's raw buffer and resized on the slot's stream before the forward.
+int stream_submit_impl(vitk_ctx* h, int slot, const uint8_t* frames_host, int n, int in_h, int in_w,
+                       int interp, int l2_normalise, int k, int metric, float* emb_host,
+                       int32_t* label_host, int32_t* idx_host, float* score_host, int32_t* counts_host) {
   Err& e = h->err;
   if (!h->finalized) { e.set("vitk_stream_submit: weights not finalized"); return 1; }
   if (slot < 0 || slot > 1) { e.set("vitk_stream_submit: slot must be 0 or 1"); return 1; }
@@ -2115,20 +2439,35 @@ extern "C" int vitk_stream_submit(vitk_handle h, int slot, const uint8_t* frames
     e.set("vitk_stream_submit: k=%d needs a bank of width %d and k <= 64", k, h->D);
     return 1;
   }
+  // frames already at the model's resolution need no resize whatever the caller asked for
+  const bool raw = in_h > 0 && !(in_h == h->cfg.image_h && in_w == h->cfg.image_w);
+  if (raw && (in_w < 1 || interp < 0 || interp > 2)) { e.set("vitk_stream_submit_raw: bad frame size / interpolation"); return 1; }
   CK(e, cudaSetDevice(h->device));
   if (stream_init(h)) return 1;
   vitk_ctx::StreamSlot& sl = h->slots[slot];
   if (sl.busy) { e.set("vitk_stream_submit: slot %d still in flight (call vitk_stream_wait)", slot); return 1; }
-  const size_t fb = pixel_bytes_per_frame(h->cfg, PIX_U8_NHWC);
+  const size_t fb = raw ? (size_t)in_h * in_w * h->cfg.channels : pixel_bytes_per_frame(h->cfg, PIX_U8_NHWC);
   const int nc = h->bank_classes > 0 ? h->bank_classes : 1;
-  CK(e, cudaMemcpyAsync(sl.pix, frames_host, (size_t)n * fb, cudaMemcpyHostToDevice, h->in_stream));
-  CK(e, cudaEventRecord(sl.ev_h2d, h->in_stream));
   cudaStream_t st = h->own_stream;
+  if (raw && sl.raw_bytes < fb * (size_t)h->cfg.max_batch) {
+    // the slot is idle (its last use was waited for), but own_stream may still run the OTHER
+    // slot's resize out of its own buffer: cudaFree synchronises the device anyway
+    cudaFree(sl.raw);
+    sl.raw = nullptr;
+    sl.raw_bytes = 0;
+    if (dev_alloc(e, &sl.raw, fb * (size_t)h->cfg.max_batch)) return 1;
+    sl.raw_bytes = fb * (size_t)h->cfg.max_batch;
+  }
+  if (order_enter(h, st)) return 1;
+  CK(e, cudaMemcpyAsync(raw ? sl.raw : sl.pix, frames_host, (size_t)n * fb, cudaMemcpyHostToDevice, h->in_stream));
+  CK(e, cudaEventRecord(sl.ev_h2d, h->in_stream));
   CK(e, cudaStreamWaitEvent(st, sl.ev_h2d, 0));
-  if (forward_chunk(h, sl.pix, PIX_U8_NHWC, n, sl.emb, nullptr, 1, st)) return 1;
-  if (vote && vitk_knn_vote(h, sl.emb, n, k, metric, 0, sl.idx, sl.score, sl.label, sl.counts, st))
+  if (raw && launch_resize_interp(h, interp, sl.raw, n, in_h, in_w, sl.pix, st)) return 1;
+  if (forward_chunk(h, sl.pix, PIX_U8_NHWC, n, sl.emb, nullptr, l2_normalise, st)) return 1;
+  if (vote && knn_vote_impl(h, sl.emb, n, k, metric, 0, nullptr, nullptr, sl.idx, sl.score, sl.label, sl.counts, st))
     return 1;
   CK(e, cudaEventRecord(sl.ev_done, st));
+  if (order_leave(h, st)) return 1;
   cudaStream_t so = h->out_stream;
   CK(e, cudaStreamWaitEvent(so, sl.ev_done, 0));
   CK(e, cudaMemcpyAsync(emb_host, sl.emb, (size_t)n * h->D * 4, cudaMemcpyDeviceToHost, so));
@@ -2141,6 +2480,25 @@ extern "C" int vitk_stream_submit(vitk_handle h, int slot, const uint8_t* frames
   CK(e, cudaEventRecord(sl.ev_out, so));
   sl.busy = true;
   return 0;
+}
+}  // namespace
+
+extern "C" int vitk_stream_submit(vitk_handle h, int slot, const uint8_t* frames_host, int n, int k,
+                                  int metric, float* emb_host, int32_t* label_host,
+                                  int32_t* idx_host, float* score_host, int32_t* counts_host) {
+  if (!h) return 1;
+  return stream_submit_impl(h, slot, frames_host, n, 0, 0, 0, 1, k, metric, emb_host, label_host, idx_host,
+                            score_host, counts_host);
+}
+
+extern "C" int vitk_stream_submit_raw(vitk_handle h, int slot, const uint8_t* frames_host, int n, int in_h,
+                                      int in_w, int interp, int l2_normalise, int k, int metric,
+                                      float* emb_host, int32_t* label_host, int32_t* idx_host,
+                                      float* score_host, int32_t* counts_host) {
+  if (!h) return 1;
+  if (in_h < 1 || in_w < 1) { h->err.set("vitk_stream_submit_raw: bad frame size"); return 1; }
+  return stream_submit_impl(h, slot, frames_host, n, in_h, in_w, interp, l2_normalise, k, metric, emb_host,
+                            label_host, idx_host, score_host, counts_host);
 }
 
 extern "C" int vitk_stream_wait(vitk_handle h, int slot) {

@@ -72,11 +72,14 @@ class ViTGeometry:
                    gelu_tanh=act != "gelu")
 
 
-def random_init_state_dict(geometry: "ViTGeometry", seed: int = 0) -> dict:
+def random_init_state_dict(geometry: "ViTGeometry", seed: int = 0, cls_zeros: bool = False) -> dict:
     """Random-init weights with HF ViT's initialiser statistics (modeling_vit.py:384-399:
     trunc-normal(0, 0.02) for Linear/Conv/pos-emb/CLS, zero biases, LayerNorm gamma=1 beta=0),
     keyed like the HF state dict.  Used by bench.py / smoke() — there is no network for
-    checkpoints, and the product path must not depend on transformers or the oracle."""
+    checkpoints, and the product path must not depend on transformers or the oracle.
+    cls_zeros=True: the TF backbone's TokenLayer initialises the CLS token to zeros
+    (models/vit_backbone.py:93-104) -- the state a freshly built reference TF model is in when
+    write_embeddings.py:101-109,243 saves `vit_random_weights.h5`."""
     import torch
 
     g = geometry
@@ -89,7 +92,7 @@ def random_init_state_dict(geometry: "ViTGeometry", seed: int = 0) -> dict:
         return t
 
     sd = {
-        "embeddings.cls_token": tn(1, 1, D),
+        "embeddings.cls_token": torch.zeros(1, 1, D) if cls_zeros else tn(1, 1, D),
         "embeddings.position_embeddings": tn(1, g.tokens, D),
         "embeddings.patch_embeddings.projection.weight": tn(D, C_, ps, ps),
         "embeddings.patch_embeddings.projection.bias": torch.zeros(D),
@@ -132,15 +135,53 @@ class ViTEmbedder:
                          float(g.u8_std))
         check(self.lib.vitk_create(C.byref(cfg), self.device, C.byref(self.handle)), None,
               "vitk_create")
+        self._weights = {}          # HF key -> float32 host array (what save_weights writes)
+        self._set_weights(state_dict)
+
+    def _set_weights(self, state_dict):
         for name, t in state_dict.items():
-            if name.startswith("pooler.") or name.startswith("vit.pooler."):
+            if name.startswith("vit."):
+                name = name[4:]
+            if name.startswith("pooler."):
                 continue
             a = t.detach().cpu().float().contiguous().numpy() if hasattr(t, "detach") else \
                 np.ascontiguousarray(t, dtype=np.float32)
             shape = (C.c_int64 * a.ndim)(*a.shape)
             check(self.lib.vitk_set_weight(self.handle, name.encode(), ptr(a), shape, a.ndim),
                   self.handle, f"vitk_set_weight({name})")
+            self._weights[name] = a
         check(self.lib.vitk_finalize_weights(self.handle), self.handle, "vitk_finalize_weights")
+
+    # ---- Keras-style weight files: model.save_weights(path) / model.load_weights(path) ------
+    def save_weights(self, path):
+        """`model.save_weights('vit_random_weights.h5')` (write_embeddings.py:243): every tensor
+        under its HF ViTModel state-dict key, float32, in one .npz (the container store.py also
+        uses for the banks).  HDF5 is not written: this image has no h5py, and the reference's
+        .h5 holds TF Model Garden variable names."""
+        path = str(path)
+        if path.endswith((".h5", ".hdf5", ".keras")):
+            raise VitkError("save_weights writes .npz (HF state-dict keys); HDF5 needs h5py, which is absent")
+        np.savez(path, **self._weights)
+        return path if path.endswith(".npz") else path + ".npz"
+
+    def load_weights(self, path):
+        """`model.load_weights(path)` (chroma.py:159, generate_clips_hmm.py:59): reads the .npz
+        written by save_weights (or any npz / dict keyed by HF state-dict names), re-uploads and
+        re-folds the LayerNorms.  Shapes are checked by vitk_set_weight."""
+        if isinstance(path, dict):
+            sd = path
+        else:
+            path = str(path)
+            if path.endswith((".h5", ".hdf5", ".keras")):
+                raise VitkError("load_weights reads .npz files keyed by HF ViTModel names; an HDF5 "
+                                "checkpoint of the TF model needs h5py + the Model Garden name map (absent here)")
+            z = np.load(path if path.endswith(".npz") else path + ".npz")
+            sd = {k: z[k] for k in z.files}
+        missing = set(self._weights) - {k[4:] if k.startswith("vit.") else k for k in sd}
+        if missing:
+            raise VitkError(f"load_weights: {len(missing)} tensors missing, e.g. {sorted(missing)[0]}")
+        self._set_weights(sd)
+        return self
 
     @classmethod
     def from_hf(cls, hf_model, device: int = 0, max_batch: int = 256) -> "ViTEmbedder":
@@ -196,7 +237,9 @@ class ViTEmbedder:
         """CUDA uint8 (N,H,W,C) frames of any size -> CUDA uint8 (N,image_h,image_w,C).
         interpolation="bilinear_aa": the HF processor's resize (BILINEAR, antialias, on uint8) as
         one kernel, bit-identical.  interpolation="area": cv2.INTER_AREA shrinking, the TF path's
-        front-end (generate_clips_hmm.py:392)."""
+        front-end (generate_clips_hmm.py:392).  interpolation="linear": cv2.resize's default
+        INTER_LINEAR, what extract_embeddings applies (smarter_generate_clips.py:81).  Both cv2
+        forms are byte-identical to OpenCV 4.13."""
         import torch
 
         g = self.geometry
@@ -212,6 +255,11 @@ class ViTEmbedder:
                                                           stream_ptr(stream)), self.handle,
                   "vitk_preprocess_resize_area_u8")
             return out
+        if interpolation == "linear":
+            check(self.lib.vitk_preprocess_resize_linear_u8(self.handle, ptr(frames), n, ih, iw, ptr(out),
+                                                            stream_ptr(stream)), self.handle,
+                  "vitk_preprocess_resize_linear_u8")
+            return out
         if interpolation != "bilinear_aa":
             raise VitkError(f"unknown interpolation {interpolation!r}")
         check(self.lib.vitk_preprocess_resize_u8(self.handle, ptr(frames), n, ih, iw, ptr(out),
@@ -220,33 +268,38 @@ class ViTEmbedder:
         return out
 
     # ---- host path (what hf_vit_embed_batch does) -----------------------------------------
-    def embed_frames(self, frames_np: np.ndarray, l2_normalise: bool = True) -> np.ndarray:
-        """(N,H,W,3) uint8 host frames at the model's resolution -> (N,hidden) float32 host."""
+    def embed_frames(self, frames_np: np.ndarray, l2_normalise: bool = True,
+                     interpolation: str = "bilinear_aa") -> np.ndarray:
+        """(N,H,W,3) uint8 host frames of ANY size -> (N,hidden) float32 host.  Frames that are not
+        at the model's resolution are resized on the GPU: interpolation="bilinear_aa" is the HF
+        processor's resize (hf_vit_embed_batch), "area" / "linear" are the cv2 resizes of the TF
+        scripts (generate_clips_hmm.py:392 / smarter_generate_clips.py:81)."""
         g = self.geometry
         frames_np = np.ascontiguousarray(frames_np)
         if frames_np.dtype != np.uint8:
             raise VitkError("embed_frames wants uint8")
         if frames_np.ndim != 4 or frames_np.shape[3] != g.channels:
             raise ValueError(f"frames {frames_np.shape} are not (N,H,W,{g.channels})")
-        if frames_np.shape[1:3] != (g.image_h, g.image_w):
-            # any other size: the processor's antialiased bilinear uint8 resize runs on the GPU
-            # (preprocess.cuh), bit-identical to ViTImageProcessor
-            n, ih, iw = frames_np.shape[:3]
-            out = np.empty((n, g.hidden), dtype=np.float32)
+        n = frames_np.shape[0]
+        raw = frames_np.shape[1:3] != (g.image_h, g.image_w)
+        out = np.empty((n, g.hidden), dtype=np.float32)
+        if n > self.max_batch or (raw and (interpolation != "bilinear_aa" or not l2_normalise)):
+            # the reference's 1024-frame batches (FRAME_BATCH_SIZE, ratt_write_clips_to_ragdb.py:29):
+            # stream max_batch-sized chunks so uploads / resizes / downloads overlap the forward
+            chunks = (frames_np[a:a + self.max_batch] for a in range(0, n, self.max_batch))
+            a = 0
+            for emb, *_ in self.embed_and_vote_stream(chunks, interpolation=interpolation,
+                                                      l2_normalise=l2_normalise):
+                out[a:a + emb.shape[0]] = emb
+                a += emb.shape[0]
+            return out
+        if raw:
+            # the processor's antialiased bilinear uint8 resize runs on the GPU (preprocess.cuh),
+            # bit-identical to ViTImageProcessor
+            ih, iw = frames_np.shape[1:3]
             check(self.lib.vitk_embed_resize_host_u8(self.handle, ptr(frames_np), n, ih, iw, ptr(out),
                                                      int(l2_normalise)), self.handle,
                   "vitk_embed_resize_host_u8")
-            return out
-        n = frames_np.shape[0]
-        out = np.empty((n, g.hidden), dtype=np.float32)
-        if n > self.max_batch and l2_normalise:
-            # the reference's 1024-frame batches (FRAME_BATCH_SIZE, ratt_write_clips_to_ragdb.py:29):
-            # stream max_batch-sized chunks so uploads / downloads overlap the forward
-            chunks = (frames_np[a:a + self.max_batch] for a in range(0, n, self.max_batch))
-            a = 0
-            for emb, *_ in self.embed_and_vote_stream(chunks):
-                out[a:a + emb.shape[0]] = emb
-                a += emb.shape[0]
             return out
         check(self.lib.vitk_embed_host_u8(self.handle, ptr(frames_np), n, ptr(out), int(l2_normalise)),
               self.handle, "vitk_embed_host_u8")
@@ -264,6 +317,9 @@ class ViTEmbedder:
             raise ValueError(f"frames {frames_np.shape}/{frames_np.dtype} do not match uint8 "
                              f"(N,{g.image_h},{g.image_w},{g.channels})")
         n, nc = frames_np.shape[0], max(index.n_classes, 1)
+        if k > _lib.STREAM_MAX_K:
+            raise VitkError(f"embed_and_vote: k={k} > {_lib.STREAM_MAX_K}; use BankIndex.search for larger k")
+        index.select()
         if out is None:
             out = (np.empty((n, g.hidden), np.float32), np.empty((n,), np.int32),
                    np.empty((n, k), np.int32), np.empty((n, k), np.float32),
@@ -274,16 +330,29 @@ class ViTEmbedder:
                                                ptr(counts)), self.handle, "vitk_embed_vote_host_u8")
         return emb, label, idx, score, counts
 
-    def embed_and_vote_stream(self, batches, index=None, k: int = 25, outs=None):
+    def embed_and_vote_stream(self, batches, index=None, k: int = 25, outs=None,
+                              interpolation: str = "bilinear_aa", l2_normalise: bool = True):
         """Streaming form of embed_and_vote for long frame lists (the reference's batched
         drivers: build_frame_store, ratt_write_clips_to_ragdb.py:197-209).  `batches` yields
         uint8 (n<=max_batch,H,W,C) arrays (pinned for true copy/compute overlap); results are
         yielded in order as (emb, label, idx, score, counts) host arrays, with two batches in
         flight: the upload of batch i+1 and the download of batch i-1 overlap the forward of
         batch i.  index=None (or k=0) skips the vote.  `outs`: optional pair of preallocated
-        output tuples, reused alternately (valid until the next-but-one result is produced)."""
+        output tuples, reused alternately (valid until the next-but-one result is produced).
+        Batches whose frames are not at the model's resolution (what build_frame_store feeds:
+        PIL frames at the video's size) are uploaded raw and resized on the GPU inside the same
+        overlapped pipeline (vitk_stream_submit_raw), `interpolation` as in embed_frames."""
         g = self.geometry
+        interp = {"bilinear_aa": _lib.RESIZE_BILINEAR_AA, "area": _lib.RESIZE_AREA,
+                  "linear": _lib.RESIZE_LINEAR}.get(interpolation)
+        if interp is None:
+            raise VitkError(f"unknown interpolation {interpolation!r}")
         k = int(k) if index is not None else 0
+        if k > _lib.STREAM_MAX_K:
+            raise VitkError(f"embed_and_vote_stream: k={k} > {_lib.STREAM_MAX_K}; query the index with "
+                            f"BankIndex.search (k <= {_lib.KNN_MAX_K}) instead")
+        if index is not None:
+            index.select()
         nc = max(index.n_classes, 1) if index is not None else 1
         metric = index.metric if index is not None else 0
         pending = []  # (slot, frames_ref, out, n)
@@ -296,11 +365,12 @@ class ViTEmbedder:
 
         for i, frames_np in enumerate(batches):
             frames_np = np.ascontiguousarray(frames_np)
-            if frames_np.dtype != np.uint8 or frames_np.ndim != 4 or \
-                    frames_np.shape[1:] != (g.image_h, g.image_w, g.channels):
-                raise ValueError(f"frames {frames_np.shape}/{frames_np.dtype} do not match uint8 "
-                                 f"(N,{g.image_h},{g.image_w},{g.channels})")
+            if frames_np.dtype != np.uint8 or frames_np.ndim != 4 or frames_np.shape[3] != g.channels:
+                raise ValueError(f"frames {frames_np.shape}/{frames_np.dtype} are not uint8 (N,H,W,{g.channels})")
             n = frames_np.shape[0]
+            if n > self.max_batch:
+                raise ValueError(f"a streamed batch holds at most max_batch={self.max_batch} frames, got {n}")
+            raw = frames_np.shape[1:3] != (g.image_h, g.image_w)
             slot = i & 1
             if len(pending) == 2:
                 yield finish()
@@ -312,9 +382,18 @@ class ViTEmbedder:
                        np.empty((n, kk), np.int32), np.empty((n, kk), np.float32),
                        np.empty((n, nc), np.int32))
             emb, label, idx, score, counts = out
-            check(self.lib.vitk_stream_submit(self.handle, slot, ptr(frames_np), n, k, metric,
-                                              ptr(emb), ptr(label), ptr(idx), ptr(score), ptr(counts)),
-                  self.handle, "vitk_stream_submit")
+            if index is not None:
+                index.select()      # the caller may have queried another bank between batches
+            if raw or not l2_normalise:
+                ih, iw = frames_np.shape[1:3]
+                check(self.lib.vitk_stream_submit_raw(self.handle, slot, ptr(frames_np), n, ih, iw, interp,
+                                                      int(l2_normalise), k, metric, ptr(emb), ptr(label),
+                                                      ptr(idx), ptr(score), ptr(counts)),
+                      self.handle, "vitk_stream_submit_raw")
+            else:
+                check(self.lib.vitk_stream_submit(self.handle, slot, ptr(frames_np), n, k, metric,
+                                                  ptr(emb), ptr(label), ptr(idx), ptr(score), ptr(counts)),
+                      self.handle, "vitk_stream_submit")
             pending.append((slot, frames_np, out, n))
         while pending:
             yield finish()
@@ -363,21 +442,33 @@ def hf_vit_embed_batch(frames_np):
 
 
 def extract_embeddings(vit_model, image_paths, batch_size=1024, loader=None):
-    """smarter_generate_clips.py:69-94: load + resize each path, predict in batches, stack the
-    un-normalised pre_logits.  `loader(path) -> (H,W,3) uint8` defaults to cv2 like the
-    reference (imread, BGR2RGB, INTER_AREA resize to the model resolution)."""
+    """smarter_generate_clips.py:69-94: load each path, resize to the model resolution, predict in
+    batches, stack the un-normalised pre_logits.
+
+    The reference resizes with `cv2.resize(im, (768, 432))` -- cv2's DEFAULT interpolation,
+    INTER_LINEAR (smarter_generate_clips.py:81; the other TF call sites use INTER_AREA).  Here the
+    default loader only decodes (imread + BGR2RGB, :79-80); a batch of equally sized frames is
+    uploaded raw and resized on the GPU by the INTER_LINEAR kernel (byte-identical to cv2), frames
+    of mixed sizes fall back to cv2.resize per frame.  `loader(path) -> (H,W,3) uint8` may return
+    frames of any size."""
     g = vit_model.geometry
     if loader is None:
         import cv2
 
         def loader(p):
-            f = cv2.cvtColor(cv2.imread(p), cv2.COLOR_BGR2RGB)
-            return cv2.resize(f, (g.image_w, g.image_h), interpolation=cv2.INTER_AREA)
+            return cv2.cvtColor(cv2.imread(p), cv2.COLOR_BGR2RGB)
     embs, batch = [], []
     for i, p in enumerate(image_paths):
-        batch.append(loader(p))
+        batch.append(np.asarray(loader(p)))
         if len(batch) == batch_size or i == len(image_paths) - 1:
-            out = vit_model.predict(np.array(batch), batch_size=batch_size, verbose=0)
-            embs.append(out["pre_logits"].reshape(len(batch), -1))
+            if len({b.shape for b in batch}) > 1:
+                import cv2
+                batch = [b if b.shape[:2] == (g.image_h, g.image_w) else cv2.resize(b, (g.image_w, g.image_h))
+                         for b in batch]
+            x = np.array(batch)
+            if x.dtype != np.uint8:
+                x = np.clip(x, 0, 255).astype(np.uint8)
+            out = vit_model.embed_frames(x, l2_normalise=False, interpolation="linear")
+            embs.append(out.reshape(len(batch), -1))
             batch = []
     return np.vstack(embs) if embs else np.zeros((0, g.hidden), np.float32)

@@ -94,8 +94,23 @@ def label_frames_sharded(embedder, index, frames: Sequence, k: int = 25, batch: 
 # ---------------------------------------------------------------------------------------------
 def merge_topk(idx: torch.Tensor, score: torch.Tensor, k: int, descending: bool = True):
     """Merge per-shard candidate lists: idx/score (Q, C) with GLOBAL row ids (-1 = empty slot) ->
-    (Q, k) best in (score, then lower row id) order — the same total order the kernels use."""
+    (Q, k) best in (score, then lower row id) order — the same total order the kernels use.
+    CUDA tensors go through vitk_op_merge_topk (C <= 4096); CPU tensors through torch."""
     q, c = idx.shape
+    if idx.is_cuda:
+        # the product path: one warp-sort kernel next to the re-rank kernels (csrc/knn.cuh,
+        # knn_merge_topk_kernel) -- no library sort / gather on the device
+        from . import _lib
+        lib = _lib.load()
+        idx_c = idx.to(torch.int32).contiguous()
+        score_c = score.to(torch.float32).contiguous()
+        out_idx = torch.empty((q, k), dtype=torch.int32, device=idx.device)
+        out_score = torch.empty((q, k), dtype=torch.float32, device=idx.device)
+        rc = lib.vitk_op_merge_topk(_lib.ptr(idx_c), _lib.ptr(score_c), q, c, int(k), int(bool(descending)),
+                                    _lib.ptr(out_idx), _lib.ptr(out_score), _lib.stream_ptr(None))
+        _lib.check(rc, None, "vitk_op_merge_topk")
+        return out_idx.to(idx.dtype), out_score.to(score.dtype)
+    # host tensors (the gloo tests of the sharding logic): plain torch
     big = torch.iinfo(torch.int64).max
     rid = torch.where(idx < 0, torch.full_like(idx, big, dtype=torch.int64), idx.to(torch.int64))
     key = score.to(torch.float64)

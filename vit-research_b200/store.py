@@ -78,7 +78,11 @@ def build_frame_store(frame_paths, batch_size=512, num_workers=16, store_name="t
                       embedder=None, cache_dir=None, loader=load_one_image):
     """Drop-in for build_frame_store (ratt_write_clips_to_ragdb.py:182-233): load frames with a
     thread pool, embed (L2-normalised rows, like hf_vit_embed_batch), write the memmap batch by
-    batch.  `embedder` defaults to the module-global installed by vit_research_b200.install()."""
+    batch.  `embedder` defaults to the module-global installed by vit_research_b200.install().
+    Frames arrive at the VIDEO's resolution (PIL .convert("RGB"), :197-206): each batch is
+    uploaded raw and the processor's resize runs on the GPU inside the overlapped streaming
+    pipeline (vitk_stream_submit_raw), so real frame folders take the same path as 224x224 ones.
+    (Like the reference's np.stack, a batch must hold frames of one size.)"""
     from . import embed as _embed
     emb = embedder if embedder is not None else _embed._default
     if emb is None:
