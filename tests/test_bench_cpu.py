@@ -9,7 +9,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def test_reference_arm_prints_one_json_line():
-    env = dict(os.environ, NCCL_DEBUG="VERSION")
+    env = dict(os.environ, NCCL_DEBUG="VERSION", VITK_BENCH_REF_FRAMES="8")
     r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference",
                         "--steps", "1", "--warmup", "0"], capture_output=True, text=True, env=env,
                        timeout=600, cwd=ROOT)
@@ -22,6 +22,7 @@ def test_reference_arm_prints_one_json_line():
     assert line["e2e"] == {"value": line["value"], "unit": "frames/s",
                            "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert line["gpu_launches"] == 0 and line["higher_is_better"] is True
+    assert line["steps"] >= 3          # the denominator of the speed-up is a mean of >= 3 timed steps
 
 
 def test_reference_arm_other_ranks_exit_quietly():

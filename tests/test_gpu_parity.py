@@ -242,21 +242,30 @@ def test_chroma_style_collection(v, b16, banks):
         assert all(d[i] <= d[i + 1] for i in range(24))  # ascending squared L2
     oi, od, _ = knn_ref.l2_topk_exact(q, rows, 25)
     np.testing.assert_allclose(np.array(res["distances"]), od, rtol=1e-4, atol=1e-2)
-    counts = [sum(m["label"] == n for m in res["metadatas"][0]) for n in v.LABEL_NAMES]
-    assert v.determine_class_pass2(counts)["dir"] == "left"
+    # the reference's own call shape: ids / metadatas / distances of one query (chroma.py:211-216)
+    r2 = v.determine_class_pass2(res["ids"][0], res["metadatas"][0], res["distances"][0])
+    assert r2["dir"] == "left" and abs(r2["probs"].sum() - 1) < 1e-12
+    assert v.determine_class_pass1(res["ids"][0], res["metadatas"][0], res["distances"][0])["dir"] in ("left", "pass2")
 
 
 def test_retriever_top10_cosine(v, b16):
+    """Exact cosine top-10 through a cosine-space collection (no metadata filter): the plain
+    `sims = Q @ C.T; argpartition; argsort` of ratt_chunk_retriever.py:123,144-148."""
     from oracle import knn_ref
     _, emb = b16
     rng = np.random.default_rng(5)
     cand = rng.standard_normal((5000, 768)).astype(np.float32)
     q = (cand[:40] + 2.0 * rng.standard_normal((40, 768))).astype(np.float32)
-    r = v.RattChunkRetriever(emb, cand, top_k=10)
-    got = r(q)
+    col = v.BankCollection(emb, cand, [f"c{i}" for i in range(5000)], None, space="cosine")
+    idx, dist = col.search_device(torch.from_numpy(q).cuda(), 10)
+    oi, ov, _ = knn_ref.cosine_topk(q, cand, 11)
+    safe = knn_ref.margins(ov, 10) > 1e-5
+    assert safe.sum() >= 38
+    assert np.array_equal(idx.cpu().numpy()[safe], oi[safe, :10])
+    np.testing.assert_allclose(1.0 - dist.cpu().numpy(), ov[:, :10], atol=2e-5)
     want = knn_ref.retriever_restated(q, cand, top_k=10)
-    assert got.shape == (40, 10, 768) and got.dtype == np.float32
-    np.testing.assert_allclose(got, want, atol=1e-6)
+    got = knn_ref.normalise(cand)[idx.cpu().numpy()]
+    np.testing.assert_allclose(got[safe], want[safe], atol=1e-6)
 
 
 def test_embed_then_vote_end_to_end(v, b16, banks):
@@ -345,6 +354,12 @@ def test_code_path_variants_agree():
     att2 = _fingerprint({"VITK_ATTN": "2"})
     cos = (base * att2).sum(1) / (np.linalg.norm(base, axis=1) * np.linalg.norm(att2, axis=1))
     assert cos.min() > 0.9999, cos.min()
+    # residual stream kept in bf16 in place (default) vs the fp32 master copy + bf16 copy of
+    # round 1: one bf16 rounding per residual add separates them
+    rf32 = _fingerprint({"VITK_RESID_F32": "1"})
+    cos = (base * rf32).sum(1) / (np.linalg.norm(base, axis=1) * np.linalg.norm(rf32, axis=1))
+    assert cos.min() > 0.9999, cos.min()
+    assert not np.array_equal(base, rf32)      # the switch really selects another code path
 
 
 def test_empty_and_ragged_inputs(v, b16, banks):

@@ -48,6 +48,22 @@ for name, seed, n in (("vit_b16", 0, 8), ("vit_l16_l2", 1, 4)):
                                       "fingerprint": vit_ref.weights_fingerprint(model),
                                       "torch": torch.__version__}
     print(name, "cls norm", np.linalg.norm(raw, axis=1)[:3])
+# 4. full-depth ViT-L/16 (BASELINE configs[3]: 24 layers) and the TF bank-writing geometry
+#    (patch 256 -> 4 tokens, raw pixels, CLS zeros) -- parity at the depths / shapes that are run
+model = vit_ref.build_hf_model("vit_l16", 1, randomise_ln=True)
+raw = vit_ref.hf_embed(model, vit_ref.synthetic_pixels(4, seed=1234), normalise=False)
+np.savez_compressed(f"{OUT}/vit_l16_seed1.npz", cls=raw, fingerprint=np.float64(vit_ref.weights_fingerprint(model)))
+manifest["vit_l16_seed1"] = {"n": 4, "pixel_seed": 1234, "layers": 24,
+                             "fingerprint": vit_ref.weights_fingerprint(model), "torch": torch.__version__}
+print("vit_l16 (24 layers) cls norm", np.linalg.norm(raw, axis=1))
+model = vit_ref.build_hf_model("vit_tf432_p256", 2, randomise_ln=True, cls_zeros=True)
+u8 = vit_ref.synthetic_frames_u8(4, seed=4321, size=(432, 768))
+raw = vit_ref.hf_embed(model, vit_ref.raw_pixels(u8), normalise=False)
+np.savez_compressed(f"{OUT}/vit_tf432_p256_seed2.npz", cls_u8=raw,
+                    fingerprint=np.float64(vit_ref.weights_fingerprint(model)))
+manifest["vit_tf432_p256_seed2"] = {"n": 4, "u8_seed": 4321, "tokens": 4, "cls_zeros": True,
+                                    "fingerprint": vit_ref.weights_fingerprint(model), "torch": torch.__version__}
+print("vit_tf432_p256 cls norm", np.linalg.norm(raw, axis=1))
 import transformers
 manifest["transformers"] = transformers.__version__
 json.dump(manifest, open(f"{OUT}/MANIFEST.json", "w"), indent=1, sort_keys=True)
