@@ -60,6 +60,8 @@ struct AttnParams {
   int q_rows;   // queries per frame that are needed (== S, or fewer: last-layer CLS shortcut)
   int nblk;     // query blocks per (frame, head): 1 if q_rows <= 128 else 2
   int reverse;  // v3: walk the (frame, head) units from the last to the first ("snake" order)
+  int handover; // v3: 32-column chunk of the softmax pass after which the exp2 turn passes to the
+                // other warpgroup (>= number of chunks: at the end of the pass)
   float scale_log2e;  // (1/sqrt(d)) * log2(e)
   long long* dbg;     // developer timeline (tools/dev_attn_timeline.py): null in production
 };
@@ -507,6 +509,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       tc_fence_after_sync();
       if (dbg_on) dbg[1] = clock64();
       float sum = 0.f;
+      bool handed = false;  // this warp has passed the exp2 turn on for this unit
       // exp2 of one 32- or 16-column chunk against the shift mxs -> bf16 pairs over the consumed
       // S cells; accumulates the row sum.  kClamp bounds the exponent (fast path only).
       auto exp_pass = [&](float mxs, bool clamp) {
@@ -607,6 +610,11 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         for (; c + 2 <= n32; c += 2) {  // va holds chunk c
           tmem_ld_32x32b_x32(t_slot + (c + 1) * 32, vb);
           att_exp_chunk<32>(va, c * 32, S, p.scale_log2e, mxs, s4, t_slot);
+          if (c >= p.handover && !handed) {  // early hand-over: the other group's TMEM loads can run
+            handed = true;                   // under the rest of this pass's exp2 work
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&turn_bar[g ^ 1]);
+          }
           tmem_ld_wait();
           reg_fence16(vb);
           reg_fence16(vb + 16);
@@ -660,7 +668,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       __syncwarp();
       if (lane == 0) {
         mbar_arrive(&p_full[g]);
-        mbar_arrive(&turn_bar[g ^ 1]);  // hand the exp2 units to the other warpgroup
+        if (!handed) mbar_arrive(&turn_bar[g ^ 1]);  // hand the exp2 units to the other warpgroup
       }
       if (dbg_on) dbg[3] = clock64();
 

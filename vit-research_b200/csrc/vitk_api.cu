@@ -271,6 +271,11 @@ int launch_attention(Err& e, const CUtensorMap& tq, const CUtensorMap& tkv, cons
   p.q_rows = q_rows > 0 && q_rows < S ? q_rows : S;
   p.nblk = (p.q_rows + 127) / 128;
   p.reverse = reverse;
+  {
+    static int handover = -1;  // VITK_ATTN_HANDOVER: chunk after which the exp2 turn is passed on
+    if (handover < 0) { const char* hv = getenv("VITK_ATTN_HANDOVER"); handover = hv ? atoi(hv) : 1000; if (handover < 0) handover = 0; }
+    p.handover = handover;
+  }
   p.scale_log2e = 0.125f * 1.4426950408889634f;  // head dim 64 -> 1/sqrt(64)
   p.dbg = g_attn_dbg;
   if (S > 256) {
