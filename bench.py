@@ -522,61 +522,46 @@ def run_other_config(args, rank, local_rank, world):
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic"}
     launches0 = 0
     if which == "c3":
-        # configs[2]: one hour of 30 fps video = 108 000 frames, sharded by contiguous chunk; host
-        # uint8 frames through the streaming API, top-25 vote, per-rank counts gathered, whole-game
-        # Viterbi on rank 0 (generate_clips_hmm.py:367-490).  STRONG scaling: total work is fixed.
+        # configs[2]: one hour of 30 fps video = 108 000 frames, 256-frame chunks dealt to the ranks
+        # round-robin; host uint8 frames through the streaming API, top-25 vote, vote counts
+        # all-gathered every 4 local steps, the whole-game Viterbi (generate_clips_hmm.py:367-490)
+        # advancing on rank 0 while the stream runs.  STRONG scaling: total work is fixed.
         total, B, k = 108_000, BATCH, K_NEIGHBOURS
         geom = v.ViTGeometry.vit_b16()
         t_setup = time.perf_counter()
         emb = v.ViTEmbedder(geom, v.random_init_state_dict(geom, 0), device=local_rank, max_batch=B)
         rows, labels, _ = v.load_label_banks(BANK_DIR)
         index = v.BankIndex(emb, rows, labels, 3, metric="cosine", normalise_rows=True)
-        lo, hi = v.frame_ranges(total, world)[rank]
-        n_mine = hi - lo
+        mine = v.round_robin_chunks(total, B, world)[rank]
+        n_mine = sum(b - a for _, a, b in mine)
         frames = [torch.randint(0, 256, (B, 224, 224, 3), generator=g, dtype=torch.uint8).pin_memory().numpy()
                   for _ in range(4)]
-        counts_all = torch.empty((n_mine, 3), dtype=torch.int32).pin_memory()
         outs = tuple(tuple(torch.empty(sh, dtype=dt).pin_memory().numpy() for sh, dt in
                            (((B, 768), torch.float32), ((B,), torch.int32), ((B, k), torch.int32),
                             ((B, k), torch.float32), ((B, 3), torch.int32))) for _ in range(2))
-        counts_dev = torch.empty((n_mine, 3), dtype=torch.int32, device="cuda")
-        ranges = v.frame_ranges(total, world)
-        parts = [torch.empty((r[1] - r[0], 3), dtype=torch.int32, device="cuda") for r in ranges] if world > 1 else None
         t_setup = time.perf_counter() - t_setup
         launches0 = emb.launch_count
-
-        def batches(n):
-            for i, a in enumerate(range(0, n, B)):
-                yield frames[i % 4][: min(B, n - a)]
-
         phases = {}
 
-        def run(n):
+        def run(n_total):
+            """The whole game: chunks dealt round-robin, the Viterbi lattice advancing on rank 0
+            while the stream runs (shard.label_and_smooth_stream)."""
+            st = {}
             t0 = time.perf_counter()
-            a = 0
-            cn = counts_all.numpy()
-            for e, lab, idx, sc, cnt in emb.embed_and_vote_stream(batches(n), index, k, outs=outs):
-                cn[a:a + len(lab)] = cnt
-                a += len(lab)
+            states, _labels = v.label_and_smooth_stream(
+                emb, index, lambda a, b: frames[(a // B) % 4][: b - a], n_total, k=k, chunk=B,
+                gather_every=4, stats=st, outs=outs)
             t1 = time.perf_counter()
-            counts_dev[:n].copy_(counts_all[:n], non_blocking=True)
-            c = counts_dev[:n]
-            if world > 1 and n == n_mine:
-                dist.all_gather(parts, c)
-                c = torch.cat(parts)
             torch.cuda.synchronize()
             t2 = time.perf_counter()
-            states = v.viterbi_from_counts(emb, c, k) if rank == 0 else None
-            torch.cuda.synchronize()
-            t3 = time.perf_counter()
-            phases.update(stream_s=t1 - t0, gather_s=t2 - t1, viterbi_s=t3 - t2)
+            phases.update(stream_s=t1 - t0, gather_s=st.get("wait_s", 0.0), viterbi_s=t2 - t1)
             return states
 
-        run(4 * B)                                   # warm-up on a short prefix
+        run(8 * B * world)                           # warm-up on a short prefix
         barrier()
         with ClockSampler(local_rank) as clk:
             t0 = time.perf_counter()
-            states = run(n_mine)
+            states = run(total)
             barrier()
             dt = sync_max(time.perf_counter() - t0)
         ph = torch.tensor([phases["stream_s"], phases["gather_s"], phases["viterbi_s"], t_setup], device="cuda", dtype=torch.float64)
@@ -591,16 +576,18 @@ def run_other_config(args, rank, local_rank, world):
             "metric": "frames/sec ViT-B/16@224 embed+kNN+Viterbi, 108k-frame stream", "value": fps, "steps": steps,
             "ms_per_step": dt * 1e3 / steps, "scaling": "strong",
             "config": {"workload": "configs[2]: ViT-B/16 224x224 bf16, synthetic 1-hour 30 fps stream (108 000 frames) "
-                                   "sharded by contiguous chunk, host uint8 frames, embed + cosine top-25 vote + "
-                                   "3-state Viterbi over the whole game on rank 0",
+                                   "sharded by chunk, host uint8 frames, embed + cosine top-25 vote + "
+                                   "3-state Viterbi over the whole game (lattice advanced on rank 0 during the stream)",
                        "frames": total, "frames_per_step_per_gpu": B, "k": k,
                        "l2_flush": "every batch is a fresh 38.5 MB host upload; ~0.9 GB of activations per step",
-                       "parallelism": f"dp{world} by contiguous frame range; one all_gather of (T,3) vote counts"},
+                       "parallelism": f"dp{world}: 256-frame chunks dealt round-robin; all_gather of the vote counts every "
+                                      "4 local steps feeds the streamed Viterbi on rank 0 while the stream runs"},
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": B * 224 * 224 * 3,
                     "d2h_bytes_per_step": sum(a.nbytes for a in outs[0]), "seconds": dt,
-                    "per_rank": [{"rank": r, "stream_s": round(float(allp[r, 0]), 4), "gather_s": round(float(allp[r, 1]), 4),
-                                  "viterbi_s": round(float(allp[r, 2]), 4), "setup_s_untimed": round(float(allp[r, 3]), 2)}
-                                 for r in range(world)]},
+                    "per_rank": [{"rank": r, "stream_and_smooth_s": round(float(allp[r, 0]), 4),
+                                  "of_which_waiting_for_results_s": round(float(allp[r, 1]), 4),
+                                  "tail_after_last_chunk_s": round(float(allp[r, 2]), 4),
+                                  "setup_s_untimed": round(float(allp[r, 3]), 2)} for r in range(world)]},
             "clocks": clk.summary(),
             "decoded_frames": int((states >= 0).sum()) if states is not None else None,
             "roofline": {"kernel": "whole stream (dense bf16 tensor work of the ViT-B forward)", "bound": "tensor",

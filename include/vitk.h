@@ -255,6 +255,18 @@ int vitk_stream_submit_raw(vitk_handle h, int slot, const uint8_t* frames_host, 
 int vitk_hmm_decode_counts(vitk_handle h, const int32_t* counts_dev, int k,
                            const int32_t* seq_offsets_host, int n_seq, int32_t* states_out_dev,
                            double* dp_out_dev, void* stream);
+/* Streamed form for ONE long sequence whose vote counts arrive segment by segment in time order
+ * (a game sharded over several GPUs by chunk: the lattice advances while the stream is still being
+ * embedded, instead of after it).  begin(capacity) opens a stream; append_counts consumes the next
+ * n frames (counts_dev (n,3) int32, same k throughout) and carries the lattice column over;
+ * finish writes the states of all T frames consumed (same conventions as above) and closes the
+ * stream.  Any segmentation yields bit for bit the states of vitk_hmm_decode_counts on the whole
+ * sequence.  These calls use their own buffers and are NOT ordered against the forward: they may
+ * run on any stream beside vitk_stream_submit; consecutive appends must be issued on one stream
+ * (or on streams ordered by the caller). */
+int vitk_hmm_stream_begin(vitk_handle h, long long capacity_frames);
+int vitk_hmm_stream_append_counts(vitk_handle h, const int32_t* counts_dev, int n, int k, void* stream);
+int vitk_hmm_stream_finish(vitk_handle h, int32_t* states_out_dev, long long* frames_out, void* stream);
 /* Same for arbitrary per-frame probabilities (T,3) float64 on the host (the dicts handed to
  * add_first / add_col_to_lattice); outputs on the host; synchronous. */
 int vitk_hmm_decode_probs_host(vitk_handle h, const double* probs_host,

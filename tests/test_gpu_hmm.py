@@ -96,3 +96,48 @@ def test_hour_long_stream_matches_oracle(v, emb):
     got, dp = v.viterbi_from_counts(emb, torch.from_numpy(counts).cuda(), k, return_dp=True)
     assert np.array_equal(got.cpu().numpy(), want)
     assert np.array_equal(dp.cpu().numpy(), want_dp)
+
+
+def test_streamed_viterbi_equals_one_shot_in_any_segmentation(v, emb):
+    """vitk_hmm_stream_*: a sequence decoded while its counts arrive in ragged pieces gives bit for
+    bit the states of the one-shot kernel (itself pinned on the reference's own class) -- T = 1, 2,
+    3 and a long stream cut at random points, including single-frame and empty pieces."""
+    rng = np.random.default_rng(5)
+    for T in (1, 2, 3, 17, 5000):
+        side = np.repeat(rng.integers(0, 3, T // 40 + 1), 40)[:T]
+        counts = np.zeros((T, 3), np.int32)
+        for t in range(T):
+            c = rng.multinomial(25, [0.8 if j == side[t] else 0.1 for j in range(3)])
+            counts[t] = c
+        dev = torch.from_numpy(counts).cuda()
+        want = v.viterbi_from_counts(emb, dev, 25).cpu().numpy()
+        for cuts in ([], [1], list(np.sort(rng.integers(0, T + 1, 9)))):
+            vs = v.ViterbiStream(emb, T, 25)
+            edges = [0] + [int(c) for c in cuts if 0 <= c <= T] + [T]
+            for a, b in zip(edges[:-1], edges[1:]):
+                vs.append(dev[a:b])
+            got = vs.finish().cpu().numpy()
+            assert np.array_equal(got, want), (T, cuts)
+    with pytest.raises(v.VitkError):
+        vs = v.ViterbiStream(emb, 4, 25)
+        vs.append(torch.zeros((5, 3), dtype=torch.int32, device="cuda"))
+
+
+def test_label_and_smooth_stream_equals_label_then_decode(v, emb, banks):
+    """shard.label_and_smooth_stream (BASELINE configs[2], single process): chunks streamed through
+    the overlapped host API with the Viterbi lattice advancing during the stream == embed + vote of
+    all frames followed by one decode."""
+    from oracle import vit_ref
+    rows, labels = banks
+    index = v.BankIndex(emb, rows, labels, 3, metric="l2")
+    frames = vit_ref.synthetic_frames_u8(61, seed=4)              # max_batch 8: 7 full chunks + 5 frames
+    states, lab = v.label_and_smooth_stream(emb, index, lambda a, b: frames[a:b], len(frames), k=25,
+                                            chunk=8, gather_every=3)
+    _e, want_lab, _i, _s, want_cnt = emb.embed_and_vote(frames[:8], index, 25)
+    all_cnt, all_lab = [], []
+    for a in range(0, 61, 8):
+        _e, l, _i, _s, c = emb.embed_and_vote(frames[a:a + 8], index, 25)
+        all_cnt.append(c.copy()); all_lab.append(l.copy())
+    want_states = v.viterbi_from_counts(emb, torch.from_numpy(np.concatenate(all_cnt)).cuda(), 25)
+    assert np.array_equal(lab, np.concatenate(all_lab))
+    assert torch.equal(states, want_states)

@@ -140,3 +140,26 @@ def test_sharded_store_exchange_over_gloo(world):
         p.join(60)
         assert p.exitcode == 0
     assert sorted(res) == [(r, True) for r in range(world)]
+
+
+def test_round_robin_chunks_cover_the_stream_in_time_order():
+    """shard.round_robin_chunks / time_order_of_round (the sharding of BASELINE configs[2]): every
+    frame belongs to exactly one rank, and replaying the gathers in rounds visits the chunks in
+    time order with the right ragged tail -- for even, ragged and tiny streams."""
+    for n, chunk, world, every in [(108_000, 256, 8, 4), (1000, 256, 3, 2), (5, 4, 4, 3), (0, 8, 2, 1), (256, 256, 1, 4)]:
+        per_rank = shard.round_robin_chunks(n, chunk, world)
+        seen = sorted((b, a, e) for r in per_rank for b, a, e in r)
+        assert [x[0] for x in seen] == list(range(len(seen)))
+        assert sum(e - a for _, a, e in seen) == n
+        for r, lst in enumerate(per_rank):
+            assert all(b % world == r for b, _, _ in lst)
+        rounds = ((n + chunk - 1) // chunk + world - 1) // world
+        pos, s = 0, 0
+        while s < rounds:
+            steps = min(every, rounds - s)
+            for r, g, valid in shard.time_order_of_round(n, chunk, world, s, steps):
+                b, a, e = per_rank[r][s + g]
+                assert a == pos and e - a == valid       # contiguous prefix in time
+                pos = e
+            s += steps
+        assert pos == n

@@ -12,8 +12,9 @@ from .knn import (BankClient, BankCollection, BankIndex, FrameRetriever, RattChu
                   LABEL_NAMES, determine_class, classify_stream_with_upserts, match_where,
                   one_hot_metadata, vote_from_counts)
 from . import hmm as hmm_module  # noqa: F401,E402
-from .hmm import hmm, viterbi_from_counts, viterbi_from_probs  # noqa: F401,E402
+from .hmm import ViterbiStream, hmm, viterbi_from_counts, viterbi_from_probs  # noqa: F401,E402
 from . import store  # noqa: F401,E402
 from .chunk_encoder import ChunkEncoder  # noqa: F401,E402
 from . import shard  # noqa: F401,E402
-from .shard import frame_ranges, gather_frames, label_frames_sharded  # noqa: F401,E402
+from .shard import (frame_ranges, gather_frames, label_and_smooth_stream, label_frames_sharded,
+                    round_robin_chunks)  # noqa: F401,E402

@@ -89,6 +89,9 @@ SIGNATURES = {
     "vitk_bank_rows": (_i, [_vp]),
     "vitk_hmm_decode_counts": (_i, [_vp, _vp, _i, _vp, _i, _vp, _vp, _vp]),
     "vitk_hmm_decode_probs_host": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
+    "vitk_hmm_stream_begin": (_i, [_vp, C.c_longlong]),
+    "vitk_hmm_stream_append_counts": (_i, [_vp, _vp, _i, _i, _vp]),
+    "vitk_hmm_stream_finish": (_i, [_vp, _vp, C.POINTER(C.c_longlong), _vp]),
     "vitk_op_gemm": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _i, _vp]),
     "vitk_op_gemm_fused": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _i, _f, _vp, _vp, _vp, _vp]),
     "vitk_op_rowstats": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),

@@ -107,6 +107,92 @@ hmm_viterbi_kernel(const double* __restrict__ loge, const int* __restrict__ offs
   }
 }
 
+// The same recursion for a sequence that ARRIVES IN PIECES (a stream sharded over several GPUs
+// delivers its vote counts segment by segment, in time order): one launch per segment continues
+// from the lattice column the previous launch left in `carry` -- carry[0..2] = the last column,
+// carry[3..5] = the one before it (decode_sequence starts from column T-1, known only at the
+// end).  Frame t is lattice column t+1; `t0` frames were consumed before this segment.  The
+// arithmetic per step is the code above, so a stream decoded in any segmentation is bit-identical
+// to the one-shot kernel.
+__global__ void __launch_bounds__(32)
+hmm_viterbi_segment_kernel(const double* __restrict__ loge, long long t0, int n, HmmParams hp,
+                           double* __restrict__ carry, int8_t* __restrict__ bp) {
+  const int lane = threadIdx.x;
+  const int s = lane < 3 ? lane : 2;
+  if (n <= 0) return;
+  double dp, prev;
+  int i = 0;
+  if (t0 == 0) {
+    dp = hp.log_third + loge[s];        // add_first: not rounded
+    prev = dp;
+    i = 1;
+  } else {
+    dp = carry[s];
+    prev = carry[3 + s];
+  }
+  for (; i < n; ++i) {
+    const double pl = __shfl_sync(0xffffffffu, dp, 0);
+    const double pr = __shfl_sync(0xffffffffu, dp, 1);
+    const double pn = __shfl_sync(0xffffffffu, dp, 2);
+    const double em = loge[(size_t)i * 3 + s];
+    double best;
+    int from;
+    if (s == 0) {
+      const double a = (pl + hp.log_stay) + em, b = (pn + hp.log_from_none) + em;
+      best = fmax(a, b);
+      from = a > b ? 0 : 2;
+    } else if (s == 1) {
+      const double a = (pr + hp.log_stay) + em, b = (pn + hp.log_from_none) + em;
+      best = fmax(a, b);
+      from = a > b ? 1 : 2;
+    } else {
+      const double a = (pl + hp.log_to_none) + em, b = (pr + hp.log_to_none) + em,
+                   d = (pn + hp.log_none_none) + em;
+      best = fmax(a, fmax(b, d));
+      from = (a >= b && a >= d) ? 0 : (b >= d ? 1 : 2);
+    }
+    prev = dp;
+    dp = py_round3(best);
+    if (lane < 3) bp[((size_t)t0 + i) * 3 + s] = (int8_t)from;
+  }
+  if (lane < 3) {
+    carry[s] = dp;
+    carry[3 + s] = prev;
+  }
+}
+
+// decode_sequence of a streamed lattice of T frames (see hmm_viterbi_kernel for the reference's
+// conventions: start at column T-1, backpointers read one column off, entries 0 and 1 stay -1).
+__global__ void __launch_bounds__(32)
+hmm_backtrace_kernel(const int8_t* __restrict__ bp, long long T, const double* __restrict__ carry,
+                     int32_t* __restrict__ out) {
+  if (threadIdx.x != 0 || T <= 0) return;
+  out[0] = -1;
+  if (T > 1) out[1] = -1;
+  int cur = 0;
+  if (T >= 2) {   // np.argmax over column T-1 (first maximum wins); for T == 2 that is the first column
+    const double a = carry[3], b = carry[4], d = carry[5];
+    cur = (a >= b && a >= d) ? 0 : (b >= d ? 1 : 2);
+  }
+  for (long long i = T - 1; i >= 2; --i) {
+    out[i] = cur;
+    cur = (i - 1 >= 2 && cur >= 0) ? bp[(size_t)(i - 2) * 3 + cur] : -1;
+  }
+}
+
+// Emissions of one streamed segment: frame t0 + i; only global frame 0 takes the first-column rule.
+__global__ void __launch_bounds__(256)
+hmm_emission_segment_kernel(const int32_t* __restrict__ counts, long long t0, int n, int k,
+                            const double* __restrict__ table, double* __restrict__ loge) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < (long long)n * 3;
+       i += (long long)gridDim.x * blockDim.x) {
+    int c = counts[i];
+    c = c < 0 ? 0 : (c > k ? k : c);
+    const bool first = t0 == 0 && i < 3;
+    loge[i] = table[(first ? 0 : k + 1) + c];
+  }
+}
+
 // counts [T,3] (left,right,none votes among k neighbours) -> log emissions.  With static one-hot
 // banks the reference's lmean/rmean/nmean are count/k (generate_clips_hmm.py:188-224), so the
 // emission takes one of k+1 values: table[0][c] = log(c/k + 1e-6) feeds a sequence's first

@@ -486,6 +486,11 @@ struct vitk_ctx {
   int8_t* hmm_bp = nullptr;
   int* hmm_offsets = nullptr;
   int hmm_cap_t = 0, hmm_cap_seq = 0, hmm_cap_k = -1;
+  // streamed Viterbi (vitk_hmm_stream_*): its own buffers, so it may run beside the forward
+  double *hs_loge = nullptr, *hs_carry = nullptr;
+  int8_t* hs_bp = nullptr;
+  long long hs_cap = 0, hs_t = -1;   // hs_t < 0: no stream open
+  int hs_seg_cap = 0;
   // several banks per handle (vitk_bank_new / vitk_bank_select): the fields above are the
   // CURRENT bank, the others are parked here
   struct BankState {
@@ -614,6 +619,7 @@ void free_ctx(vitk_ctx* c) {
   cudaFree(c->knn_pool); cudaFree(c->knn_pool_n); cudaFree(c->knn_thresh); cudaFree(c->knn_overflow);
   if (c->knn_overflow_host) cudaFreeHost(c->knn_overflow_host);
   cudaFree(c->hmm_loge); cudaFree(c->hmm_table); cudaFree(c->hmm_bp); cudaFree(c->hmm_offsets);
+  cudaFree(c->hs_loge); cudaFree(c->hs_carry); cudaFree(c->hs_bp);
   for (auto& kv : c->resize_plans) cudaFree(kv.second.blob);
   for (auto& kv : c->area_plans) cudaFree(kv.second.blob);
   for (auto& kv : c->linear_plans) cudaFree(kv.second.blob);
@@ -2089,7 +2095,95 @@ int hmm_prepare(vitk_ctx* h, const int32_t* seq_offsets_host, int n_seq, int* to
   *total = T;
   return 0;
 }
+// emission table on the host: std::log is the libm CPython's math.log calls
+int hmm_ensure_table(vitk_ctx* h, int k, cudaStream_t st) {
+  Err& e = h->err;
+  if (h->hmm_cap_k == k) return 0;
+  std::vector<double> tab(2 * ((size_t)k + 1));
+  for (int c = 0; c <= k; ++c) {
+    const double p = (double)c / (double)k;
+    tab[c] = std::log(p + 0.000001);                       // hmm.py:36-38
+    tab[(size_t)k + 1 + c] = std::log(c == 0 ? 0.000001 : p);  // hmm.py:45-50
+  }
+  CK(e, cudaDeviceSynchronize());   // a streamed decode on another stream may still read the old table
+  cudaFree(h->hmm_table);
+  h->hmm_table = nullptr;
+  if (dev_alloc(e, &h->hmm_table, tab.size())) return 1;
+  CK(e, cudaMemcpy(h->hmm_table, tab.data(), tab.size() * sizeof(double), cudaMemcpyHostToDevice));
+  h->hmm_cap_k = k;
+  return 0;
+}
 }  // namespace
+
+// ---- streamed form: a sequence whose vote counts arrive segment by segment, in time order -------
+extern "C" int vitk_hmm_stream_begin(vitk_handle h, long long capacity_frames) {
+  if (!h) return 1;
+  Err& e = h->err;
+  if (capacity_frames < 1) { e.set("vitk_hmm_stream_begin: capacity must be >= 1 frame"); return 1; }
+  CK(e, cudaSetDevice(h->device));
+  if (capacity_frames > h->hs_cap) {
+    CK(e, cudaDeviceSynchronize());
+    cudaFree(h->hs_bp);
+    h->hs_bp = nullptr;
+    h->hs_cap = 0;
+    if (dev_alloc(e, &h->hs_bp, (size_t)capacity_frames * 3)) return 1;
+    h->hs_cap = capacity_frames;
+  }
+  if (!h->hs_carry && dev_alloc(e, &h->hs_carry, (size_t)8)) return 1;
+  h->hs_t = 0;
+  return 0;
+}
+
+extern "C" int vitk_hmm_stream_append_counts(vitk_handle h, const int32_t* counts_dev, int n, int k,
+                                             void* stream) {
+  if (!h) return 1;
+  Err& e = h->err;
+  if (h->hs_t < 0) { e.set("vitk_hmm_stream_append_counts: no stream open (call vitk_hmm_stream_begin)"); return 1; }
+  if (n == 0) return 0;
+  if (!counts_dev || n < 0 || k < 1 || k > 4096) { e.set("vitk_hmm_stream_append_counts: bad argument"); return 1; }
+  if (h->hs_t + n > h->hs_cap) {
+    e.set("vitk_hmm_stream_append_counts: %lld + %d frames exceed the capacity %lld given to begin", h->hs_t, n, h->hs_cap);
+    return 1;
+  }
+  CK(e, cudaSetDevice(h->device));
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (hmm_ensure_table(h, k, st)) return 1;
+  if (n > h->hs_seg_cap) {
+    CK(e, cudaDeviceSynchronize());
+    cudaFree(h->hs_loge);
+    h->hs_loge = nullptr;
+    h->hs_seg_cap = 0;
+    const int cap = n < 4096 ? 4096 : n;
+    if (dev_alloc(e, &h->hs_loge, (size_t)cap * 3)) return 1;
+    h->hs_seg_cap = cap;
+  }
+  const int blocks = (n * 3 + 255) / 256;
+  hmm_emission_segment_kernel<<<blocks < 64 ? blocks : 64, 256, 0, st>>>(counts_dev, h->hs_t, n, k, h->hmm_table,
+                                                                     h->hs_loge);
+  CK(e, cudaGetLastError());
+  hmm_viterbi_segment_kernel<<<1, 32, 0, st>>>(h->hs_loge, h->hs_t, n, hmm_params(), h->hs_carry, h->hs_bp);
+  CK(e, cudaGetLastError());
+  h->hs_t += n;
+  h->launches += 2;
+  return 0;
+}
+
+extern "C" int vitk_hmm_stream_finish(vitk_handle h, int32_t* states_out_dev, long long* frames_out,
+                                      void* stream) {
+  if (!h) return 1;
+  Err& e = h->err;
+  if (h->hs_t < 0) { e.set("vitk_hmm_stream_finish: no stream open"); return 1; }
+  if (frames_out) *frames_out = h->hs_t;
+  const long long T = h->hs_t;
+  h->hs_t = -1;
+  if (T == 0) return 0;
+  if (!states_out_dev) { e.set("vitk_hmm_stream_finish: states_out is NULL"); return 1; }
+  CK(e, cudaSetDevice(h->device));
+  hmm_backtrace_kernel<<<1, 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(h->hs_bp, T, h->hs_carry, states_out_dev);
+  CK(e, cudaGetLastError());
+  h->launches += 1;
+  return 0;
+}
 
 extern "C" int vitk_hmm_decode_counts(vitk_handle h, const int32_t* counts_dev, int k,
                                       const int32_t* seq_offsets_host, int n_seq,
@@ -2104,21 +2198,7 @@ extern "C" int vitk_hmm_decode_counts(vitk_handle h, const int32_t* counts_dev, 
   int T = 0;
   if (hmm_prepare(h, seq_offsets_host, n_seq, &T, st)) return 1;
   if (T == 0) return 0;
-  if (h->hmm_cap_k != k) {
-    // emission table on the host: std::log is the libm CPython's math.log calls
-    std::vector<double> tab(2 * ((size_t)k + 1));
-    for (int c = 0; c <= k; ++c) {
-      const double p = (double)c / (double)k;
-      tab[c] = std::log(p + 0.000001);                       // hmm.py:36-38
-      tab[(size_t)k + 1 + c] = std::log(c == 0 ? 0.000001 : p);  // hmm.py:45-50
-    }
-    CK(e, cudaStreamSynchronize(st));
-    cudaFree(h->hmm_table);
-    h->hmm_table = nullptr;
-    if (dev_alloc(e, &h->hmm_table, tab.size())) return 1;
-    CK(e, cudaMemcpy(h->hmm_table, tab.data(), tab.size() * sizeof(double), cudaMemcpyHostToDevice));
-    h->hmm_cap_k = k;
-  }
+  if (hmm_ensure_table(h, k, st)) return 1;
   hmm_emission_from_counts_kernel<<<n_seq, 256, 0, st>>>(counts_dev, h->hmm_offsets, n_seq, k,
                                                          h->hmm_table, h->hmm_loge);
   CK(e, cudaGetLastError());

@@ -43,6 +43,43 @@ def viterbi_from_counts(embedder_or_handle, counts, k, seq_offsets=None, return_
     return (states, dp) if return_dp else states
 
 
+class ViterbiStream:
+    """One long sequence decoded while its vote counts still arrive (vitk_hmm_stream_*): the
+    lattice of hmm.py:5-135 advances segment by segment, so a game sharded over several GPUs is
+    smoothed DURING the stream instead of after it.  Any segmentation gives bit for bit the
+    states of viterbi_from_counts on the whole sequence."""
+
+    def __init__(self, embedder_or_handle, capacity_frames, k):
+        self.lib = _lib.load()
+        self.handle = getattr(embedder_or_handle, "handle", embedder_or_handle)
+        self.k = int(k)
+        self.frames = 0
+        check(self.lib.vitk_hmm_stream_begin(self.handle, int(capacity_frames)), self.handle,
+              "vitk_hmm_stream_begin")
+
+    def append(self, counts, stream=None):
+        """counts: CUDA int32 (n,3) votes of the NEXT n frames in time order."""
+        import torch
+        if not counts.is_cuda or counts.dtype != torch.int32 or counts.dim() != 2 or counts.shape[1] != 3:
+            raise VitkError("ViterbiStream.append() wants a CUDA int32 (n,3) tensor")
+        counts = counts.contiguous()
+        check(self.lib.vitk_hmm_stream_append_counts(self.handle, ptr(counts), counts.shape[0], self.k,
+                                                     stream_ptr(stream)), self.handle,
+              "vitk_hmm_stream_append_counts")
+        self.frames += counts.shape[0]
+        self._keep = counts          # alive until the next call on the same stream
+
+    def finish(self, device=None, stream=None):
+        """States of every frame appended, CUDA int32 (T,) in {0,1,2,-1}."""
+        import ctypes as C
+        import torch
+        states = torch.full((self.frames,), -1, dtype=torch.int32, device=device or "cuda")
+        n = C.c_longlong(0)
+        check(self.lib.vitk_hmm_stream_finish(self.handle, ptr(states) if self.frames else None, C.byref(n),
+                                              stream_ptr(stream)), self.handle, "vitk_hmm_stream_finish")
+        return states
+
+
 def viterbi_from_probs(embedder_or_handle, probs, seq_offsets=None, return_dp=False):
     """probs: host (T,3) float64 [left,right,none].  Returns numpy int32 (T,) states (and dp)."""
     lib = _lib.load()

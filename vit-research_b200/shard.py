@@ -89,6 +89,106 @@ def label_frames_sharded(embedder, index, frames: Sequence, k: int = 25, batch: 
 
 
 # ---------------------------------------------------------------------------------------------
+# One long game sharded BY CHUNK with the smoother running during the stream (BASELINE configs[2])
+# ---------------------------------------------------------------------------------------------
+def round_robin_chunks(n_frames: int, chunk: int, world: int) -> List[List[Tuple[int, int, int]]]:
+    """Chunks of `chunk` consecutive frames dealt to the ranks in turn: chunk b = frames
+    [b*chunk, min((b+1)*chunk, n_frames)) belongs to rank b % world.  Returns, per rank, its
+    (chunk index, start, stop) list in time order.  After every rank has finished its s-th chunk the
+    frames [0, (s+1)*world*chunk) are complete -- a contiguous prefix in time, which is what lets
+    the sequential Viterbi smoother (nba_proj/hmm.py) advance while the stream is still running."""
+    if n_frames < 0 or chunk < 1 or world < 1:
+        raise ValueError("need n_frames >= 0, chunk >= 1 and world >= 1")
+    out: List[List[Tuple[int, int, int]]] = [[] for _ in range(world)]
+    n_chunks = (n_frames + chunk - 1) // chunk
+    for b in range(n_chunks):
+        out[b % world].append((b, b * chunk, min((b + 1) * chunk, n_frames)))
+    return out
+
+
+def time_order_of_round(n_frames: int, chunk: int, world: int, first_step: int, steps: int):
+    """For an all-gather of every rank's local steps [first_step, first_step + steps): the
+    (rank, local step offset, valid frames) triples in TIME order, skipping chunks past the end."""
+    n_chunks = (n_frames + chunk - 1) // chunk
+    order = []
+    for g in range(steps):
+        for r in range(world):
+            b = (first_step + g) * world + r
+            if b < n_chunks:
+                order.append((r, g, min(chunk, n_frames - b * chunk)))
+    return order
+
+
+def label_and_smooth_stream(embedder, index, load_chunk: Callable, n_frames: int, k: int = 25,
+                            chunk: int | None = None, gather_every: int = 4, stats: dict | None = None,
+                            outs=None):
+    """Embed + vote + Viterbi-smooth ONE long frame sequence on all ranks (the per-frame loop of
+    generate_clips_hmm.py:367-490 for a whole game).  Chunks of `chunk` frames are dealt to the
+    ranks round-robin (round_robin_chunks); each rank streams its chunks through the overlapped
+    host API; every `gather_every` local steps the ranks all-gather those steps' (chunk,3) vote
+    counts (NCCL / gloo: 3 KB per chunk) and rank 0 feeds them, in time order, to the streamed
+    Viterbi (ViterbiStream), which therefore finishes a few milliseconds after the last chunk
+    instead of after a serial pass over the whole game.
+    load_chunk(start, stop) -> uint8 (stop-start, H, W, C) frames (any size; pinned for overlap).
+    `outs`: optional pair of preallocated (pinned) output tuples for embed_and_vote_stream.
+    Returns (states CUDA int32 (n_frames,) on rank 0 else None, labels of this rank's frames)."""
+    import torch.distributed as dist
+    from .hmm import ViterbiStream
+
+    dist_on = dist.is_available() and dist.is_initialized()
+    world = dist.get_world_size() if dist_on else 1
+    rank = dist.get_rank() if dist_on else 0
+    chunk = int(chunk or embedder.max_batch)
+    mine = round_robin_chunks(n_frames, chunk, world)[rank]
+    rounds = ((n_frames + chunk - 1) // chunk + world - 1) // world      # local steps of the busiest rank
+    dev = f"cuda:{embedder.device}"
+    counts_dev = torch.zeros((max(rounds, 1), chunk, 3), dtype=torch.int32, device=dev)
+    gathered = torch.empty((world, gather_every, chunk, 3), dtype=torch.int32, device=dev) if world > 1 else None
+    vit = ViterbiStream(embedder, max(n_frames, 1), k) if rank == 0 else None
+    labels = []
+    t_wait = 0.0
+
+    def flush(s0, s1):
+        """Counts of local steps [s0, s1) of every rank -> rank 0's lattice, in time order."""
+        n = s1 - s0
+        if world > 1:
+            send = counts_dev[s0:s0 + gather_every]
+            if send.shape[0] < gather_every:          # last, short round: pad to the fixed shape
+                pad = torch.zeros((gather_every, chunk, 3), dtype=torch.int32, device=dev)
+                pad[: send.shape[0]] = send
+                send = pad
+            dist.all_gather_into_tensor(gathered.view(world * gather_every, chunk, 3), send)
+        if rank == 0:
+            src = gathered if world > 1 else counts_dev[s0:s1].unsqueeze(0)
+            for r, g, valid in time_order_of_round(n_frames, chunk, world, s0, n):
+                vit.append(src[r, g, :valid])
+
+    import time as _time
+    batches = (load_chunk(a, b) for _, a, b in mine)
+    done = 0
+    stream_iter = embedder.embed_and_vote_stream(batches, index, k, outs=outs)
+    for s in range(rounds):
+        if s < len(mine):
+            t0 = _time.perf_counter()
+            _emb, lab, _idx, _sc, cnt = next(stream_iter)
+            t_wait += _time.perf_counter() - t0
+            labels.append(lab.copy())
+            counts_dev[s, : cnt.shape[0]].copy_(torch.from_numpy(cnt), non_blocking=False)
+        done = s + 1
+        if done % gather_every == 0:
+            flush(done - gather_every, done)
+    if done % gather_every:
+        flush(done - done % gather_every, done)
+    for _ in stream_iter:      # exhausted; closes the generator
+        pass
+    states = vit.finish(device=dev) if rank == 0 else None
+    if stats is not None:
+        stats.update(wait_s=t_wait, local_steps=len(mine), rounds=rounds)
+    lab_all = np.concatenate(labels) if labels else np.zeros((0,), np.int32)
+    return states, lab_all
+
+
+# ---------------------------------------------------------------------------------------------
 # Row-sharded clip store (SURVEY.md §8e, the "exchange step" alternative for BASELINE configs[4]):
 # rank r holds store rows [row_ranges[r]) and its own share of the queries.
 # ---------------------------------------------------------------------------------------------
