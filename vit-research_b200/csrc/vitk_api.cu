@@ -489,7 +489,7 @@ struct vitk_ctx {
   // streamed Viterbi (vitk_hmm_stream_*): its own buffers, so it may run beside the forward
   double *hs_loge = nullptr, *hs_carry = nullptr;
   int8_t* hs_bp = nullptr;
-  long long hs_cap = 0, hs_t = -1;   // hs_t < 0: no stream open
+  long long hs_cap = 0, hs_limit = 0, hs_t = -1;   // hs_t < 0: no stream open; hs_limit = capacity of the open stream
   int hs_seg_cap = 0;
   // several banks per handle (vitk_bank_new / vitk_bank_select): the fields above are the
   // CURRENT bank, the others are parked here
@@ -2130,6 +2130,7 @@ extern "C" int vitk_hmm_stream_begin(vitk_handle h, long long capacity_frames) {
     h->hs_cap = capacity_frames;
   }
   if (!h->hs_carry && dev_alloc(e, &h->hs_carry, (size_t)8)) return 1;
+  h->hs_limit = capacity_frames;
   h->hs_t = 0;
   return 0;
 }
@@ -2141,8 +2142,8 @@ extern "C" int vitk_hmm_stream_append_counts(vitk_handle h, const int32_t* count
   if (h->hs_t < 0) { e.set("vitk_hmm_stream_append_counts: no stream open (call vitk_hmm_stream_begin)"); return 1; }
   if (n == 0) return 0;
   if (!counts_dev || n < 0 || k < 1 || k > 4096) { e.set("vitk_hmm_stream_append_counts: bad argument"); return 1; }
-  if (h->hs_t + n > h->hs_cap) {
-    e.set("vitk_hmm_stream_append_counts: %lld + %d frames exceed the capacity %lld given to begin", h->hs_t, n, h->hs_cap);
+  if (h->hs_t + n > h->hs_limit) {
+    e.set("vitk_hmm_stream_append_counts: %lld + %d frames exceed the capacity %lld given to begin", h->hs_t, n, h->hs_limit);
     return 1;
   }
   CK(e, cudaSetDevice(h->device));
