@@ -411,6 +411,8 @@ def run_ours(args, rank, local_rank, world):
     # sustained: the same device-resident step for >= 200 steps and >= 2 s, so the power cap has
     # settled (the 20-step `value` lasts 0.2 s and still rides the burst clocks)
     sus_steps = max(200, int(2.2e3 / max(ms_total / args.steps, 1e-3)) + 1)
+    if args.quick:
+        sus_steps = 1
     barrier()
     with ClockSampler(local_rank) as clk_sus:
         e0.record()
@@ -445,7 +447,10 @@ def run_ours(args, rank, local_rank, world):
     }
     if e2e_ranks is not None:
         line["e2e"]["per_rank"] = e2e_ranks
-    if rank == 0 and world == 1:
+    if args.quick:
+        line["quick"] = True
+        line.pop("sustained", None)
+    if rank == 0 and world == 1 and not args.quick:
         # per-kernel numbers are "kernel timed alone": let the board's power average recover from
         # the timed loop first (the step itself runs under sw_power_cap, see `clocks`), so they are
         # comparable with the burst peak they are divided by
@@ -744,6 +749,9 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--quick", action="store_true",
+                    help="developer A/B runs: only the timed device loop and e2e (no sustained loop, per-kernel "
+                         "timings, library bar or CPU baseline)")
     ap.add_argument("--config", default="c2", choices=["c2", "c3", "c4", "c5", "c5s"],
                     help="c2 = BASELINE.json configs[1] (the metric's config, default); the others are the "
                          "remaining BASELINE.json configs at full size")

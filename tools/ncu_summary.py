@@ -1,6 +1,7 @@
 """Summarise ncu outputs into small text files for profiles/ (run in the build container).
   python tools/ncu_summary.py launches gpurun_out/launches.csv > profiles/rNN_launches.txt
   python tools/ncu_summary.py full gpurun_out/prof.ncu-rep   > profiles/rNN_ncu_x.txt
+  python tools/ncu_summary.py inseq gpurun_out/inseq.csv     > profiles/rNN_ncu_in_sequence.txt
 """
 import collections, csv, re, subprocess, sys
 
@@ -74,5 +75,31 @@ def full(path):
             print(f"  {int(x[si])/tot*100:5.1f}%  {x[so].strip()[:100]}")
 
 
+def inseq(path):
+    """--cache-control none pass (kernels run on the caches their producers left): per kernel the
+    mean duration, DRAM bytes read / written and tensor-pipe activity, and the totals."""
+    lines = [l for l in open(path) if not l.startswith("==")]
+    per = collections.OrderedDict()
+    for row in csv.DictReader(lines):
+        d = per.setdefault(row["ID"], {"name": re.sub(r"\(.*", "", row["Kernel Name"]).replace("void ", "").replace("vitk::", "")})
+        d[row["Metric Name"]] = float(row["Metric Value"].replace(",", ""))
+    agg = collections.OrderedDict()
+    for d in per.values():
+        a = agg.setdefault(d["name"], [0, 0.0, 0.0, 0.0, 0.0])
+        a[0] += 1
+        a[1] += d.get("gpu__time_duration.sum", 0.0) / 1e3
+        a[2] += d.get("dram__bytes_read.sum", 0.0) / 1e6
+        a[3] += d.get("dram__bytes_write.sum", 0.0) / 1e6
+        a[4] += d.get("sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", 0.0)
+    print(f"{'count':>5} {'avg_us':>8} {'rd_MB':>8} {'wr_MB':>8} {'tensor%':>8}  kernel")
+    for k, a in agg.items():
+        n = a[0]
+        print(f"{n:5d} {a[1]/n:8.1f} {a[2]/n:8.1f} {a[3]/n:8.1f} {a[4]/n:8.1f}  {k[:110]}")
+    rd = sum(a[2] for a in agg.values()) / 1e3
+    wr = sum(a[3] for a in agg.values()) / 1e3
+    print(f"# total DRAM read {rd:.2f} GB, write {wr:.2f} GB over these {len(per)} launches "
+          f"({sum(a[1] for a in agg.values())/1e3:.2f} ms of kernel time)")
+
+
 if __name__ == "__main__":
-    {"launches": launches, "full": full}[sys.argv[1]](sys.argv[2])
+    {"launches": launches, "full": full, "inseq": inseq}[sys.argv[1]](sys.argv[2])

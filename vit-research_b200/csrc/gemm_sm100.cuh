@@ -41,6 +41,8 @@ enum GemmEpilogue : int {
   EPI_THRESH_POOL = 6,     // no matrix out: (key, column) of every score that beats its row's
                            //   running threshold is appended to that row's candidate pool
                            //   (large-store top-k: the score matrix never exists — knn.cuh)
+  EPI_TABLE_BF16 = 8,      // out bf16 = acc + table[m % table_rows, n] (patch embed straight into the bf16
+                           //   residual stream) + per-row partial (sum, sumsq): layer 0's LayerNorm inputs
   EPI_BIAS_RESID_BF16 = 7, // out bf16 = acc + bias[n] + resid[m,n], resid bf16 (normally aliasing
                            //   out: the residual stream IS the next GEMM's A operand); optional
                            //   per-row partial (sum, sumsq) of the fp32 value before rounding
@@ -141,7 +143,8 @@ struct EpiTraits {
                                     EPI == EPI_BIAS_GELUT_BF16);
   static constexpr bool kResid = (EPI == EPI_BIAS_RESID_F32 || EPI == EPI_BIAS_RESID_BF16);
   static constexpr bool kUsesVec = kOutBf16 || kResid || EPI == EPI_THRESH_POOL;
-  static constexpr int kChunkCols = (kOutBf16 || EPI == EPI_BIAS_RESID_BF16) ? 64 : 32;  // 128 B of output per row per chunk
+  static constexpr bool kStatsOut = kResid || EPI == EPI_TABLE_BF16;
+  static constexpr int kChunkCols = (kOutBf16 || EPI == EPI_BIAS_RESID_BF16 || EPI == EPI_TABLE_BF16) ? 64 : 32;  // 128 B of output per row per chunk
 };
 
 __device__ __forceinline__ uint32_t dynamic_smem_size() {
@@ -509,6 +512,40 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               *reinterpret_cast<float4*>(sbuf + lane * 128 + ((j ^ (lane & 7)) << 4)) = o;
             }
           }
+        } else if constexpr (EPI == EPI_TABLE_BF16) {
+          // patch embedding: acc + (position | CLS | conv-bias) table row -> bf16, straight into the
+          // residual stream, with the per-row partial sums layer 0's folded LayerNorm needs (no fp32
+          // round trip through HBM and no separate cast / row-statistics pass)
+          uint32_t r0[32], r1[32];
+          tmem_ld_32x32b_x32(t_row + c * CH, r0);
+          tmem_ld_32x32b_x32(t_row + c * CH + 32, r1);
+          tmem_ld_wait();
+          if (lane == 0) tma_store_wait_read<NBUF - 1>();
+          __syncwarp();
+          const float4* tp = reinterpret_cast<const float4*>(
+              p.table + (size_t)((row < p.M ? row : 0) % p.table_rows) * p.N + col0);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t* acc8 = j < 4 ? r0 + 8 * j : r1 + 8 * (j - 4);
+            float4 t0 = make_float4(0.f, 0.f, 0.f, 0.f), t1 = t0;
+            if (live && row < p.M && col0 + 8 * j < p.N) { t0 = __ldg(tp + 2 * j); t1 = __ldg(tp + 2 * j + 1); }
+            float y[8];
+            y[0] = __uint_as_float(acc8[0]) + t0.x; y[1] = __uint_as_float(acc8[1]) + t0.y;
+            y[2] = __uint_as_float(acc8[2]) + t0.z; y[3] = __uint_as_float(acc8[3]) + t0.w;
+            y[4] = __uint_as_float(acc8[4]) + t1.x; y[5] = __uint_as_float(acc8[5]) + t1.y;
+            y[6] = __uint_as_float(acc8[6]) + t1.z; y[7] = __uint_as_float(acc8[7]) + t1.w;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              st_s += y[i];
+              st_ss = fmaf(y[i], y[i], st_ss);
+            }
+            uint4 o;
+            o.x = pack_bf16x2(y[0], y[1]);
+            o.y = pack_bf16x2(y[2], y[3]);
+            o.z = pack_bf16x2(y[4], y[5]);
+            o.w = pack_bf16x2(y[6], y[7]);
+            *reinterpret_cast<uint4*>(sbuf + lane * 128 + ((j ^ (lane & 7)) << 4)) = o;
+          }
         } else if constexpr (EPI == EPI_BIAS_RESID_BF16) {
           // bf16 residual stream: TMA-load the 32 x 64 bf16 residual tile into the staging buffer,
           // add accumulator + bias in fp32, round once, store back in place and TMA-store it.  The
@@ -626,7 +663,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           }
         }
       }
-      if constexpr (EpiTraits<EPI>::kResid) {
+      if constexpr (EpiTraits<EPI>::kStatsOut) {
         if (p.stats_out != nullptr && row < p.M) {
           float2* so = reinterpret_cast<float2*>(p.stats_out + (size_t)row * p.stats_out_stride);
           so[2 * n_blk + half] = make_float2(st_s, st_ss);

@@ -245,6 +245,7 @@ int launch_gemm(Err& e, int epi, const CUtensorMap& a, const CUtensorMap& b, con
     case EPI_F32: return launch_gemm_e<EPI_F32>(e, a, b, c, r, p, st);
     case EPI_THRESH_POOL: return launch_gemm_e<EPI_THRESH_POOL>(e, a, b, c, r, p, st);
     case EPI_BIAS_RESID_BF16: return launch_gemm_e<EPI_BIAS_RESID_BF16>(e, a, b, c, r, p, st);
+    case EPI_TABLE_BF16: return launch_gemm_e<EPI_TABLE_BF16>(e, a, b, c, r, p, st);
   }
   e.set("gemm: unknown epilogue %d", epi);
   return 1;
@@ -397,6 +398,7 @@ struct LayerW {
   float *b_qkv = nullptr, *b_o = nullptr, *b_fc1 = nullptr, *b_fc2 = nullptr;
   float *c1_qkv = nullptr, *c1_fc1 = nullptr;
   CUtensorMap tm_qkv, tm_o, tm_fc1, tm_fc2;
+  CUtensorMap tm_q, tm_kv;   // rows [0,D) and [D,3D) of w_qkv (last layer: Q for the CLS rows only)
   // host fp32 copies kept from vitk_set_weight until vitk_finalize_weights folds them
   std::vector<float> h_wqkv, h_bqkv, h_wfc1, h_bfc1, h_ln1g, h_ln1b, h_ln2g, h_ln2b;
   bool dirty = true;
@@ -410,6 +412,7 @@ struct BatchMaps {  // tensor maps that depend on the number of frames in the ca
   CUtensorMap a_act_cls, a_xb_cls, a_h_cls, c_resid_cls, c_h_cls;
   // bf16 residual stream (default): the residual GEMMs update xb in place
   CUtensorMap c_xb, c_xb_cls;
+  CUtensorMap c_kv, c_q_cls;                // last layer: K|V columns of every token, Q of the CLS rows
   CUtensorMap c_patch;                      // fp32 patch-embedding output (scratch in hbuf)
 };
 
@@ -432,6 +435,8 @@ struct vitk_ctx {
   int stat_parts = 0;                 // 2 * hidden / 256
   bool cls_only_last = true;          // VITK_FULL_LAST_LAYER=1 computes all tokens in the last layer
   bool resid_f32 = false;             // VITK_RESID_F32=1: fp32 master residual stream + bf16 copy (round-1 form)
+  bool fused_patch = true;            // VITK_FUSED_PATCH=0: patch GEMM -> fp32 scratch -> cast + row-stats pass
+  bool split_last_qkv = true;         // VITK_SPLIT_LAST_QKV=0: the last layer projects Q for every token too
   float *resid = nullptr, *emb = nullptr;
   uint8_t* pix_stage = nullptr;  // device staging for vitk_embed_host_u8
   std::map<int, BatchMaps> maps;
@@ -727,6 +732,10 @@ extern "C" int vitk_create(const vitk_config* cfg, int device, vitk_handle* out)
   {
     const char* v = getenv("VITK_RESID_F32");
     c->resid_f32 = v && atoi(v) == 1;
+    v = getenv("VITK_FUSED_PATCH");
+    c->fused_patch = !(v && atoi(v) == 0);
+    v = getenv("VITK_SPLIT_LAST_QKV");
+    c->split_last_qkv = !(v && atoi(v) == 0);
   }
   if (c->S > ATT_MAX_S) { e.set("tokens per frame %d > %d unsupported by the attention kernel", c->S, ATT_MAX_S); return fail(c); }
   if (c->Kp % 64) { e.set("channels*patch^2 must be a multiple of 64"); return fail(c); }
@@ -741,6 +750,8 @@ extern "C" int vitk_create(const vitk_config* cfg, int device, vitk_handle* out)
           dev_alloc(e, &L.b_fc2, D) | dev_alloc(e, &L.c1_qkv, 3 * D) | dev_alloc(e, &L.c1_fc1, F);
     if (rc) return fail(c);
     rc |= tmap_operand(e, &L.tm_qkv, L.w_qkv, 3 * D, D, 128) |
+          tmap_operand(e, &L.tm_q, L.w_qkv, D, D, 128) |
+          tmap_operand(e, &L.tm_kv, L.w_qkv + D * D, 2 * D, D, 128) |
           tmap_operand(e, &L.tm_o, L.w_o, D, D, 128) |
           tmap_operand(e, &L.tm_fc1, L.w_fc1, F, D, 128) |
           tmap_operand(e, &L.tm_fc2, L.w_fc2, D, F, 128);
@@ -751,7 +762,7 @@ extern "C" int vitk_create(const vitk_config* cfg, int device, vitk_handle* out)
   rc |= dev_alloc(e, &c->w_patch, D * Kp) | dev_alloc(e, &c->posb, (size_t)c->S * D) |
         dev_alloc(e, &c->lnf_g, D) | dev_alloc(e, &c->lnf_b, D) | dev_alloc(e, &c->act, M * actw) |
         dev_alloc(e, &c->qkv, M * 3 * D) | dev_alloc(e, &c->hbuf, M * F) |
-        ((c->resid_f32 || F < 2 * D) ? dev_alloc(e, &c->resid, M * D) : 0) | dev_alloc(e, &c->xb, M * D) |
+        ((c->resid_f32 || !c->fused_patch) ? dev_alloc(e, &c->resid, M * D) : 0) | dev_alloc(e, &c->xb, M * D) |
         dev_alloc(e, &c->stats[0], M * 2 * (2 * D / 256)) |
         dev_alloc(e, &c->stats[1], M * 2 * (2 * D / 256)) |
         dev_alloc(e, &c->emb, (size_t)cfg->max_batch * D) |
@@ -971,10 +982,12 @@ int get_maps(vitk_ctx* c, int n, BatchMaps** out) {
            tmap_operand(e, &m.a_h, c->hbuf, M, F, GEMM_BM) |
            tmap_operand(e, &m.a_xb, c->xb, M, D, GEMM_BM) |
            (c->resid_f32 ? tmap_output(e, &m.c_resid, c->resid, M, D, false) : 0) |
-           tmap_output(e, &m.c_patch, c->resid ? (void*)c->resid : (void*)c->hbuf, M, D, false) |
+           (c->resid ? tmap_output(e, &m.c_patch, c->resid, M, D, false) : 0) |
            tmap_output(e, &m.c_xb, c->xb, M, D, true) |
            tmap_output(e, &m.c_xb_cls, c->xb, n, D, true, (long long)c->S * D) |
            tmap_output(e, &m.c_qkv, c->qkv, M, 3 * D, true) |
+           tmap_output(e, &m.c_kv, c->qkv + D, M, 2 * D, true, 3LL * D) |
+           tmap_output(e, &m.c_q_cls, c->qkv, n, D, true, (long long)c->S * 3 * D) |
            tmap_output(e, &m.c_h, c->hbuf, M, F, true) |
            tmap_tokens(e, &m.att_q, c->qkv, n, c->S, 3 * D, 128) |
            tmap_tokens(e, &m.att_kv, c->qkv, n, c->S, 3 * D, sk) |
@@ -1004,16 +1017,21 @@ int forward_chunk(vitk_ctx* c, const void* pix, int fmt, int n, float* emb_f32,
   GemmParams gp{};
   gp.M = M; gp.N = D; gp.K = c->Kp;
   gp.table = c->posb; gp.table_rows = c->S;
-  // The embedded tokens land in fp32 scratch (the fp32 residual buffer, or -- bf16 residual
-  // stream -- the not yet used MLP buffer) ...
-  const float* patch_out = c->resid ? c->resid : reinterpret_cast<const float*>(c->hbuf);
-  if (launch_gemm(e, EPI_TABLE_F32, mp->a_patch, c->tm_patch, mp->c_patch, mp->c_patch, gp, st))
-    return 1;
-  // ... and one pass produces the bf16 residual stream / copy + the row statistics that feed
-  // layer 0's folded LayerNorm
   const int parts = c->stat_parts;
   const long long sstride = 2LL * parts;
-  if (launch_rowstats(e, patch_out, c->xb, c->stats[0], M, D, parts, st)) return 1;
+  if (!c->resid_f32 && c->fused_patch) {
+    // bf16 residual stream: the patch GEMM's epilogue writes the stream and the row sums itself
+    gp.stats_out = c->stats[0];
+    gp.stats_out_stride = sstride;
+    if (launch_gemm(e, EPI_TABLE_BF16, mp->a_patch, c->tm_patch, mp->c_xb, mp->c_xb, gp, st)) return 1;
+    c->launches -= 1;   // one launch fewer than the fp32 form counted below
+  } else {
+    // fp32 master residual (VITK_RESID_F32=1) or VITK_FUSED_PATCH=0: fp32 tokens, then one pass for
+    // the bf16 stream / copy + the row statistics that feed layer 0's folded LayerNorm
+    if (launch_gemm(e, EPI_TABLE_F32, mp->a_patch, c->tm_patch, mp->c_patch, mp->c_patch, gp, st))
+      return 1;
+    if (launch_rowstats(e, c->resid, c->xb, c->stats[0], M, D, parts, st)) return 1;
+  }
   // Residual stream: bf16 in place in `xb` (default; the residual GEMMs read and write the tile
   // their own epilogue owns) or the round-1 form, an fp32 master copy + a bf16 copy (VITK_RESID_F32=1).
   const bool rf32 = c->resid_f32;
@@ -1039,11 +1057,23 @@ int forward_chunk(vitk_ctx* c, const void* pix, int fmt, int n, float* emb_f32,
     q.stats = c->stats[0]; q.stats_parts = parts; q.stats_stride = sstride;
     q.inv_d = 1.0f / D; q.eps = cfg.ln_eps;
     q.reverse_m = next_dir();
-    if (launch_gemm(e, EPI_BIAS_BF16, mp->a_xb, L.tm_qkv, mp->c_qkv, mp->c_qkv, q, st)) return 1;
     // Last layer: the reference reads only last_hidden_state[:,0,:] (ratt_write_clips_to_ragdb.py
     // :148), and after the attention every remaining op is row-wise, so only the CLS query and
     // the CLS rows of proj / MLP are computed (bit-identical for those rows).
     const bool cls_only = (li + 1 == nl) && c->cls_only_last && c->S > 1;
+    if (cls_only && c->split_last_qkv) {
+      // ... which also means only the CLS rows need a QUERY: K and V for every token (the 2D
+      // right-hand columns of the fused projection), Q for one row per frame
+      GemmParams kv = q;
+      kv.N = 2 * D; kv.bias = L.b_qkv + D; kv.c1 = L.c1_qkv + D;
+      if (launch_gemm(e, EPI_BIAS_BF16, mp->a_xb, L.tm_kv, mp->c_kv, mp->c_kv, kv, st)) return 1;
+      GemmParams qc = q;
+      qc.M = n; qc.N = D; qc.stats_stride = (long long)c->S * sstride; qc.reverse_m = 0;
+      if (launch_gemm(e, EPI_BIAS_BF16, mp->a_xb_cls, L.tm_q, mp->c_q_cls, mp->c_q_cls, qc, st)) return 1;
+      c->launches += 1;
+    } else if (launch_gemm(e, EPI_BIAS_BF16, mp->a_xb, L.tm_qkv, mp->c_qkv, mp->c_qkv, q, st)) {
+      return 1;
+    }
     // (a5.3) attention
     if (launch_attention(e, mp->att_q, mp->att_kv, mp->att_o, n, c->S, cfg.heads, st,
                          cls_only ? 1 : 0, next_dir()))
@@ -2271,10 +2301,11 @@ int op_gemm_common(const void* a, const void* w, void* out, int M, int N, int K,
   if (M < 1 || N < 4 || N % 4) { e.set("vitk_op_gemm: bad shape M=%d N=%d", M, N); return fail(); }
   const bool is_resid = epi == EPI_BIAS_RESID_F32 || epi == EPI_BIAS_RESID_BF16;
   const bool bf16_out = epi == EPI_BIAS_BF16 || epi == EPI_BIAS_GELU_BF16 || epi == EPI_BIAS_GELUT_BF16 ||
-                        epi == EPI_BIAS_RESID_BF16;
+                        epi == EPI_BIAS_RESID_BF16 || epi == EPI_TABLE_BF16;
   if (epi == EPI_THRESH_POOL) { e.set("vitk_op_gemm: epilogue %d is internal to the k-NN path", epi); return fail(); }
   if (bf16_out && N % 8) { e.set("vitk_op_gemm: bf16 output needs N %% 8 == 0"); return fail(); }
-  if ((bf16_out || is_resid) && !bias) { e.set("vitk_op_gemm: bias required"); return fail(); }
+  if ((bf16_out || is_resid) && epi != EPI_TABLE_BF16 && !bias) { e.set("vitk_op_gemm: bias required"); return fail(); }
+  if ((epi == EPI_TABLE_F32 || epi == EPI_TABLE_BF16) && !table) { e.set("vitk_op_gemm: table required"); return fail(); }
   if (is_resid && !resid) { e.set("vitk_op_gemm: resid required"); return fail(); }
   CUtensorMap ta, tb, tc, tr;
   GemmParams p{};
@@ -2284,7 +2315,7 @@ int op_gemm_common(const void* a, const void* w, void* out, int M, int N, int K,
     p.c1 = c1; p.stats = stats; p.stats_parts = stats_parts; p.stats_stride = 2LL * stats_parts;
     p.inv_d = 1.0f / K; p.eps = ln_eps;
   }
-  if (is_resid) {
+  if (is_resid || epi == EPI_TABLE_BF16) {
     if (epi == EPI_BIAS_RESID_F32) { p.xb = reinterpret_cast<__nv_bfloat16*>(xb_out); p.xb_ld = N; }
     p.stats_out = stats_out; p.stats_out_stride = 2LL * (2 * ((N + 255) / 256));
   }
