@@ -354,6 +354,17 @@ def test_code_path_variants_agree():
     att2 = _fingerprint({"VITK_ATTN": "2"})
     cos = (base * att2).sum(1) / (np.linalg.norm(base, axis=1) * np.linalg.norm(att2, axis=1))
     assert cos.min() > 0.9999, cos.min()
+    # attention v5 (softmax split over a loader and a math warp per scheduler, S through a shared-
+    # memory ring): v3's arithmetic in another schedule -- bit for bit (slower: profiles/r02_attn_v5_timeline.txt)
+    att5 = _fingerprint({"VITK_ATTN": "5"})
+    assert np.array_equal(base, att5)
+    # the patch GEMM writing the bf16 stream + row sums itself vs fp32 scratch + a cast / statistics
+    # pass (one rounding of the same fp32 value either way; the row sums are grouped differently)
+    unfused = _fingerprint({"VITK_FUSED_PATCH": "0"})
+    cos = (base * unfused).sum(1) / (np.linalg.norm(base, axis=1) * np.linalg.norm(unfused, axis=1))
+    assert cos.min() > 0.99999, cos.min()
+    # last layer: Q projected for the CLS rows only vs for every token: same arithmetic for the rows read
+    assert np.array_equal(base, _fingerprint({"VITK_SPLIT_LAST_QKV": "0"}))
     # residual stream kept in bf16 in place (default) vs the fp32 master copy + bf16 copy of
     # round 1: one bf16 rounding per residual add separates them
     rf32 = _fingerprint({"VITK_RESID_F32": "1"})

@@ -728,4 +728,441 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   }
 }
 
+// =============================================================================================
+// v5: the v3 pipeline with the softmax split over TWO warp roles per TMEM lane quarter.
+//
+// What bounds v3 (tools/dev_attn_timeline.py): per query block a softmax warp spends
+// ~1300 cycles in tcgen05.ld (the S block leaves TMEM at ~80 B/clk per SM, and the instruction holds
+// the issuing warp until its data is back) and ~1850 cycles in the exp2 loop (MUFU-bound), one
+// after the other, and the two warpgroups take turns.  Prefetching, an FMA-pipe exp2 and a column
+// split between two warps of a quarter all failed to overlap the two because each warp still did
+// both jobs.  Here the jobs belong to different warps of the same scheduler:
+//   warps 4-7   "loaders": tcgen05.ld the S chunks and hand them over through a shared-memory
+//               ring (2 x 4 KB per lane quarter, 128B-swizzled, mbarrier full / empty pairs);
+//               afterwards the epilogue of the PREVIOUS block (O from TMEM, 1/rowsum, bf16, TMA store)
+//   warps 8-11  "math": first chunk straight from TMEM (it yields the shift), the others from the
+//               ring with ld.shared (which does not hold the warp), exp2, row sum, P back into TMEM
+// so one quarter's TMEM reads run under the same quarter's MUFU work, block after block, and no
+// turn-taking is needed.  Arithmetic (shift, exp2 inputs, summation order, rounding of P and O) is
+// v3's own code, so the output is bit-identical to v3.  K/V/Q staging, the MMA issuer and the
+// overflow redo are v3's.  Shared memory: 2 stages x (Q0|Q1|K|V) + one 16 KB output tile + the
+// 32 KB ring: fits for S <= 208 (ViT @224: S = 197); longer sequences keep v3.
+// =============================================================================================
+constexpr int ATT5_MAX_SK = 208;
+
+struct Attn5SmemLayout {
+  int sk, kv_bytes, stage_bytes, off_o, off_ring, off_sum, off_bar, total;
+};
+__host__ __device__ inline Attn5SmemLayout attn5_smem_layout(int S) {
+  Attn5SmemLayout L;
+  L.sk = (S + 15) & ~15;
+  L.kv_bytes = ((L.sk * 128) + 1023) & ~1023;
+  L.stage_bytes = 2 * 16384 + 2 * L.kv_bytes;   // Q0 | Q1 | K | V
+  L.off_o = ATT3_STAGES * L.stage_bytes;        // one 16 KB output tile (only the loader group stores)
+  L.off_ring = L.off_o + 16384;                 // [quarter][buffer] 4 KB chunks of S
+  L.off_sum = L.off_ring + 4 * 2 * 4096;        // [slot][row] row sums, math -> loaders
+  L.off_bar = L.off_sum + 2 * 128 * 4;
+  L.total = L.off_bar + 512 + 1024;
+  return L;
+}
+
+__global__ void __launch_bounds__(ATT3_THREADS, 1)
+attention_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
+                       const __grid_constant__ CUtensorMap tmO, const AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  const Attn5SmemLayout L = attn5_smem_layout(p.S);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.off_bar);
+  uint64_t* kv_full = bars + 0;      // [2] stage
+  uint64_t* v_full = bars + 2;       // [2] stage
+  uint64_t* stage_empty = bars + 4;  // [2] stage, count 2 (one per query block of the unit)
+  uint64_t* s_full = bars + 6;       // [2] slot
+  uint64_t* p_full = bars + 8;       // [2] slot, count 4 (math warps)
+  uint64_t* o_full = bars + 10;      // [2] slot
+  uint64_t* slot_free = bars + 12;   // [2] slot, count 4 (loader warps)
+  uint64_t* redo_bar = bars + 14;    // [2] slot
+  uint64_t* sum_ready = bars + 16;   // [2] slot, count 4 (math warps): row sums are in shared memory
+  uint64_t* ring_full = bars + 18;   // [4 quarters][2 buffers]
+  uint64_t* ring_empty = bars + 26;  // [4 quarters][2 buffers]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 34);
+  float* s_sum = reinterpret_cast<float*>(smem + L.off_sum);
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31;
+  const int D = p.heads * ATT_D;
+  const int S = p.S, SK = L.sk;
+  const int units = p.frames * p.heads;
+  const int nblk = p.nblk;
+  const int n32 = SK >> 5;
+  const bool tail = (SK & 16) != 0;
+  const int nchunks = n32 + (tail ? 1 : 0);
+
+  if (tid == 0) {
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmKV);
+    tma_prefetch_desc(&tmO);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&kv_full[i], 1);
+      mbar_init(&v_full[i], 1);
+      mbar_init(&stage_empty[i], 2);
+      mbar_init(&s_full[i], 1);
+      mbar_init(&p_full[i], 4);
+      mbar_init(&o_full[i], 1);
+      mbar_init(&slot_free[i], 4);
+      mbar_init(&redo_bar[i], 1);
+      mbar_init(&sum_ready[i], 4);
+    }
+    for (int i = 0; i < 8; ++i) {
+      mbar_init(&ring_full[i], 1);
+      mbar_init(&ring_empty[i], 1);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc<512>(tmem_slot);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------ loader of Q / K / V (as v3) ------------------------------
+    if (lane == 0) {
+      int j = 0;
+      for (int u = blockIdx.x; u < units; u += gridDim.x, ++j) {
+        const int st = j & 1;
+        const uint32_t ph = (j >> 1) & 1;
+        const int uu = p.reverse ? units - 1 - u : u;
+        const int frame = uu / p.heads, head = uu % p.heads;
+        uint8_t* sb = smem + st * L.stage_bytes;
+        mbar_wait(&stage_empty[st], ph ^ 1u);
+        mbar_arrive_expect_tx(&kv_full[st], 16384 * nblk + SK * 128);
+        tma_load_3d(sb, &tmQ, &kv_full[st], head * ATT_D, 0, frame);
+        if (nblk == 2) tma_load_3d(sb + 16384, &tmQ, &kv_full[st], head * ATT_D, 128, frame);
+        tma_load_3d(sb + 32768, &tmKV, &kv_full[st], D + head * ATT_D, 0, frame);
+        mbar_arrive_expect_tx(&v_full[st], SK * 128);
+        tma_load_3d(sb + 32768 + L.kv_bytes, &tmKV, &v_full[st], 2 * D + head * ATT_D, 0, frame);
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------ MMA issuer (as v3) ------------------------------
+    if (lane == 0) {
+      const int my_units = (units - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+      const uint32_t idesc_s = make_idesc_bf16_f32(128, (uint32_t)SK, false, false);
+      const uint32_t idesc_o = make_idesc_bf16_f32(128, ATT_D, false, true);
+      int uj[2] = {0, 0};
+      int phs[2] = {0, 0};
+      long long t0 = clock64();
+      while (uj[0] < my_units || uj[1] < my_units) {
+        bool progressed = false;
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+          const int j = uj[s];
+          if (j >= my_units) continue;
+          const int st = j & 1;
+          const uint32_t sph = (j >> 1) & 1, uph = j & 1;
+          const int b = s ^ (j & 1);
+          uint8_t* sb = smem + st * L.stage_bytes;
+          const uint32_t t_slot = tmem_base + s * 256;
+          if (phs[s] == 0) {
+            if (!mbar_test_wait(&kv_full[st], sph) || !mbar_test_wait(&slot_free[s], uph ^ 1u)) continue;
+            tc_fence_after_sync();
+            if (b < nblk) {
+              const uint64_t dq = make_smem_desc_sw128(smem_u32(sb + b * 16384), 1024, 0);
+              const uint64_t dk = make_smem_desc_sw128(smem_u32(sb + 32768), 1024, 0);
+#pragma unroll
+              for (int k = 0; k < ATT_D / 16; ++k)
+                umma_bf16_ss(t_slot, dq + 2 * k, dk + 2 * k, idesc_s, k != 0 ? 1u : 0u);
+            }
+            umma_commit(&s_full[s]);
+            phs[s] = 1;
+          } else {
+            if (!mbar_test_wait(&p_full[s], uph) || !mbar_test_wait(&v_full[st], sph)) continue;
+            tc_fence_after_sync();
+            if (b < nblk) {
+              const uint32_t sv = smem_u32(sb + 32768 + L.kv_bytes);
+              const uint64_t dv0 = make_smem_desc_sw128(sv, 1024, 1024);
+              const uint32_t t_o_acc = t_slot + SK / 2;
+              umma_bf16_ts(t_o_acc, t_slot, dv0, idesc_o, 0u);
+#pragma unroll 4
+              for (int kk = 1; kk < SK / 16; ++kk)
+                umma_bf16_ts(t_o_acc, t_slot + kk * 8, dv0 + (uint64_t)(kk * 128), idesc_o, 1u);
+            }
+            umma_commit(&o_full[s]);
+            phs[s] = 0;
+            uj[s] = j + 1;
+          }
+          progressed = true;
+        }
+        if (progressed) t0 = clock64();
+        else if (clock64() - t0 > 4000000000LL) {
+          printf("vitk: attention(v5) MMA poll timeout block %d\n", (int)blockIdx.x);
+          __trap();
+        }
+      }
+    }
+  } else if (warp >= 4 && warp < 8) {
+    // ------------------------------ loaders: S -> ring, then the previous block's epilogue ------
+    const int wq = warp & 3;
+    const int r = wq * 32 + lane;
+    const uint32_t lane_off = static_cast<uint32_t>(wq * 32) << 16;
+    uint8_t* ring = smem + L.off_ring + wq * 8192;
+    uint64_t* rf = ring_full + wq * 2;
+    uint64_t* re = ring_empty + wq * 2;
+    uint8_t* sO = smem + L.off_o;
+    uint32_t lc = 0;  // chunks this warp has pushed through the ring
+    // epilogue of item (slot s, unit parity uph, ...): O from TMEM -> / rowsum -> bf16 -> TMA store
+    auto epilogue = [&](int s, uint32_t uph, int st, int b, int frame, int head) {
+      const bool blk_active = b < nblk;
+      const int rows_valid = blk_active ? min(128, p.q_rows - b * 128) : 0;
+      const bool warp_active = wq * 32 < rows_valid;
+      const uint32_t t_o = tmem_base + s * 256 + lane_off + static_cast<uint32_t>(SK / 2);
+      mbar_wait(&o_full[s], uph);
+      tc_fence_after_sync();
+      if (wq == 0 && lane == 0) {
+        mbar_arrive(&stage_empty[st]);   // O = P V has retired: this block no longer needs Q / K / V
+        tma_store_wait_read<0>();        // the previous block's store has drained the output tile
+      }
+      named_bar_sync(3, 128);
+      if (warp_active) {
+        mbar_wait(&sum_ready[s], uph);
+        const float inv = 1.0f / s_sum[s * 128 + r];
+        uint32_t v0[32], v1[32];
+        tmem_ld_32x32b_x32(t_o, v0);
+        tmem_ld_32x32b_x32(t_o + 32, v1);
+        tmem_ld_wait();
+        tc_fence_before_sync();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&slot_free[s]);  // O is in registers: the slot can be refilled
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const uint32_t* src = i < 4 ? v0 + 8 * i : v1 + 8 * (i - 4);
+          uint4 o;
+          o.x = pack_bf16x2(__uint_as_float(src[0]) * inv, __uint_as_float(src[1]) * inv);
+          o.y = pack_bf16x2(__uint_as_float(src[2]) * inv, __uint_as_float(src[3]) * inv);
+          o.z = pack_bf16x2(__uint_as_float(src[4]) * inv, __uint_as_float(src[5]) * inv);
+          o.w = pack_bf16x2(__uint_as_float(src[6]) * inv, __uint_as_float(src[7]) * inv);
+          *reinterpret_cast<uint4*>(sO + r * 128 + ((i ^ (r & 7)) << 4)) = o;
+        }
+        fence_proxy_async_smem();
+      } else {
+        tc_fence_before_sync();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&slot_free[s]);
+      }
+      named_bar_sync(3, 128);
+      if (wq == 0 && lane == 0 && blk_active) {
+        tma_store_3d(&tmO, sO, head * ATT_D, b * 128, frame);
+        tma_store_commit();
+      }
+    };
+    bool have_prev = false;
+    int ps = 0, pst = 0, pb = 0, pframe = 0, phead = 0;
+    uint32_t puph = 0;
+    int j = 0;
+    for (int u = blockIdx.x; u < units; u += gridDim.x, ++j) {
+      const int st = j & 1;
+      const uint32_t uph = j & 1;
+      const int uu = p.reverse ? units - 1 - u : u;
+      const int frame = uu / p.heads, head = uu % p.heads;
+#pragma unroll 1
+      for (int s = 0; s < 2; ++s) {
+        const int b = s ^ (j & 1);
+        const int rows_valid = b < nblk ? min(128, p.q_rows - b * 128) : 0;
+        const bool warp_active = wq * 32 < rows_valid;
+        const uint32_t t_slot = tmem_base + s * 256 + lane_off;
+        const int item = 2 * j + s;
+        const bool dbg_on = p.dbg != nullptr && blockIdx.x == 0 && wq == 0 && lane == 0 && item < 16;
+        long long* dbg = p.dbg + (0 * 16 + item) * 8;
+        if (dbg_on) dbg[0] = clock64();
+        mbar_wait(&s_full[s], uph);
+        tc_fence_after_sync();
+        if (dbg_on) dbg[1] = clock64();
+        if (warp_active) {
+#pragma unroll 1
+          for (int c = 1; c < nchunks; ++c, ++lc) {   // chunk 0 is read by the math warp itself
+            const uint32_t buf = lc & 1u;
+            uint8_t* dst = ring + buf * 4096 + lane * 128;
+            uint32_t v[32];
+            if (c < n32) {
+              tmem_ld_32x32b_x32(t_slot + c * 32, v);
+              tmem_ld_wait();
+              mbar_wait(&re[buf], ((lc >> 1) & 1u) ^ 1u);
+#pragma unroll
+              for (int g = 0; g < 8; ++g)
+                *reinterpret_cast<uint4*>(dst + ((g ^ (lane & 7)) << 4)) =
+                    make_uint4(v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
+            } else {
+              tmem_ld_32x32b_x16(t_slot + c * 32, *reinterpret_cast<uint32_t(*)[16]>(v));
+              tmem_ld_wait();
+              mbar_wait(&re[buf], ((lc >> 1) & 1u) ^ 1u);
+#pragma unroll
+              for (int g = 0; g < 4; ++g)
+                *reinterpret_cast<uint4*>(dst + ((g ^ (lane & 7)) << 4)) =
+                    make_uint4(v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&rf[buf]);
+          }
+        }
+        if (dbg_on) dbg[2] = clock64();
+        if (have_prev) epilogue(ps, puph, pst, pb, pframe, phead);
+        if (dbg_on) dbg[3] = clock64();
+        have_prev = true;
+        ps = s; puph = uph; pst = st; pb = b; pframe = frame; phead = head;
+      }
+    }
+    if (have_prev) epilogue(ps, puph, pst, pb, pframe, phead);
+  } else if (warp >= 8) {
+    // ------------------------------ math: exp2, row sums, P -> TMEM ------------------------------
+    const int wq = warp & 3;
+    const int r = wq * 32 + lane;
+    const uint32_t lane_off = static_cast<uint32_t>(wq * 32) << 16;
+    const uint8_t* ring = smem + L.off_ring + wq * 8192;
+    uint64_t* rf = ring_full + wq * 2;
+    uint64_t* re = ring_empty + wq * 2;
+    uint32_t mc = 0;  // chunks this warp has taken out of the ring
+    uint32_t redo_phase[2] = {0u, 0u};
+    int j = 0;
+    for (int u = blockIdx.x; u < units; u += gridDim.x, ++j) {
+      const int st = j & 1;
+      const uint32_t uph = j & 1;
+#pragma unroll 1
+      for (int s = 0; s < 2; ++s) {
+        const int b = s ^ (j & 1);
+        const bool blk_active = b < nblk;
+        const int rows_valid = blk_active ? min(128, p.q_rows - b * 128) : 0;
+        const bool warp_active = wq * 32 < rows_valid;
+        const uint32_t t_slot = tmem_base + s * 256 + lane_off;
+        const int item = 2 * j + s;
+        const bool dbg_on = p.dbg != nullptr && blockIdx.x == 0 && wq == 0 && lane == 0 && item < 16;
+        long long* dbg = p.dbg + (1 * 16 + item) * 8;
+        if (dbg_on) dbg[0] = clock64();
+        mbar_wait(&s_full[s], uph);
+        tc_fence_after_sync();
+        if (dbg_on) dbg[1] = clock64();
+        float sum = 0.f;
+        bool redo = false;
+        // next chunk out of the ring into `dst` (floats as raw bits), releasing its buffer
+        auto ring_take = [&](uint32_t* dst, bool full32) {
+          const uint32_t buf = mc & 1u;
+          const uint8_t* src = ring + buf * 4096 + lane * 128;
+          mbar_wait(&rf[buf], (mc >> 1) & 1u);
+          if (full32) {
+#pragma unroll
+            for (int g = 0; g < 8; ++g) {
+              const uint4 t = *reinterpret_cast<const uint4*>(src + ((g ^ (lane & 7)) << 4));
+              dst[4 * g] = t.x; dst[4 * g + 1] = t.y; dst[4 * g + 2] = t.z; dst[4 * g + 3] = t.w;
+            }
+          } else {
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+              const uint4 t = *reinterpret_cast<const uint4*>(src + ((g ^ (lane & 7)) << 4));
+              dst[4 * g] = t.x; dst[4 * g + 1] = t.y; dst[4 * g + 2] = t.z; dst[4 * g + 3] = t.w;
+            }
+          }
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&re[buf]);
+          ++mc;
+        };
+        if (warp_active) {
+          uint32_t va[32], vb[32];
+          if (n32 > 0) tmem_ld_32x32b_x32(t_slot, va);
+          else tmem_ld_32x32b_x16(t_slot, *reinterpret_cast<uint32_t(*)[16]>(va));
+          tmem_ld_wait();
+          reg_fence16(va);
+          if (n32 > 0) reg_fence16(va + 16);
+          float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+          const int first = n32 > 0 ? 32 : 16;
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (i < first && i < S) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(va[i]));
+          const float mxs = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])) * p.scale_log2e;
+          float2 s4[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
+          if (dbg_on) dbg[2] = clock64();
+          // v3's chunk order and accumulation pattern: va / vb alternate, two 32-column chunks per turn
+          int c = 0;
+          for (; c + 2 <= n32; c += 2) {  // va holds chunk c
+            ring_take(vb, true);
+            att_exp_chunk<32>(va, c * 32, S, p.scale_log2e, mxs, s4, t_slot);
+            if (c + 2 < n32) ring_take(va, true);
+            else if (tail) ring_take(va, false);
+            att_exp_chunk<32>(vb, (c + 1) * 32, S, p.scale_log2e, mxs, s4, t_slot);
+          }
+          if (c < n32) {  // odd number of 32-column chunks: va holds the last one
+            if (tail) ring_take(vb, false);
+            att_exp_chunk<32>(va, c * 32, S, p.scale_log2e, mxs, s4, t_slot);
+            if (tail) att_exp_chunk<16>(vb, (c + 1) * 32, S, p.scale_log2e, mxs, s4, t_slot);
+          } else if (tail) {  // va holds the 16-column tail
+            att_exp_chunk<16>(va, n32 * 32, S, p.scale_log2e, mxs, s4, t_slot);
+          }
+          tmem_st_wait();
+          sum = (s4[0].x + s4[0].y) + (s4[1].x + s4[1].y);
+          redo = !(sum < 1.0e30f);
+        }
+        if (dbg_on) dbg[3] = clock64();
+        // overflow of the single-pass shift: the whole block takes v3's exact path (S recomputed
+        // into the slot, row maximum, second exp2 pass), run by the math warps straight from TMEM
+        tc_fence_before_sync();
+        if (named_bar_or(2, 128, redo)) {
+          if (wq == 0 && lane == 0 && blk_active) {
+            tc_fence_after_sync();
+            uint8_t* sb = smem + st * L.stage_bytes;
+            const uint32_t idesc_s = make_idesc_bf16_f32(128, (uint32_t)SK, false, false);
+            const uint64_t dq = make_smem_desc_sw128(smem_u32(sb + b * 16384), 1024, 0);
+            const uint64_t dk = make_smem_desc_sw128(smem_u32(sb + 32768), 1024, 0);
+#pragma unroll
+            for (int k = 0; k < ATT_D / 16; ++k)
+              umma_bf16_ss(tmem_base + s * 256, dq + 2 * k, dk + 2 * k, idesc_s, k != 0 ? 1u : 0u);
+            umma_commit(&redo_bar[s]);
+          }
+          if (blk_active) {
+            mbar_wait(&redo_bar[s], redo_phase[s]);
+            redo_phase[s] ^= 1u;
+            tc_fence_after_sync();
+          }
+          if (warp_active) {
+            float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+            for (int c0 = 0; c0 < SK; c0 += 16) {
+              uint32_t v[16];
+              tmem_ld_32x32b_x16(t_slot + c0, v);
+              tmem_ld_wait();
+#pragma unroll
+              for (int i = 0; i < 16; ++i)
+                if (c0 + i < S) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(v[i]));
+            }
+            const float mxs = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])) * p.scale_log2e;
+            float2 s4[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
+            for (int c0 = 0; c0 < SK; c0 += 16) {
+              uint32_t v[16];
+              tmem_ld_32x32b_x16(t_slot + c0, v);
+              tmem_ld_wait();
+              reg_fence16(v);
+              att_exp_chunk<16>(v, c0, S, p.scale_log2e, mxs, s4, t_slot);
+            }
+            tmem_st_wait();
+            sum = (s4[0].x + s4[0].y) + (s4[1].x + s4[1].y);
+          }
+        }
+        if (warp_active) s_sum[s * 128 + r] = sum;
+        tc_fence_before_sync();
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive(&sum_ready[s]);
+          mbar_arrive(&p_full[s]);
+        }
+        if (dbg_on) dbg[4] = clock64();
+      }
+    }
+  }
+
+  if (warp == 4 && lane == 0) tma_store_wait_read<0>();  // before smem goes away
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after_sync();
+    tmem_dealloc<512>(tmem_base);
+  }
+}
+
 }  // namespace vitk

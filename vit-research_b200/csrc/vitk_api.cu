@@ -260,10 +260,11 @@ int launch_attention(Err& e, const CUtensorMap& tq, const CUtensorMap& tkv, cons
     e.set("attention: S=%d unsupported (1..%d)", S, ATT_MAX_S);
     return 1;
   }
-  static int version = -1;  // VITK_ATTN=2 selects the simpler non-persistent v2 kernel
+  static int version = -1;  // VITK_ATTN=2: the simpler non-persistent v2 kernel; 3: v3; 5: the loader / math split
   if (version < 0) {
     const char* v = getenv("VITK_ATTN");
-    version = (v && atoi(v) == 2) ? 2 : 3;
+    version = v ? atoi(v) : 3;
+    if (version != 2 && version != 3 && version != 5) version = 3;
   }
   AttnParams p;
   p.S = S;
@@ -299,6 +300,17 @@ int launch_attention(Err& e, const CUtensorMap& tq, const CUtensorMap& tkv, cons
       attr_bytes = L.total;
     }
     attention_v2_kernel<false><<<frames * heads * p.nblk, ATT_THREADS, L.total, st>>>(tq, tkv, to, p);
+  } else if (version == 5 && ((S + 15) & ~15) <= ATT5_MAX_SK) {
+    const Attn5SmemLayout L = attn5_smem_layout(S);
+    static int attr_bytes5 = 0;
+    if (L.total > attr_bytes5) {
+      CK(e, cudaFuncSetAttribute(attention_split_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 L.total));
+      attr_bytes5 = L.total;
+    }
+    const int units = frames * heads;
+    const int grid = units < num_sms() ? units : num_sms();
+    attention_split_kernel<<<grid, ATT3_THREADS, L.total, st>>>(tq, tkv, to, p);
   } else {
     const Attn3SmemLayout L = attn3_smem_layout(S);
     static int attr_bytes3 = 0;
