@@ -358,6 +358,10 @@ def test_code_path_variants_agree():
     # memory ring): v3's arithmetic in another schedule -- bit for bit (slower: profiles/r02_attn_v5_timeline.txt)
     att5 = _fingerprint({"VITK_ATTN": "5"})
     assert np.array_equal(base, att5)
+    # attention v6 (P in shared memory, SS-form P.V in two halves): again v3's arithmetic, bit for bit
+    # (slower too: profiles/r02_attn_v6_timeline.txt); and v3 with its round-1 single MMA-issuing thread
+    assert np.array_equal(base, _fingerprint({"VITK_ATTN": "6"}))
+    assert np.array_equal(base, _fingerprint({"VITK_ATTN_ISSUER": "1"}))
     # the patch GEMM writing the bf16 stream + row sums itself vs fp32 scratch + a cast / statistics
     # pass (one rounding of the same fp32 value either way; the row sums are grouped differently)
     unfused = _fingerprint({"VITK_FUSED_PATCH": "0"})

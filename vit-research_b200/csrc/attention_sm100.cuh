@@ -60,6 +60,7 @@ struct AttnParams {
   int q_rows;   // queries per frame that are needed (== S, or fewer: last-layer CLS shortcut)
   int nblk;     // query blocks per (frame, head): 1 if q_rows <= 128 else 2
   int reverse;  // v3: walk the (frame, head) units from the last to the first ("snake" order)
+  int one_issuer; // v3: 1 = both TMEM slots' MMAs issued by one polling thread (round-1 form)
   int handover; // v3: 32-column chunk of the softmax pass after which the exp2 turn passes to the
                 // other warpgroup (>= number of chunks: at the end of the pass)
   float scale_log2e;  // (1/sqrt(d)) * log2(e)
@@ -412,12 +413,56 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         tma_load_3d(sb + 32768 + L.kv_bytes, &tmKV, &v_full[st], 2 * D + head * ATT_D, 0, frame);
       }
     }
-  } else if (warp == 1) {
-    // ------------------------------ MMA issuer ------------------------------
-    if (lane == 0) {
+  } else if (warp == 1 || warp == 3) {
+    // ------------------------------ MMA issuers ------------------------------
+    // One issuing thread PER TMEM SLOT (warp 1: slot 0, warp 3: slot 1), each walking its own
+    // chain  S = Q K^T -> (softmax) -> O = P V  with blocking waits.  Round 1 ran both chains as
+    // polled state machines in ONE thread; the timeline (tools/dev_attn_timeline.py) showed the
+    // other slot's 13 TS-form P.V instructions (~1 075 cycles of issue) sitting between a slot
+    // becoming free and its next S being issued (wait_S ~800 cycles, P.V issued ~300 cycles late).
+    // p.one_issuer != 0 keeps the single-thread form for A/B runs.
+    const bool both = p.one_issuer != 0;
+    if (lane == 0 && (warp == 1 || !both)) {
       const int my_units = (units - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
       const uint32_t idesc_s = make_idesc_bf16_f32(128, (uint32_t)SK, false, false);
       const uint32_t idesc_o = make_idesc_bf16_f32(128, ATT_D, false, true);
+      if (!both) {
+        const int s = warp == 1 ? 0 : 1;
+        const uint32_t t_slot = tmem_base + s * 256;
+        for (int j = 0; j < my_units; ++j) {
+          const int st = j & 1;
+          const uint32_t sph = (j >> 1) & 1, uph = j & 1;
+          const int b = s ^ (j & 1);  // query block this slot holds in unit j
+          uint8_t* sb = smem + st * L.stage_bytes;
+          mbar_wait(&kv_full[st], sph);
+          mbar_wait(&slot_free[s], uph ^ 1u);
+          tc_fence_after_sync();
+          if (b < nblk) {
+            const uint64_t dq = make_smem_desc_sw128(smem_u32(sb + b * 16384), 1024, 0);
+            const uint64_t dk = make_smem_desc_sw128(smem_u32(sb + 32768), 1024, 0);
+#pragma unroll
+            for (int k = 0; k < ATT_D / 16; ++k)
+              umma_bf16_ss(t_slot, dq + 2 * k, dk + 2 * k, idesc_s, k != 0 ? 1u : 0u);
+          }
+          umma_commit(&s_full[s]);
+          mbar_wait(&p_full[s], uph);
+          mbar_wait(&v_full[st], sph);
+          tc_fence_after_sync();
+          const bool mdbg = p.dbg != nullptr && blockIdx.x == 0 && j < 16;
+          if (mdbg) p.dbg[(s * 16 + j) * 8 + 6] = clock64();
+          if (b < nblk) {
+            const uint32_t sv = smem_u32(sb + 32768 + L.kv_bytes);
+            const uint64_t dv0 = make_smem_desc_sw128(sv, 1024, 1024);
+            const uint32_t t_o_acc = t_slot + SK / 2;
+            umma_bf16_ts(t_o_acc, t_slot, dv0, idesc_o, 0u);
+#pragma unroll 4
+            for (int kk = 1; kk < SK / 16; ++kk)
+              umma_bf16_ts(t_o_acc, t_slot + kk * 8, dv0 + (uint64_t)(kk * 128), idesc_o, 1u);
+          }
+          umma_commit(&o_full[s]);
+          if (mdbg) p.dbg[(s * 16 + j) * 8 + 7] = clock64();
+        }
+      } else {
       int uj[2] = {0, 0};   // unit each slot's state machine is working on
       int phs[2] = {0, 0};  // 0: S = Q K^T is next, 1: O = P V is next
       long long t0 = clock64();
@@ -471,6 +516,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           printf("vitk: attention MMA poll timeout block %d\n", (int)blockIdx.x);
           __trap();
         }
+      }
       }
     }
   } else if (warp >= 4) {
@@ -1157,6 +1203,442 @@ attention_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
   }
 
   if (warp == 4 && lane == 0) tma_store_wait_read<0>();  // before smem goes away
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after_sync();
+    tmem_dealloc<512>(tmem_base);
+  }
+}
+
+// =============================================================================================
+// v6: v3 with the probabilities in SHARED memory instead of TMEM.
+//
+// What the round-2 timelines showed (tools/dev_attn_timeline.py): per (frame, head)
+// the TMEM read port is busy ~5 550 of v3's ~7 000 cycles -- 2 x 1 300 for tcgen05.ld of the S
+// blocks, 2 x 400 for O, and 2 x 1 075 for the 13 TS-form P.V instructions, which fetch their A
+// operand (P) from TMEM at ~83 cycles each where the tensor pipe needs 32.  The S = Q K^T of the
+// other slot queues behind them (wait_S ~700 cycles).  Overlap experiments (hand-over, v5, two
+// issuing threads) cannot beat a saturated port; taking P out of TMEM can:
+//   * the softmax warps write P (bf16) with st.shared into K-major 128B-swizzled 64-key tiles --
+//     the layout of a Q tile -- and P.V becomes an SS-form tcgen05.mma (A = P tile, B = V);
+//   * P.V is issued in two halves: keys 0-127 as soon as the first four chunks of the pass are
+//     written (it runs under the rest of the pass), the remaining keys at the end of the pass;
+//   * 48 KB hold the tiles (X: keys 0-127, Y: keys 128-191; the 16-key tail re-uses X tile 0 once the
+//     first half has been consumed), shared by both slots because the two warpgroups take turns;
+//     the space comes from staging O in the (by then dead) Q tile of its own block.
+// Arithmetic per element is v3's (same shift, exp2 inputs, summation order, bf16 rounding of P);
+// O accumulates the same 13 K-steps in the same order.  Needs S <= 208 like v5; longer sequences keep v3.
+// =============================================================================================
+struct Attn6SmemLayout {
+  int sk, kv_bytes, stage_bytes, off_p, off_bar, total;
+};
+__host__ __device__ inline Attn6SmemLayout attn6_smem_layout(int S) {
+  Attn6SmemLayout L;
+  L.sk = (S + 15) & ~15;
+  L.kv_bytes = ((L.sk * 128) + 1023) & ~1023;
+  L.stage_bytes = 2 * 16384 + 2 * L.kv_bytes;   // Q0 | Q1 | K | V ; O of block b is staged over Q_b
+  L.off_p = ATT3_STAGES * L.stage_bytes;        // X tile 0 | X tile 1 | Y : three 16 KB P tiles
+  L.off_bar = L.off_p + 3 * 16384;
+  L.total = L.off_bar + 512 + 1024;
+  return L;
+}
+
+// exp2(s*scale - mxs) of NC = 32 or 16 scores starting at key c0 -> bf16, written into the P tile
+// row `prow` (128 B = 64 keys, 16-byte granules XOR-swizzled with the row index); accumulates the
+// row sum exactly like att_exp_chunk.  r7 = row & 7.
+template <int NC>
+__device__ __forceinline__ void att_exp_chunk_smem(const uint32_t* v, int c0, int S, float scale, float mxs,
+                                                   float2 (&s2)[2], uint8_t* prow, int r7) {
+  uint32_t pk[NC / 2];
+  const bool full = c0 + NC <= S;
+  const float2 sc2 = make_float2(scale, scale), nm2 = make_float2(-mxs, -mxs);
+#pragma unroll
+  for (int i = 0; i < NC / 2; ++i) {
+    const float2 x = __ffma2_rn(make_float2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1])), sc2, nm2);
+    float2 e = make_float2(ex2_approx(x.x), ex2_approx(x.y));
+    if (!full) {
+      e.x = (c0 + 2 * i < S) ? e.x : 0.f;
+      e.y = (c0 + 2 * i + 1 < S) ? e.y : 0.f;
+    }
+    s2[i & 1] = __fadd2_rn(s2[i & 1], e);
+    pk[i] = pack_bf16x2(e.x, e.y);
+  }
+  const int g0 = ((c0 & 63) >> 3);   // first 16-byte granule of this chunk inside the 64-key row
+#pragma unroll
+  for (int i = 0; i < NC / 8; ++i)
+    *reinterpret_cast<uint4*>(prow + (((g0 + i) ^ r7) << 4)) =
+        make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+}
+
+__global__ void __launch_bounds__(ATT3_THREADS, 1)
+attention_smemp_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
+                       const __grid_constant__ CUtensorMap tmO, const AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  const Attn6SmemLayout L = attn6_smem_layout(p.S);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.off_bar);
+  uint64_t* kv_full = bars + 0;      // [2] stage
+  uint64_t* v_full = bars + 2;       // [2] stage
+  uint64_t* stage_empty = bars + 4;  // [2] stage, count 2 (one per query block, after its O store)
+  uint64_t* s_full = bars + 6;       // [2] slot
+  uint64_t* p_half = bars + 8;       // [2] slot, count 4: keys 0-127 of P are in shared memory
+  uint64_t* p_full = bars + 10;      // [2] slot, count 4: all of P is
+  uint64_t* pv1_done = bars + 12;    // [2] slot: the first-half P.V instructions have retired
+  uint64_t* o_full = bars + 14;      // [2] slot
+  uint64_t* slot_free = bars + 16;   // [2] slot, count 4
+  uint64_t* redo_bar = bars + 18;    // [2] slot
+  uint64_t* turn_bar = bars + 20;    // [2] group, count 4
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 22);
+  volatile int* redo_flag = reinterpret_cast<volatile int*>(bars + 23);  // [2] slot: P.V was issued by the exact path
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31;
+  const int D = p.heads * ATT_D;
+  const int S = p.S, SK = L.sk;
+  const int units = p.frames * p.heads;
+  const int nblk = p.nblk;
+  const int nk = SK >> 4;                 // 16-key K-steps of P.V (<= 13)
+  const int nk1 = nk < 8 ? nk : 8;        // first half: keys 0-127 (tiles X0, X1)
+  uint8_t* sP = smem + L.off_p;
+  // shared-memory address of K-step kk's P operand: tile kk/4 (tile 3, the 16-key tail, lives in X tile 0)
+  auto p_tile_of = [&](int kk) { const int t = kk >> 2; return t == 3 ? 0 : t; };
+
+  if (tid == 0) {
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmKV);
+    tma_prefetch_desc(&tmO);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&kv_full[i], 1);
+      mbar_init(&v_full[i], 1);
+      mbar_init(&stage_empty[i], 2);
+      mbar_init(&s_full[i], 1);
+      mbar_init(&p_half[i], 4);
+      mbar_init(&p_full[i], 4);
+      mbar_init(&pv1_done[i], 1);
+      mbar_init(&o_full[i], 1);
+      mbar_init(&slot_free[i], 4);
+      mbar_init(&redo_bar[i], 1);
+      mbar_init(&turn_bar[i], 4);
+      redo_flag[i] = 0;
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc<512>(tmem_slot);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t idesc_s = make_idesc_bf16_f32(128, (uint32_t)SK, false, false);
+  const uint32_t idesc_o = make_idesc_bf16_f32(128, ATT_D, false, true);
+  // P.V K-steps [k0, k1) of one block: A = P tile (K-major, like Q), B = V (MN-major as TMA delivered it)
+  auto issue_pv = [&](uint32_t t_o_acc, uint8_t* sb, int k0, int k1, bool first_clears) {
+    const uint32_t sv = smem_u32(sb + 32768 + L.kv_bytes);
+    const uint64_t dv0 = make_smem_desc_sw128(sv, 1024, 1024);
+    for (int kk = k0; kk < k1; ++kk) {
+      const uint64_t dp = make_smem_desc_sw128(smem_u32(sP + p_tile_of(kk) * 16384), 1024, 0) +
+                          static_cast<uint64_t>(2 * (kk & 3));
+      umma_bf16_ss(t_o_acc, dp, dv0 + (uint64_t)(kk * 128), idesc_o, (kk == k0 && first_clears) ? 0u : 1u);
+    }
+  };
+
+  if (warp == 0) {
+    // ------------------------------ loader (as v3) ------------------------------
+    if (lane == 0) {
+      int j = 0;
+      for (int u = blockIdx.x; u < units; u += gridDim.x, ++j) {
+        const int st = j & 1;
+        const uint32_t ph = (j >> 1) & 1;
+        const int uu = p.reverse ? units - 1 - u : u;
+        const int frame = uu / p.heads, head = uu % p.heads;
+        uint8_t* sb = smem + st * L.stage_bytes;
+        mbar_wait(&stage_empty[st], ph ^ 1u);
+        mbar_arrive_expect_tx(&kv_full[st], 16384 * nblk + SK * 128);
+        tma_load_3d(sb, &tmQ, &kv_full[st], head * ATT_D, 0, frame);
+        if (nblk == 2) tma_load_3d(sb + 16384, &tmQ, &kv_full[st], head * ATT_D, 128, frame);
+        tma_load_3d(sb + 32768, &tmKV, &kv_full[st], D + head * ATT_D, 0, frame);
+        mbar_arrive_expect_tx(&v_full[st], SK * 128);
+        tma_load_3d(sb + 32768 + L.kv_bytes, &tmKV, &v_full[st], 2 * D + head * ATT_D, 0, frame);
+      }
+    }
+  } else if (warp == 1 || warp == 3) {
+    // ------------------------------ MMA issuers: warp 1 = slot 0, warp 3 = slot 1 ------------------
+    if (lane == 0) {
+      const int my_units = (units - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+      const int s = warp == 1 ? 0 : 1;
+      const uint32_t t_slot = tmem_base + s * 256;
+      for (int j = 0; j < my_units; ++j) {
+        const int st = j & 1;
+        const uint32_t sph = (j >> 1) & 1, uph = j & 1;
+        const int b = s ^ (j & 1);
+        uint8_t* sb = smem + st * L.stage_bytes;
+        mbar_wait(&kv_full[st], sph);
+        mbar_wait(&slot_free[s], uph ^ 1u);
+        tc_fence_after_sync();
+        if (b < nblk) {
+          const uint64_t dq = make_smem_desc_sw128(smem_u32(sb + b * 16384), 1024, 0);
+          const uint64_t dk = make_smem_desc_sw128(smem_u32(sb + 32768), 1024, 0);
+#pragma unroll
+          for (int k = 0; k < ATT_D / 16; ++k)
+            umma_bf16_ss(t_slot, dq + 2 * k, dk + 2 * k, idesc_s, k != 0 ? 1u : 0u);
+        }
+        umma_commit(&s_full[s]);
+        // first half of O = P V: keys 0-127, under the rest of the softmax pass
+        mbar_wait(&p_half[s], uph);
+        mbar_wait(&v_full[st], sph);
+        tc_fence_after_sync();
+        if (b < nblk) issue_pv(t_slot, sb, 0, nk1, true);   // O accumulates at columns 0-63 of the slot
+        umma_commit(&pv1_done[s]);
+        // second half at the end of the pass (unless the exact path has issued everything itself)
+        mbar_wait(&p_full[s], uph);
+        tc_fence_after_sync();
+        if (redo_flag[s]) {
+          redo_flag[s] = 0;
+        } else {
+          if (b < nblk) issue_pv(t_slot, sb, nk1, nk, false);
+          umma_commit(&o_full[s]);
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ------------------------------ softmax + epilogue ------------------------------
+    const int g = (warp - 4) >> 2;  // warpgroup == TMEM slot
+    const int wq = warp & 3;        // TMEM lane quarter
+    const int r = wq * 32 + lane;   // row within the query block == TMEM lane
+    const int r7 = r & 7;
+    const uint32_t lane_off = static_cast<uint32_t>(wq * 32) << 16;
+    const uint32_t t_slot = tmem_base + g * 256 + lane_off;
+    const uint32_t t_o = t_slot;    // O accumulates over S columns 0-63 (read before the first-half P.V)
+    const int n32 = SK >> 5;
+    const bool tail = (SK & 16) != 0;
+    const int half_cols = nk1 * 16;   // keys of the first-half P.V (128, or all of a short sequence)
+    // row r of the P tile that holds keys [c0, c0 + 32): tiles X0, X1, Y, and X0 again for keys >= 192
+    auto prow_of = [&](int c0) { return sP + p_tile_of(c0 >> 4) * 16384 + r * 128; };
+    int j = 0;
+    uint32_t redo_phase = 0;
+    for (int u = blockIdx.x; u < units; u += gridDim.x, ++j) {
+      const int st = j & 1;
+      const uint32_t uph = j & 1;
+      const int b = g ^ (j & 1);
+      const int uu = p.reverse ? units - 1 - u : u;
+      const int frame = uu / p.heads, head = uu % p.heads;
+      const bool blk_active = b < nblk;
+      const int rows_valid = blk_active ? min(128, p.q_rows - b * 128) : 0;
+      const bool warp_active = wq * 32 < rows_valid;
+      uint8_t* sb = smem + st * L.stage_bytes;
+      uint8_t* sO = sb + b * 16384;   // this block's Q tile: dead once S = Q K^T (and any redo) is done
+
+      const bool dbg_on = p.dbg != nullptr && blockIdx.x == 0 && wq == 0 && lane == 0 && j < 16;
+      long long* dbg = p.dbg + (g * 16 + j) * 8;
+      if (dbg_on) dbg[0] = clock64();
+      mbar_wait(&s_full[g], uph);
+      if (dbg_on) dbg[6] = clock64();
+      // the two warpgroups take turns in the softmax (see v3); the turn also hands over the P tiles:
+      // the other group's second-half P.V (which reads Y and the tail in X tile 0) must have retired
+      if (g == 0) {
+        if (j > 0) {
+          mbar_wait(&turn_bar[0], (uint32_t)(j - 1) & 1u);
+          mbar_wait(&o_full[1], (uint32_t)(j - 1) & 1u);
+        }
+      } else {
+        mbar_wait(&turn_bar[1], uph);
+        mbar_wait(&o_full[0], uph);
+      }
+      tc_fence_after_sync();
+      if (dbg_on) dbg[1] = clock64();
+      float sum = 0.f;
+      bool redo = false;
+      bool half_sent = false;
+      // keys [0, 128) (or all of them when SK <= 128) are in shared memory: let the first-half P.V go
+      auto send_half = [&]() {
+        half_sent = true;
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&p_half[g]);
+      };
+      if (warp_active) {
+        uint32_t va[32], vb[32];
+        if (n32 > 0) tmem_ld_32x32b_x32(t_slot, va);
+        else tmem_ld_32x32b_x16(t_slot, *reinterpret_cast<uint32_t(*)[16]>(va));
+        tmem_ld_wait();
+        reg_fence16(va);
+        if (n32 > 0) reg_fence16(va + 16);
+        float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        const int first = n32 > 0 ? 32 : 16;
+#pragma unroll
+        for (int i = 0; i < 32; ++i)
+          if (i < first && i < S) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(va[i]));
+        const float mxs = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])) * p.scale_log2e;
+        float2 s4[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
+        int c = 0;
+        for (; c + 2 <= n32; c += 2) {  // va holds chunk c
+          tmem_ld_32x32b_x32(t_slot + (c + 1) * 32, vb);
+          att_exp_chunk_smem<32>(va, c * 32, S, p.scale_log2e, mxs, s4, prow_of(c * 32), r7);
+          tmem_ld_wait();
+          reg_fence16(vb);
+          reg_fence16(vb + 16);
+          if (c + 2 < n32) tmem_ld_32x32b_x32(t_slot + (c + 2) * 32, va);
+          else if (tail) tmem_ld_32x32b_x16(t_slot + (c + 2) * 32, *reinterpret_cast<uint32_t(*)[16]>(va));
+          att_exp_chunk_smem<32>(vb, (c + 1) * 32, S, p.scale_log2e, mxs, s4, prow_of((c + 1) * 32), r7);
+          tmem_ld_wait();
+          reg_fence16(va);
+          reg_fence16(va + 16);
+          if (!half_sent && (c + 2) * 32 >= half_cols) send_half();   // the first half's keys are written
+          if ((c + 2) * 32 == 192 && tail) {    // the tail goes into X tile 0: first-half P.V must be done with it
+            mbar_wait(&pv1_done[g], uph);
+          }
+        }
+        if (c < n32) {  // odd number of 32-column chunks: va holds the last one
+          if (tail) tmem_ld_32x32b_x16(t_slot + (c + 1) * 32, *reinterpret_cast<uint32_t(*)[16]>(vb));
+          att_exp_chunk_smem<32>(va, c * 32, S, p.scale_log2e, mxs, s4, prow_of(c * 32), r7);
+          tmem_ld_wait();
+          reg_fence16(vb);
+          if (!half_sent && (c + 1) * 32 >= half_cols) send_half();
+          if (tail) {
+            if ((c + 1) * 32 >= 192) mbar_wait(&pv1_done[g], uph);
+            att_exp_chunk_smem<16>(vb, (c + 1) * 32, S, p.scale_log2e, mxs, s4, prow_of((c + 1) * 32), r7);
+          }
+        } else if (tail) {  // va holds the 16-column tail
+          if (n32 * 32 >= 192) mbar_wait(&pv1_done[g], uph);
+          att_exp_chunk_smem<16>(va, n32 * 32, S, p.scale_log2e, mxs, s4, prow_of(n32 * 32), r7);
+        }
+        sum = (s4[0].x + s4[0].y) + (s4[1].x + s4[1].y);
+        redo = !(sum < 1.0e30f);
+      }
+      if (dbg_on) dbg[2] = clock64();
+      if (!half_sent) send_half();   // inactive warps and short sequences: the arrival is still owed
+      // Overflow of the single-pass shift -> the EXACT path for the whole block: S recomputed, row
+      // maximum, second exp2 pass, and this group issues the block's P.V itself (the issuer thread
+      // skips its second half when redo_flag is set).  Rare (never seen on real activations).
+      tc_fence_before_sync();
+      if (named_bar_or(2 + g, 128, redo)) {
+        const bool leader = wq == 0 && lane == 0;
+        // the first-half P.V issued on the overflowed probabilities must have retired before S is
+        // recomputed over its accumulator columns (it is re-issued from scratch below)
+        mbar_wait(&pv1_done[g], uph);
+        if (leader && blk_active) {
+          tc_fence_after_sync();
+          const uint64_t dq = make_smem_desc_sw128(smem_u32(sb + b * 16384), 1024, 0);
+          const uint64_t dk = make_smem_desc_sw128(smem_u32(sb + 32768), 1024, 0);
+#pragma unroll
+          for (int k = 0; k < ATT_D / 16; ++k)
+            umma_bf16_ss(tmem_base + g * 256, dq + 2 * k, dk + 2 * k, idesc_s, k != 0 ? 1u : 0u);
+          umma_commit(&redo_bar[g]);   // in order behind the (garbage) first-half P.V already issued
+        }
+        if (blk_active) {
+          mbar_wait(&redo_bar[g], redo_phase);
+          redo_phase ^= 1u;
+          tc_fence_after_sync();
+        }
+        float mxs = 0.f;
+        float2 s4[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
+        const int main_cols = SK < 192 ? SK : 192;     // keys that fit tiles X0, X1, Y
+        if (warp_active) {
+          float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+          for (int c0 = 0; c0 < SK; c0 += 16) {
+            uint32_t v[16];
+            tmem_ld_32x32b_x16(t_slot + c0, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+              if (c0 + i < S) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(v[i]));
+          }
+          mxs = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])) * p.scale_log2e;
+          for (int c0 = 0; c0 < main_cols; c0 += 16) {
+            uint32_t v[16];
+            tmem_ld_32x32b_x16(t_slot + c0, v);
+            tmem_ld_wait();
+            reg_fence16(v);
+            att_exp_chunk_smem<16>(v, c0, S, p.scale_log2e, mxs, s4, prow_of(c0), r7);
+          }
+        }
+        uint32_t vt[16];
+        if (warp_active && SK > 192) {   // the tail's scores leave TMEM before O = P V overwrites nothing of them
+          tmem_ld_32x32b_x16(t_slot + 192, vt);
+          tmem_ld_wait();
+          reg_fence16(vt);
+        }
+        fence_proxy_async_smem();
+        tc_fence_before_sync();
+        named_bar_sync(2 + g, 128);
+        if (leader && blk_active) {
+          tc_fence_after_sync();
+          issue_pv(tmem_base + g * 256, sb, 0, main_cols >> 4, true);
+          umma_commit(&redo_bar[g]);
+        }
+        if (blk_active) {
+          mbar_wait(&redo_bar[g], redo_phase);
+          redo_phase ^= 1u;
+          tc_fence_after_sync();
+        }
+        if (warp_active && SK > 192)
+          att_exp_chunk_smem<16>(vt, 192, S, p.scale_log2e, mxs, s4, prow_of(192), r7);
+        sum = (s4[0].x + s4[0].y) + (s4[1].x + s4[1].y);
+        fence_proxy_async_smem();
+        tc_fence_before_sync();
+        named_bar_sync(2 + g, 128);
+        if (leader) {
+          if (blk_active) {
+            tc_fence_after_sync();
+            if (SK > 192) issue_pv(tmem_base + g * 256, sb, 12, nk, false);
+          }
+          redo_flag[g] = 1;
+          umma_commit(&o_full[g]);
+        }
+      }
+      fence_proxy_async_smem();
+      tc_fence_before_sync();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(&p_full[g]);
+        mbar_arrive(&turn_bar[g ^ 1]);  // hand the exp2 units (and the P tiles) to the other warpgroup
+      }
+      if (dbg_on) dbg[3] = clock64();
+
+      mbar_wait(&o_full[g], uph);
+      tc_fence_after_sync();
+      if (dbg_on) dbg[4] = clock64();
+      if (warp_active) {
+        const float inv = 1.0f / sum;
+        uint32_t v0[32], v1[32];
+        tmem_ld_32x32b_x32(t_o, v0);
+        tmem_ld_32x32b_x32(t_o + 32, v1);
+        tmem_ld_wait();
+        tc_fence_before_sync();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&slot_free[g]);  // O is in registers: the slot can be refilled
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const uint32_t* src = i < 4 ? v0 + 8 * i : v1 + 8 * (i - 4);
+          uint4 o;
+          o.x = pack_bf16x2(__uint_as_float(src[0]) * inv, __uint_as_float(src[1]) * inv);
+          o.y = pack_bf16x2(__uint_as_float(src[2]) * inv, __uint_as_float(src[3]) * inv);
+          o.z = pack_bf16x2(__uint_as_float(src[4]) * inv, __uint_as_float(src[5]) * inv);
+          o.w = pack_bf16x2(__uint_as_float(src[6]) * inv, __uint_as_float(src[7]) * inv);
+          *reinterpret_cast<uint4*>(sO + r * 128 + ((i ^ (r & 7)) << 4)) = o;
+        }
+        fence_proxy_async_smem();
+      } else {
+        tc_fence_before_sync();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&slot_free[g]);
+      }
+      named_bar_sync(2 + g, 128);
+      if (wq == 0 && lane == 0) {
+        if (blk_active) {
+          // rows of idle warps hold stale bytes: tokens >= S are clipped by the 3-D map, and with
+          // q_rows < S (last-layer CLS shortcut) the extra rows are never read
+          tma_store_3d(&tmO, sO, head * ATT_D, b * 128, frame);
+          tma_store_commit();
+          tma_store_wait_read<0>();   // the tile lives in the stage's Q block: read out before release
+        }
+        mbar_arrive(&stage_empty[st]);
+      }
+      if (dbg_on) dbg[5] = clock64();
+    }
+  }
+
   tc_fence_before_sync();
   __syncthreads();
   if (warp == 2) {

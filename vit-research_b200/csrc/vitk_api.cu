@@ -264,7 +264,7 @@ int launch_attention(Err& e, const CUtensorMap& tq, const CUtensorMap& tkv, cons
   if (version < 0) {
     const char* v = getenv("VITK_ATTN");
     version = v ? atoi(v) : 3;
-    if (version != 2 && version != 3 && version != 5) version = 3;
+    if (version != 2 && version != 3 && version != 5 && version != 6) version = 3;
   }
   AttnParams p;
   p.S = S;
@@ -277,6 +277,9 @@ int launch_attention(Err& e, const CUtensorMap& tq, const CUtensorMap& tkv, cons
     static int handover = -1;  // VITK_ATTN_HANDOVER: chunk after which the exp2 turn is passed on
     if (handover < 0) { const char* hv = getenv("VITK_ATTN_HANDOVER"); handover = hv ? atoi(hv) : 1000; if (handover < 0) handover = 0; }
     p.handover = handover;
+    static int one_issuer = -1;  // VITK_ATTN_ISSUER=1: the round-1 single MMA-issuing thread
+    if (one_issuer < 0) { const char* iv = getenv("VITK_ATTN_ISSUER"); one_issuer = (iv && atoi(iv) == 1) ? 1 : 0; }
+    p.one_issuer = one_issuer;
   }
   p.scale_log2e = 0.125f * 1.4426950408889634f;  // head dim 64 -> 1/sqrt(64)
   p.dbg = g_attn_dbg;
@@ -300,6 +303,17 @@ int launch_attention(Err& e, const CUtensorMap& tq, const CUtensorMap& tkv, cons
       attr_bytes = L.total;
     }
     attention_v2_kernel<false><<<frames * heads * p.nblk, ATT_THREADS, L.total, st>>>(tq, tkv, to, p);
+  } else if (version == 6 && ((S + 15) & ~15) <= ATT5_MAX_SK) {
+    const Attn6SmemLayout L = attn6_smem_layout(S);
+    static int attr_bytes6 = 0;
+    if (L.total > attr_bytes6) {
+      CK(e, cudaFuncSetAttribute(attention_smemp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 L.total));
+      attr_bytes6 = L.total;
+    }
+    const int units = frames * heads;
+    const int grid = units < num_sms() ? units : num_sms();
+    attention_smemp_kernel<<<grid, ATT3_THREADS, L.total, st>>>(tq, tkv, to, p);
   } else if (version == 5 && ((S + 15) & ~15) <= ATT5_MAX_SK) {
     const Attn5SmemLayout L = attn5_smem_layout(S);
     static int attr_bytes5 = 0;
