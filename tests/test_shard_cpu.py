@@ -163,3 +163,47 @@ def test_round_robin_chunks_cover_the_stream_in_time_order():
                 pos = e
             s += steps
         assert pos == n
+
+
+def _rr_worker(rank, world, port, n_frames, chunk, every, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        mine = shard.round_robin_chunks(n_frames, chunk, world)[rank]
+        rounds = ((n_frames + chunk - 1) // chunk + world - 1) // world
+        # "vote counts" of frame i = [i, 2i, 3i]: a pure function of the global frame index
+        local = torch.zeros((max(rounds, 1), chunk, 3), dtype=torch.int32)
+        for s_, (_b, a, e) in enumerate(mine):
+            idx = torch.arange(a, e, dtype=torch.int32)
+            local[s_, : e - a] = torch.stack([idx, 2 * idx, 3 * idx], 1)
+        got, done = [], 0
+        for s_ in range(rounds):
+            done = s_ + 1
+            if done % every == 0:
+                got += shard.gather_round_in_time_order(local, done - every, done, n_frames, chunk, every)
+        if done % every:
+            got += shard.gather_round_in_time_order(local, done - done % every, done, n_frames, chunk, every)
+        allc = torch.cat(got) if got else torch.zeros((0, 3), dtype=torch.int32)
+        want = torch.arange(n_frames, dtype=torch.int32)
+        q.put((rank, bool(allc.shape == (n_frames, 3) and torch.equal(allc[:, 0], want)
+                          and torch.equal(allc[:, 2], 3 * want))))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n_frames,chunk,every", [(2, 1000, 64, 4), (3, 997, 32, 3), (2, 5, 8, 2)])
+def test_round_robin_gathers_rebuild_the_stream_in_time_order_over_gloo(world, n_frames, chunk, every):
+    """The N > 1 data flow of BASELINE configs[2] (shard.label_and_smooth_stream) on CPU: chunks dealt
+    round-robin, fixed-shape all-gathers every few local steps, segments handed on in time order --
+    every rank rebuilds the whole stream, ragged tail and short last round included."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_rr_worker, args=(r, world, port, n_frames, chunk, every, q)) for r in range(world)]
+    for p_ in procs:
+        p_.start()
+    res = [q.get(timeout=120) for _ in range(world)]
+    for p_ in procs:
+        p_.join(60)
+    assert sorted(res) == [(r, True) for r in range(world)]

@@ -119,6 +119,34 @@ def time_order_of_round(n_frames: int, chunk: int, world: int, first_step: int, 
     return order
 
 
+def gather_round_in_time_order(local: torch.Tensor, s0: int, s1: int, n_frames: int, chunk: int,
+                               gather_every: int, scratch: torch.Tensor | None = None, group=None):
+    """One gather of the round-robin stream: `local` is this rank's (rounds, chunk, ...) per-chunk
+    result buffer; local steps [s0, s1) (at most gather_every of them) of EVERY rank are all-gathered
+    with one fixed-shape collective and returned as the list of per-chunk tensors in TIME order
+    (ragged last chunk trimmed, chunks past the end skipped).  Single process: slices of `local`."""
+    import torch.distributed as dist
+
+    dist_on = dist.is_available() and dist.is_initialized()
+    world = dist.get_world_size(group) if dist_on else 1
+    n = s1 - s0
+    if world == 1:
+        src = local[s0:s1].unsqueeze(0)
+    else:
+        send = local[s0:s0 + gather_every]
+        if send.shape[0] < gather_every:          # last, short round: pad to the fixed shape
+            pad = torch.zeros((gather_every,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+            pad[: send.shape[0]] = send
+            send = pad
+        if scratch is None:
+            scratch = torch.empty((world, gather_every) + tuple(local.shape[1:]), dtype=local.dtype,
+                                  device=local.device)
+        dist.all_gather_into_tensor(scratch.view((world * gather_every,) + tuple(local.shape[1:])),
+                                    send.contiguous(), group=group)
+        src = scratch
+    return [src[r, g, :valid] for r, g, valid in time_order_of_round(n_frames, chunk, world, s0, n)]
+
+
 def label_and_smooth_stream(embedder, index, load_chunk: Callable, n_frames: int, k: int = 25,
                             chunk: int | None = None, gather_every: int = 4, stats: dict | None = None,
                             outs=None):
@@ -150,18 +178,9 @@ def label_and_smooth_stream(embedder, index, load_chunk: Callable, n_frames: int
 
     def flush(s0, s1):
         """Counts of local steps [s0, s1) of every rank -> rank 0's lattice, in time order."""
-        n = s1 - s0
-        if world > 1:
-            send = counts_dev[s0:s0 + gather_every]
-            if send.shape[0] < gather_every:          # last, short round: pad to the fixed shape
-                pad = torch.zeros((gather_every, chunk, 3), dtype=torch.int32, device=dev)
-                pad[: send.shape[0]] = send
-                send = pad
-            dist.all_gather_into_tensor(gathered.view(world * gather_every, chunk, 3), send)
-        if rank == 0:
-            src = gathered if world > 1 else counts_dev[s0:s1].unsqueeze(0)
-            for r, g, valid in time_order_of_round(n_frames, chunk, world, s0, n):
-                vit.append(src[r, g, :valid])
+        for seg in gather_round_in_time_order(counts_dev, s0, s1, n_frames, chunk, gather_every, gathered):
+            if rank == 0:
+                vit.append(seg)
 
     import time as _time
     batches = (load_chunk(a, b) for _, a, b in mine)
