@@ -20,4 +20,4 @@ for rep in range(3):
     e1.record()
     torch.cuda.synchronize()
     res.append(round(e0.elapsed_time(e1) / 50 * 1e3, 1))
-print("attention us:", res, "issuer", os.environ.get("VITK_ATTN_ISSUER", "3"))
+print("attention us:", res, "VITK_ATTN", os.environ.get("VITK_ATTN", "3"), "handover", os.environ.get("VITK_ATTN_HANDOVER", "end"))
