@@ -41,6 +41,8 @@ enum GemmEpilogue : int {
   EPI_THRESH_POOL = 6,     // no matrix out: (key, column) of every score that beats its row's
                            //   running threshold is appended to that row's candidate pool
                            //   (large-store top-k: the score matrix never exists — knn.cuh)
+  EPI_THRESH_POOL_FILT = 9,  // EPI_THRESH_POOL + the per-query row predicate (KnnFilter): a separate instantiation,
+                           //   because the predicate's loads in the epilogue cost the unfiltered search 26 %
   EPI_TABLE_BF16 = 8,      // out bf16 = acc + table[m % table_rows, n] (patch embed straight into the bf16
                            //   residual stream) + per-row partial (sum, sumsq): layer 0's LayerNorm inputs
   EPI_BIAS_RESID_BF16 = 7, // out bf16 = acc + bias[n] + resid[m,n], resid bf16 (normally aliasing
@@ -142,7 +144,9 @@ struct EpiTraits {
   static constexpr bool kOutBf16 = (EPI == EPI_BIAS_BF16 || EPI == EPI_BIAS_GELU_BF16 ||
                                     EPI == EPI_BIAS_GELUT_BF16);
   static constexpr bool kResid = (EPI == EPI_BIAS_RESID_F32 || EPI == EPI_BIAS_RESID_BF16);
-  static constexpr bool kUsesVec = kOutBf16 || kResid || EPI == EPI_THRESH_POOL;
+  static constexpr bool kPool = (EPI == EPI_THRESH_POOL || EPI == EPI_THRESH_POOL_FILT);
+  static constexpr bool kFilt = (EPI == EPI_THRESH_POOL_FILT);
+  static constexpr bool kUsesVec = kOutBf16 || kResid || kPool;
   static constexpr bool kStatsOut = kResid || EPI == EPI_TABLE_BF16;
   static constexpr int kChunkCols = (kOutBf16 || EPI == EPI_BIAS_RESID_BF16 || EPI == EPI_TABLE_BF16) ? 64 : 32;  // 128 B of output per row per chunk
 };
@@ -380,7 +384,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
       unsigned long long pool_t = ~0ull;  // EPI_THRESH_POOL: this row's running threshold
       float pool_tf = INFINITY;           // its key part as a float (v >= pool_tf <=> key bits >= t_hi)
-      if constexpr (EPI == EPI_THRESH_POOL) {
+      if constexpr (EpiTraits<EPI>::kPool) {
         if (row < p.M) {
           pool_t = __ldg(p.pool_thresh + row);
           const uint32_t t_hi = static_cast<uint32_t>(pool_t >> 32);
@@ -447,7 +451,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               st_global_256(xp, o[0], o[1]);
               st_global_256(xp + 2, o[2], o[3]);
             }
-          } else if constexpr (EPI == EPI_THRESH_POOL) {
+          } else if constexpr (EpiTraits<EPI>::kPool) {
             if (p.pool_l2) {
               const float sc = p.pool_l2 == 1 ? 2.0f : 1.0f;
 #pragma unroll
@@ -459,7 +463,8 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 for (int j = 0; j < 32; ++j)
                   if (col0 + j < p.N && col0 + j < p.pool_cap) {
                     // a row the query's predicate rejects leaves an EMPTY slot (key bits 0)
-                    const bool ok = !p.filt.active || knn_filter_pass(p.filt, row, p.col_base + col0 + j);
+                    bool ok = true;
+                    if constexpr (EpiTraits<EPI>::kFilt) ok = knn_filter_pass(p.filt, row, p.col_base + col0 + j);
                     p.pool[(size_t)row * p.pool_cap + col0 + j] = make_uint2(
                         static_cast<uint32_t>(p.col_base + col0 + j), ok ? float_order_bits(v[j]) : 0u);
                   }
@@ -478,7 +483,9 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     const uint32_t bi = static_cast<uint32_t>(p.col_base + col0 + j);
                     const unsigned long long comp = (static_cast<unsigned long long>(kb) << 32) | (~bi);
                     // the predicate runs only for the rare score that beats the threshold
-                    if (comp > pool_t && (!p.filt.active || knn_filter_pass(p.filt, row, (int)bi))) {
+                    bool take = comp > pool_t;
+                    if constexpr (EpiTraits<EPI>::kFilt) take = take && knn_filter_pass(p.filt, row, (int)bi);
+                    if (take) {
                       const int pos = atomicAdd(p.pool_n + row, 1);
                       if (pos < p.pool_cap) p.pool[(size_t)row * p.pool_cap + pos] = make_uint2(bi, kb);
                     }
@@ -501,11 +508,11 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           }
           // the TMA store that last read this staging tile must have finished reading it (the
           // residual epilogue already waited before the residual was loaded into it)
-          if constexpr (EPI != EPI_BIAS_RESID_F32 && EPI != EPI_THRESH_POOL) {
+          if constexpr (EPI != EPI_BIAS_RESID_F32 && !EpiTraits<EPI>::kPool) {
             if (lane == 0) tma_store_wait_read<NBUF - 1>();
             __syncwarp();
           }
-          if constexpr (EPI != EPI_THRESH_POOL) {
+          if constexpr (!EpiTraits<EPI>::kPool) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
               float4 o = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
@@ -648,7 +655,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             else mbar_arrive(&tempty_bar[acc]);
           }
         }
-        if constexpr (EPI == EPI_THRESH_POOL) continue;  // nothing is stored
+        if constexpr (EpiTraits<EPI>::kPool) continue;  // nothing is stored
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) {

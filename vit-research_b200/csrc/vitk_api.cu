@@ -244,6 +244,7 @@ int launch_gemm(Err& e, int epi, const CUtensorMap& a, const CUtensorMap& b, con
     case EPI_TABLE_F32: return launch_gemm_e<EPI_TABLE_F32>(e, a, b, c, r, p, st);
     case EPI_F32: return launch_gemm_e<EPI_F32>(e, a, b, c, r, p, st);
     case EPI_THRESH_POOL: return launch_gemm_e<EPI_THRESH_POOL>(e, a, b, c, r, p, st);
+    case EPI_THRESH_POOL_FILT: return launch_gemm_e<EPI_THRESH_POOL_FILT>(e, a, b, c, r, p, st);
     case EPI_BIAS_RESID_BF16: return launch_gemm_e<EPI_BIAS_RESID_BF16>(e, a, b, c, r, p, st);
     case EPI_TABLE_BF16: return launch_gemm_e<EPI_TABLE_BF16>(e, a, b, c, r, p, st);
   }
@@ -1522,7 +1523,7 @@ int knn_stage(vitk_ctx* h, int n, int kc, int cap, int metric, int lo, int hi, i
   gp.pool_l2 = metric == METRIC_L2 ? 1 : (h->knn_pen_cur ? 2 : 0);
   gp.pool_direct = direct ? 1 : 0;
   gp.filt = filt;
-  if (launch_gemm(e, EPI_THRESH_POOL, ta, tb, ta, ta, gp, st)) return 1;
+  if (launch_gemm(e, filt.active ? EPI_THRESH_POOL_FILT : EPI_THRESH_POOL, ta, tb, ta, ta, gp, st)) return 1;
   h->launches += 1;
   return launch_pool_select(h, cap, n, kc, direct ? hi - lo : -1, 0, 0, nullptr, h->knn_overflow + flag, st);
 }
@@ -2328,7 +2329,7 @@ int op_gemm_common(const void* a, const void* w, void* out, int M, int N, int K,
   const bool is_resid = epi == EPI_BIAS_RESID_F32 || epi == EPI_BIAS_RESID_BF16;
   const bool bf16_out = epi == EPI_BIAS_BF16 || epi == EPI_BIAS_GELU_BF16 || epi == EPI_BIAS_GELUT_BF16 ||
                         epi == EPI_BIAS_RESID_BF16 || epi == EPI_TABLE_BF16;
-  if (epi == EPI_THRESH_POOL) { e.set("vitk_op_gemm: epilogue %d is internal to the k-NN path", epi); return fail(); }
+  if (epi == EPI_THRESH_POOL || epi == EPI_THRESH_POOL_FILT) { e.set("vitk_op_gemm: epilogue %d is internal to the k-NN path", epi); return fail(); }
   if (bf16_out && N % 8) { e.set("vitk_op_gemm: bf16 output needs N %% 8 == 0"); return fail(); }
   if ((bf16_out || is_resid) && epi != EPI_TABLE_BF16 && !bias) { e.set("vitk_op_gemm: bias required"); return fail(); }
   if ((epi == EPI_TABLE_F32 || epi == EPI_TABLE_BF16) && !table) { e.set("vitk_op_gemm: table required"); return fail(); }
