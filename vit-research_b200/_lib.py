@@ -129,7 +129,8 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     if not os.path.exists(nvcc):
         raise VitkError("nvcc not found: cannot build libvitk.so")
     tmp = LIB_PATH.with_suffix(".so.tmp%d" % os.getpid())
-    cmd = [nvcc, *NVCC_FLAGS, "-o", str(tmp), str(CSRC / "vitk_api.cu")]
+    extra = os.environ.get("VITK_NVCC_EXTRA", "").split()     # developer builds, e.g. -DVITK_ATT_POLY_MASK=0x8888u
+    cmd = [nvcc, *NVCC_FLAGS, *extra, "-o", str(tmp), str(CSRC / "vitk_api.cu")]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
     r = subprocess.run(cmd, capture_output=True, text=True)
@@ -149,6 +150,10 @@ def load(auto_build: bool = True):
     global _lib
     if _lib is not None:
         return _lib
+    global LIB_PATH
+    if os.environ.get("VITK_LIB"):              # developer A/B runs against another build of the library
+        LIB_PATH = Path(os.environ["VITK_LIB"]).resolve()
+        auto_build = False
     if auto_build and needs_build():
         build()
     if not LIB_PATH.exists():

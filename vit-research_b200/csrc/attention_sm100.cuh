@@ -302,6 +302,33 @@ __device__ __forceinline__ void reg_fence16(uint32_t* r) {
                     "+r"(r[7]), "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]),
                     "+r"(r[13]), "+r"(r[14]), "+r"(r[15]));
 }
+// exp2 on the FMA / ALU pipes (Cody-Waite split + degree-3 minimax of 2^f on [-0.5, 0.5], max relative
+// error 7.5e-5 -- 1/50 of the bf16 rounding of P): x = n + f, 2^x = poly(f) with n added to the exponent
+// field.  Inputs are clamped to [-126, 127.9]: an overflowing row still reaches > 1e30 and takes the
+// exact redo.  The softmax pass is MUFU-bound (one ex2 per score, 8 cycles per warp instruction); the
+// pairs selected by VITK_ATT_POLY_MASK (bit i%16 of the pair index inside a chunk) take this route
+// instead, so that the MUFU and the FMA pipe share the exponentials (cf. FlashAttention-4's software exp2).
+#ifndef VITK_ATT_POLY_MASK
+#define VITK_ATT_POLY_MASK 0u
+#endif
+__device__ __forceinline__ float2 exp2_poly2(float2 x) {
+  const float2 xc = make_float2(fminf(fmaxf(x.x, -126.0f), 127.9f), fminf(fmaxf(x.y, -126.0f), 127.9f));
+  const float2 magic = make_float2(12582912.0f, 12582912.0f);   // 1.5 * 2^23
+  const float2 t = __fadd2_rn(xc, magic);
+  const float2 n = __fadd2_rn(t, make_float2(-12582912.0f, -12582912.0f));
+  const float2 f = __ffma2_rn(n, make_float2(-1.0f, -1.0f), xc);
+  float2 q = make_float2(5.517124757e-02f, 5.517124757e-02f);
+  q = __ffma2_rn(q, f, make_float2(2.426100969e-01f, 2.426100969e-01f));
+  q = __ffma2_rn(q, f, make_float2(6.932609677e-01f, 6.932609677e-01f));
+  q = __ffma2_rn(q, f, make_float2(9.999281168e-01f, 9.999281168e-01f));
+  return make_float2(__int_as_float(__float_as_int(q.x) + (__float_as_int(t.x) << 23)),
+                     __int_as_float(__float_as_int(q.y) + (__float_as_int(t.y) << 23)));
+}
+__device__ __forceinline__ float2 att_exp2_pair(float2 x, int i) {
+  if ((VITK_ATT_POLY_MASK >> (i & 15)) & 1u) return exp2_poly2(x);
+  return make_float2(ex2_approx(x.x), ex2_approx(x.y));
+}
+
 // exp2(s*scale - mxs) of NC = 32 or 16 scores starting at column c0 -> bf16 pairs stored over S
 // cells [c0/2, c0/2 + NC/2) (already consumed); accumulates the row sum.  Packed fp32 (FFMA2 /
 // FADD2): 2.5 issue slots per element next to its one MUFU op — a single softmax warp per
@@ -316,7 +343,7 @@ __device__ __forceinline__ void att_exp_chunk(const uint32_t* v, int c0, int S, 
 #pragma unroll
   for (int i = 0; i < NC / 2; ++i) {
     const float2 x = __ffma2_rn(make_float2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1])), sc2, nm2);
-    float2 e = make_float2(ex2_approx(x.x), ex2_approx(x.y));
+    float2 e = att_exp2_pair(x, i);
     if (!full) {
       e.x = (c0 + 2 * i < S) ? e.x : 0.f;
       e.y = (c0 + 2 * i + 1 < S) ? e.y : 0.f;
@@ -1256,7 +1283,7 @@ __device__ __forceinline__ void att_exp_chunk_smem(const uint32_t* v, int c0, in
 #pragma unroll
   for (int i = 0; i < NC / 2; ++i) {
     const float2 x = __ffma2_rn(make_float2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1])), sc2, nm2);
-    float2 e = make_float2(ex2_approx(x.x), ex2_approx(x.y));
+    float2 e = att_exp2_pair(x, i);
     if (!full) {
       e.x = (c0 + 2 * i < S) ? e.x : 0.f;
       e.y = (c0 + 2 * i + 1 < S) ? e.y : 0.f;
