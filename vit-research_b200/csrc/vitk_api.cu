@@ -253,6 +253,7 @@ int launch_gemm(Err& e, int epi, const CUtensorMap& a, const CUtensorMap& b, con
 }
 
 long long* g_attn_dbg = nullptr;  // developer timeline buffer (vitk_dev_attn_timeline)
+long long* g_gemm_dbg = nullptr;  // same for the GEMM of vitk_op_gemm* (vitk_dev_gemm_timeline)
 
 // q_rows > 0: only the first q_rows queries of every frame are needed (last layer: the CLS row)
 int launch_attention(Err& e, const CUtensorMap& tq, const CUtensorMap& tkv, const CUtensorMap& to,
@@ -2354,6 +2355,7 @@ int op_gemm_common(const void* a, const void* w, void* out, int M, int N, int K,
     else
       tr = tc;
   }
+  p.dbg = g_gemm_dbg;
   rc = rc || launch_gemm(e, epi, ta, tb, tc, tr, p, reinterpret_cast<cudaStream_t>(stream));
   if (rc) return fail();
   return 0;
@@ -2478,6 +2480,13 @@ extern "C" int vitk_op_chunk_head(const float* x, const float* w1, const float* 
 // CTA 0 of the attention kernel; pass NULL to switch the instrumentation off.
 extern "C" int vitk_dev_attn_timeline(long long* buf_dev) {
   g_attn_dbg = buf_dev;
+  return 0;
+}
+
+// Same for the stand-alone GEMM entry points (vitk_op_gemm / vitk_op_gemm_fused): 40 * 8 int64 samples
+// written by CTA 0 (MMA thread, first epilogue warp of each column half, producer), per work unit.
+extern "C" int vitk_dev_gemm_timeline(long long* buf_dev) {
+  g_gemm_dbg = buf_dev;
   return 0;
 }
 

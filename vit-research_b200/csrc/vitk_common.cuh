@@ -76,6 +76,25 @@ __device__ __forceinline__ bool mbar_test_wait(uint64_t* bar, uint32_t parity) {
 }
 // Bounded wait: a protocol bug must trap, never hang the box (a hung GPU is a strike).
 // try_wait itself sleeps in hardware for a bounded time, so this loop is cheap.
+// One lane of a fully converged warp (always the same one).  Code that reaches this through
+// warp-uniform control flow keeps its operands in uniform registers, so a tcgen05.mma / TMA issue
+// under `if (elect_one_sync())` is ONE instruction; under `if (lane == 0)` ptxas wraps every such
+// instruction in an ELECT / R2UR.BROADCAST x5 / BRA.U.ANY loop (~20 issue slots per MMA).
+__device__ __forceinline__ bool elect_one_sync() {
+  uint32_t pred;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "elect.sync _|p, 0xffffffff;\n"
+      "selp.b32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(pred));
+  return pred != 0;
+}
+// warp index as a value ptxas knows to be warp-uniform (threadIdx.x >> 5 alone is not)
+__device__ __forceinline__ int uniform_warp_idx() {
+  return __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
+}
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   long long t0 = clock64();
@@ -377,6 +396,11 @@ __device__ __forceinline__ void tmem_dealloc_cg2(uint32_t taddr) {
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
 }
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
