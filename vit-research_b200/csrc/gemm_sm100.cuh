@@ -364,6 +364,30 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if constexpr (EpiTraits<EPI>::kResid) {
       if (lane == 0) resid_request(first_unit, 0, 0);
     }
+    // per-column c1 / bias of this thread's column and the per-row partial sums of this thread's
+    // row, for the unit AFTER the one being processed
+    static_assert(!EpiTraits<EPI>::kUsesVec || BN == GEMM_EPI_WARPS * 32, "one column per epilogue thread");
+    float nx_c1 = 0.f, nx_bias = 0.f;
+    float4 nx_st[GEMM_MAX_STAT_PARTS / 2];
+    auto fetch_unit_inputs = [&](int tile_) {
+      if constexpr (EpiTraits<EPI>::kUsesVec) {
+        if (tile_ >= num_tiles) return;
+        const int n = (tile_ % n_tiles) * BN + et;
+        nx_c1 = (p.stats != nullptr && n < p.N) ? __ldg(p.c1 + n) : 0.f;
+        nx_bias = (n < p.N && p.bias != nullptr) ? __ldg(p.bias + n) : 0.f;
+        if constexpr (EpiTraits<EPI>::kOutBf16) {
+          const int nrow = (m_unit_of(tile_) * CG + (int)rank) * GEMM_BM + q * 32 + lane;
+          if (p.stats != nullptr && nrow < p.M) {
+            // all partial pairs in flight at once
+            const float4* sp = reinterpret_cast<const float4*>(p.stats + (size_t)nrow * p.stats_stride);
+#pragma unroll
+            for (int i = 0; i < GEMM_MAX_STAT_PARTS / 2; ++i)
+              nx_st[i] = (2 * i < p.stats_parts) ? __ldg(sp + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+        }
+      }
+    };
+    fetch_unit_inputs(first_unit);
     int ti = 0;
     for (int tile = first_unit; tile < num_tiles; tile += unit_stride, ++ti) {
       const int m_blk = m_unit_of(tile) * CG + (int)rank, n_blk = tile % n_tiles;
@@ -371,57 +395,32 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const int row0 = m_blk * GEMM_BM + q * 32;
       const int row = row0 + lane;
       if constexpr (EpiTraits<EPI>::kUsesVec) {
-        // per-column vectors of this N tile -> smem (read back as broadcast float4s)
+        // per-column vectors of this N tile -> smem (read back as broadcast float4s); the values
+        // were fetched into registers one work unit ago
         named_bar_sync(1, GEMM_EPI_WARPS * 32);  // every warp is done with the previous tile's
-        for (int i = et; i < BN; i += GEMM_EPI_WARPS * 32) {
-          const int n = n_blk * BN + i;
-          sVec[i] = (p.stats != nullptr && n < p.N) ? __ldg(p.c1 + n) : 0.f;
-          sVec[BN + i] = (n < p.N && p.bias != nullptr) ? __ldg(p.bias + n) : 0.f;
-        }
+        sVec[et] = nx_c1;
+        sVec[BN + et] = nx_bias;
         named_bar_sync(1, GEMM_EPI_WARPS * 32);
       }
       // LayerNorm fold: per-row mean / rstd from the partial sums left by the producing GEMM
       float mean = 0.f, rstd = 1.f;
       if constexpr (EpiTraits<EPI>::kOutBf16) {
         if (p.stats != nullptr && row < p.M) {
-          // all partial pairs in flight at once (a dependent add per load would serialise
-          // stats_parts L2 round trips on the in-order issue path)
-          const float4* sp = reinterpret_cast<const float4*>(p.stats + (size_t)row * p.stats_stride);
-          float4 t[GEMM_MAX_STAT_PARTS / 2];
-#pragma unroll
-          for (int i = 0; i < GEMM_MAX_STAT_PARTS / 2; ++i)
-            t[i] = (2 * i < p.stats_parts) ? __ldg(sp + i) : make_float4(0.f, 0.f, 0.f, 0.f);
           float s = 0.f, ss = 0.f;
 #pragma unroll
           for (int i = 0; i < GEMM_MAX_STAT_PARTS / 2; ++i) {
-            s += t[i].x + t[i].z;
-            ss += t[i].y + t[i].w;
+            s += nx_st[i].x + nx_st[i].z;
+            ss += nx_st[i].y + nx_st[i].w;
           }
           mean = s * p.inv_d;
           const float var = fmaxf(fmaf(-mean, mean, ss * p.inv_d), 0.f);
           rstd = rsqrtf(var + p.eps);
         }
       }
-      // pull the NEXT tile's per-row sums and per-column vectors towards L1 while this tile is
-      // processed (their L2 latency otherwise sits on the epilogue's critical path every tile)
-      if constexpr (EpiTraits<EPI>::kUsesVec) {
-        const int nt = tile + unit_stride;
-        if (nt < num_tiles) {
-          const int nn = (nt % n_tiles) * BN + et;
-          if (nn < p.N && p.bias != nullptr) {
-            prefetch_l1(p.bias + nn);
-            if (p.stats != nullptr) prefetch_l1(p.c1 + nn);
-          }
-          if constexpr (EpiTraits<EPI>::kOutBf16) {
-            const int nrow = (m_unit_of(nt) * CG + (int)rank) * GEMM_BM + q * 32 + lane;
-            if (p.stats != nullptr && nrow < p.M) {
-              const float* np_ = p.stats + (size_t)nrow * p.stats_stride;
-              prefetch_l1(np_);
-              prefetch_l1(np_ + 2 * p.stats_parts - 1);
-            }
-          }
-        }
-      }
+      // the NEXT unit's vectors and row sums: in flight while this unit is processed (two L2 round
+      // trips sat at the top of every unit when they were loaded here for the current one -- the
+      // SM's L1 is all shared memory in this kernel, so a prefetch hint did not stick)
+      fetch_unit_inputs(tile + unit_stride);
       unsigned long long pool_t = ~0ull;  // EPI_THRESH_POOL: this row's running threshold
       float pool_tf = INFINITY;           // its key part as a float (v >= pool_tf <=> key bits >= t_hi)
       if constexpr (EpiTraits<EPI>::kPool) {
