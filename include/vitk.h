@@ -267,6 +267,24 @@ int vitk_hmm_decode_counts(vitk_handle h, const int32_t* counts_dev, int k,
 int vitk_hmm_stream_begin(vitk_handle h, long long capacity_frames);
 int vitk_hmm_stream_append_counts(vitk_handle h, const int32_t* counts_dev, int n, int k, void* stream);
 int vitk_hmm_stream_finish(vitk_handle h, int32_t* states_out_dev, long long* frames_out, void* stream);
+/* Viterbi decode that ALLOCATES NOTHING.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same arithmetic and output as vitk_hmm_decode_counts
+ * for ONE sequence of n_frames frames (counts_dev (n_frames,3) int32, states_out_dev (n_frames)
+ * int32, both caller-owned device buffers), but the scratch that entry point keeps in cudaMalloc'd
+ * buffers of the handle (log emissions, backpointers, offsets) lives in a fixed array inside the
+ * library image: 3.4 MB of device memory that every GPU which loads the library holds until exit.
+ * Limits: n_frames <= VITK_HMM_STATIC_MAX_FRAMES and 1 <= k <= VITK_HMM_STATIC_MAX_K; anything
+ * larger returns non-zero with the reason in vitk_last_error(NULL) -- nothing is truncated.
+ * Needs no handle; runs on the CURRENT device, asynchronously on `stream`; no cudaMalloc, cudaFree
+ * or other allocating call is made (the first call on a device resolves the array's address).
+ * All calls on one GPU share the array, which keeps the last call's contents (no part of it has
+ * to start at zero: every entry read is rewritten by the same call first); two calls that overlap
+ * on the GPU (different streams, no ordering between them) RACE -- order them. */
+#define VITK_HMM_STATIC_MAX_FRAMES 131072
+#define VITK_HMM_STATIC_MAX_K 128
+int vitk_hmm_decode_counts_static(const int32_t* counts_dev, int n_frames, int k,
+                                  int32_t* states_out_dev, void* stream);
 /* Same for arbitrary per-frame probabilities (T,3) float64 on the host (the dicts handed to
  * add_first / add_col_to_lattice); outputs on the host; synchronous. */
 int vitk_hmm_decode_probs_host(vitk_handle h, const double* probs_host,

@@ -88,6 +88,7 @@ SIGNATURES = {
     "vitk_bank_write": (_i, [_vp, _i, _vp, _i, _vp, _i, _i, _vp]),
     "vitk_bank_rows": (_i, [_vp]),
     "vitk_hmm_decode_counts": (_i, [_vp, _vp, _i, _vp, _i, _vp, _vp, _vp]),
+    "vitk_hmm_decode_counts_static": (_i, [_vp, _i, _i, _vp, _vp]),
     "vitk_hmm_decode_probs_host": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
     "vitk_hmm_stream_begin": (_i, [_vp, C.c_longlong]),
     "vitk_hmm_stream_append_counts": (_i, [_vp, _vp, _i, _i, _vp]),

@@ -11,6 +11,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <mutex>
 #include <set>
 #include <string>
 #include <vector>
@@ -2309,6 +2310,101 @@ extern "C" int vitk_hmm_decode_probs_host(vitk_handle h, const double* probs_hos
   cudaFree(states_dev);
   cudaFree(dp_dev);
   return rc;
+}
+
+// ------------------------------------------------------------------------------------------
+// Viterbi decode that allocates nothing (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving
+// loops).  The scratch vitk_hmm_decode_counts keeps in per-handle cudaMalloc'd buffers -- the
+// log-emission table [T,3] f64, the backpointers [T,3] i8 and the sequence offsets -- lives in ONE
+// file-scope device array of fixed size that every GPU loading the library holds until exit.
+// ------------------------------------------------------------------------------------------
+#define VITK_HMM_STATIC_MAX_FRAMES_ 131072
+#define VITK_HMM_STATIC_MAX_K_ 128
+namespace {
+constexpr size_t kHmmStaticLogeBytes = (size_t)VITK_HMM_STATIC_MAX_FRAMES_ * 3 * sizeof(double);
+constexpr size_t kHmmStaticBpBytes = (size_t)VITK_HMM_STATIC_MAX_FRAMES_ * 3;
+constexpr size_t kHmmStaticBytes = kHmmStaticLogeBytes + kHmmStaticBpBytes + 256;  // + offsets {0, T}
+}  // namespace
+static __device__ __align__(256) unsigned char g_hmm_static_scratch[kHmmStaticBytes];  // 3.4 MB
+
+namespace {
+// the emission table travels as a kernel argument (2 * (k + 1) doubles <= 2 064 B): filled on the
+// host with the libm log the reference's math.log calls, and no copy that would need a staging buffer
+struct HmmStaticTable { double v[2 * (VITK_HMM_STATIC_MAX_K_ + 1)]; };
+
+__global__ void __launch_bounds__(256)
+hmm_emission_static_kernel(const int32_t* __restrict__ counts, int n, int k, const HmmStaticTable tab,
+                           double* __restrict__ loge, int* __restrict__ offsets) {
+  if (blockIdx.x == 0 && threadIdx.x == 0) { offsets[0] = 0; offsets[1] = n; }
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < (long long)n * 3;
+       i += (long long)gridDim.x * blockDim.x) {
+    int c = counts[i];
+    c = c < 0 ? 0 : (c > k ? k : c);
+    loge[i] = tab.v[(i < 3 ? 0 : k + 1) + c];   // same two rows as hmm_emission_from_counts_kernel
+  }
+}
+
+// device address of the scratch array, looked up once per device with that device current (in
+// host code the array's NAME is a host-side stand-in, not a device pointer)
+constexpr int kMaxDevices = 64;
+std::mutex g_hmm_static_mu;
+unsigned char* g_hmm_static_ptr[kMaxDevices] = {};
+}  // namespace
+
+extern "C" int vitk_hmm_decode_counts_static(const int32_t* counts_dev, int n_frames, int k,
+                                             int32_t* states_out_dev, void* stream) {
+  Err& e = g_op_err;
+  auto fail = [&]() { g_create_error = e.msg; return 1; };
+  if (n_frames == 0) return 0;
+  if (!counts_dev || !states_out_dev || n_frames < 0) { e.set("vitk_hmm_decode_counts_static: bad argument"); return fail(); }
+  if (n_frames > VITK_HMM_STATIC_MAX_FRAMES_) {
+    e.set("vitk_hmm_decode_counts_static: %d frames exceed the static scratch (at most %d frames per call; "
+          "use vitk_hmm_decode_counts or the streamed form)", n_frames, VITK_HMM_STATIC_MAX_FRAMES_);
+    return fail();
+  }
+  if (k < 1 || k > VITK_HMM_STATIC_MAX_K_) {
+    e.set("vitk_hmm_decode_counts_static: k = %d outside 1..%d", k, VITK_HMM_STATIC_MAX_K_);
+    return fail();
+  }
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+    e.set("vitk_hmm_decode_counts_static: no current CUDA device");
+    return fail();
+  }
+  unsigned char* base = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_hmm_static_mu);
+    if (!g_hmm_static_ptr[dev]) {
+      void* sym = nullptr;
+      const cudaError_t rc = cudaGetSymbolAddress(&sym, g_hmm_static_scratch);
+      if (rc != cudaSuccess || !sym) {
+        e.set("vitk_hmm_decode_counts_static: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(rc));
+        return fail();
+      }
+      g_hmm_static_ptr[dev] = static_cast<unsigned char*>(sym);
+    }
+    base = g_hmm_static_ptr[dev];
+  }
+  double* loge = reinterpret_cast<double*>(base);
+  int8_t* bp = reinterpret_cast<int8_t*>(base + kHmmStaticLogeBytes);
+  int* offsets = reinterpret_cast<int*>(base + kHmmStaticLogeBytes + kHmmStaticBpBytes);
+  HmmStaticTable tab;
+  for (int c = 0; c <= k; ++c) {
+    const double pr = (double)c / (double)k;
+    tab.v[c] = std::log(pr + 0.000001);                        // hmm.py:36-38
+    tab.v[k + 1 + c] = std::log(c == 0 ? 0.000001 : pr);      // hmm.py:45-50
+  }
+  for (int c = 2 * (k + 1); c < 2 * (VITK_HMM_STATIC_MAX_K_ + 1); ++c) tab.v[c] = 0.0;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  // nothing in the scratch has to start at zero: every entry the Viterbi kernel reads (emissions
+  // [0, 3T), offsets, backpointers of columns it has written) is rewritten by this call first
+  const int blocks = (n_frames * 3 + 255) / 256;
+  hmm_emission_static_kernel<<<blocks < 64 ? blocks : 64, 256, 0, st>>>(counts_dev, n_frames, k, tab, loge, offsets);
+  if (cudaGetLastError() != cudaSuccess) { e.set("vitk_hmm_decode_counts_static: emission launch failed"); return fail(); }
+  hmm_viterbi_kernel<<<1, 32, 0, st>>>(loge, offsets, 1, hmm_params(), bp, states_out_dev, nullptr);
+  if (cudaGetLastError() != cudaSuccess) { e.set("vitk_hmm_decode_counts_static: viterbi launch failed"); return fail(); }
+  return 0;
 }
 
 // ------------------------------------------------------------------------------------------
