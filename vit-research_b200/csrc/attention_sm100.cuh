@@ -79,8 +79,9 @@ __global__ void __launch_bounds__(ATT_THREADS, WIDE ? 1 : 2)
 attention_v2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
                  const __grid_constant__ CUtensorMap tmO, const AttnParams p) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~static_cast<uintptr_t>(1023));
+  // aligned by POINTER arithmetic on the __shared__ array: an integer round trip makes every access
+  // through the result a generic LD / ST (with R2UR descriptor traffic) instead of LDS / STS
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const AttnSmemLayout L = attn_smem_layout(p.S);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.off_bar);
   uint64_t* bar_qk = bars + 0;
@@ -376,8 +377,9 @@ __global__ void __launch_bounds__(ATT3_THREADS, 1)
 attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
                  const __grid_constant__ CUtensorMap tmO, const AttnParams p) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~static_cast<uintptr_t>(1023));
+  // aligned by POINTER arithmetic on the __shared__ array: an integer round trip makes every access
+  // through the result a generic LD / ST (with R2UR descriptor traffic) instead of LDS / STS
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const Attn3SmemLayout L = attn3_smem_layout(p.S);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.off_bar);
   uint64_t* kv_full = bars + 0;      // [2] stage
@@ -843,8 +845,9 @@ __global__ void __launch_bounds__(ATT3_THREADS, 1)
 attention_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
                        const __grid_constant__ CUtensorMap tmO, const AttnParams p) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~static_cast<uintptr_t>(1023));
+  // aligned by POINTER arithmetic on the __shared__ array: an integer round trip makes every access
+  // through the result a generic LD / ST (with R2UR descriptor traffic) instead of LDS / STS
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const Attn5SmemLayout L = attn5_smem_layout(p.S);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.off_bar);
   uint64_t* kv_full = bars + 0;      // [2] stage
@@ -1302,8 +1305,9 @@ __global__ void __launch_bounds__(ATT3_THREADS, 1)
 attention_smemp_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
                        const __grid_constant__ CUtensorMap tmO, const AttnParams p) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~static_cast<uintptr_t>(1023));
+  // aligned by POINTER arithmetic on the __shared__ array: an integer round trip makes every access
+  // through the result a generic LD / ST (with R2UR descriptor traffic) instead of LDS / STS
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const Attn6SmemLayout L = attn6_smem_layout(p.S);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.off_bar);
   uint64_t* kv_full = bars + 0;      // [2] stage

@@ -184,8 +184,9 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   constexpr int CH = EpiTraits<EPI>::kChunkCols;
 
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~static_cast<uintptr_t>(1023));
+  // aligned by POINTER arithmetic on the __shared__ array: an integer round trip makes every access
+  // through the result a generic LD / ST (with R2UR descriptor traffic) instead of LDS / STS
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   if (threadIdx.x == 0 &&
       static_cast<uint32_t>(smem - smem_raw) + Cfg::kCarveBytes > dynamic_smem_size()) {
     printf("vitk: gemm dynamic smem window misaligned (%u B needed)\n",
