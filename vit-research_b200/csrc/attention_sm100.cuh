@@ -91,7 +91,7 @@ attention_v2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
 
   const int tid = threadIdx.x;
-  const int warp = tid >> 5, lane = tid & 31;
+  const int warp = uniform_warp_idx(), lane = tid & 31;
   const int blk = blockIdx.x % p.nblk;              // query block (fastest: K/V re-read hits L2)
   const int fh = blockIdx.x / p.nblk;
   const int frame = fh / p.heads;
@@ -394,7 +394,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 18);
 
   const int tid = threadIdx.x;
-  const int warp = tid >> 5, lane = tid & 31;
+  const int warp = uniform_warp_idx(), lane = tid & 31;
   const int D = p.heads * ATT_D;
   const int S = p.S, SK = L.sk;
   const int units = p.frames * p.heads;
@@ -451,11 +451,14 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     // becoming free and its next S being issued (wait_S ~800 cycles, P.V issued ~300 cycles late).
     // p.one_issuer != 0 keeps the single-thread form for A/B runs.
     const bool both = p.one_issuer != 0;
-    if (lane == 0 && (warp == 1 || !both)) {
+    if (!both || (lane == 0 && warp == 1)) {
       const int my_units = (units - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
       const uint32_t idesc_s = make_idesc_bf16_f32(128, (uint32_t)SK, false, false);
       const uint32_t idesc_o = make_idesc_bf16_f32(128, ATT_D, false, true);
       if (!both) {
+        // the whole warp walks the chain (warp-uniform control flow) and ONE elected lane issues:
+        // the tcgen05.mma operands then sit in uniform registers, one instruction each, where
+        // `if (lane == 0)` code wraps every one of them in an ELECT / R2UR loop (see gemm_sm100.cuh)
         const int s = warp == 1 ? 0 : 1;
         const uint32_t t_slot = tmem_base + s * 256;
         for (int j = 0; j < my_units; ++j) {
@@ -466,29 +469,35 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           mbar_wait(&kv_full[st], sph);
           mbar_wait(&slot_free[s], uph ^ 1u);
           tc_fence_after_sync();
-          if (b < nblk) {
-            const uint64_t dq = make_smem_desc_sw128(smem_u32(sb + b * 16384), 1024, 0);
-            const uint64_t dk = make_smem_desc_sw128(smem_u32(sb + 32768), 1024, 0);
+          if (elect_one_sync()) {
+            if (b < nblk) {
+              const uint64_t dq = make_smem_desc_sw128(smem_u32(sb + b * 16384), 1024, 0);
+              const uint64_t dk = make_smem_desc_sw128(smem_u32(sb + 32768), 1024, 0);
 #pragma unroll
-            for (int k = 0; k < ATT_D / 16; ++k)
-              umma_bf16_ss(t_slot, dq + 2 * k, dk + 2 * k, idesc_s, k != 0 ? 1u : 0u);
+              for (int k = 0; k < ATT_D / 16; ++k)
+                umma_bf16_ss(t_slot, dq + 2 * k, dk + 2 * k, idesc_s, k != 0 ? 1u : 0u);
+            }
+            umma_commit(&s_full[s]);
           }
-          umma_commit(&s_full[s]);
+          __syncwarp();
           mbar_wait(&p_full[s], uph);
           mbar_wait(&v_full[st], sph);
           tc_fence_after_sync();
-          const bool mdbg = p.dbg != nullptr && blockIdx.x == 0 && j < 16;
+          const bool mdbg = p.dbg != nullptr && blockIdx.x == 0 && j < 16 && lane == 0;
           if (mdbg) p.dbg[(s * 16 + j) * 8 + 6] = clock64();
-          if (b < nblk) {
-            const uint32_t sv = smem_u32(sb + 32768 + L.kv_bytes);
-            const uint64_t dv0 = make_smem_desc_sw128(sv, 1024, 1024);
-            const uint32_t t_o_acc = t_slot + SK / 2;
-            umma_bf16_ts(t_o_acc, t_slot, dv0, idesc_o, 0u);
+          if (elect_one_sync()) {
+            if (b < nblk) {
+              const uint32_t sv = smem_u32(sb + 32768 + L.kv_bytes);
+              const uint64_t dv0 = make_smem_desc_sw128(sv, 1024, 1024);
+              const uint32_t t_o_acc = t_slot + SK / 2;
+              umma_bf16_ts(t_o_acc, t_slot, dv0, idesc_o, 0u);
 #pragma unroll 4
-            for (int kk = 1; kk < SK / 16; ++kk)
-              umma_bf16_ts(t_o_acc, t_slot + kk * 8, dv0 + (uint64_t)(kk * 128), idesc_o, 1u);
+              for (int kk = 1; kk < SK / 16; ++kk)
+                umma_bf16_ts(t_o_acc, t_slot + kk * 8, dv0 + (uint64_t)(kk * 128), idesc_o, 1u);
+            }
+            umma_commit(&o_full[s]);
           }
-          umma_commit(&o_full[s]);
+          __syncwarp();
           if (mdbg) p.dbg[(s * 16 + j) * 8 + 7] = clock64();
         }
       } else {
@@ -865,7 +874,7 @@ attention_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
   float* s_sum = reinterpret_cast<float*>(smem + L.off_sum);
 
   const int tid = threadIdx.x;
-  const int warp = tid >> 5, lane = tid & 31;
+  const int warp = uniform_warp_idx(), lane = tid & 31;
   const int D = p.heads * ATT_D;
   const int S = p.S, SK = L.sk;
   const int units = p.frames * p.heads;
@@ -1325,7 +1334,7 @@ attention_smemp_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
   volatile int* redo_flag = reinterpret_cast<volatile int*>(bars + 23);  // [2] slot: P.V was issued by the exact path
 
   const int tid = threadIdx.x;
-  const int warp = tid >> 5, lane = tid & 31;
+  const int warp = uniform_warp_idx(), lane = tid & 31;
   const int D = p.heads * ATT_D;
   const int S = p.S, SK = L.sk;
   const int units = p.frames * p.heads;

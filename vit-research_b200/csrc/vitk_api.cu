@@ -277,8 +277,9 @@ int launch_attention(Err& e, const CUtensorMap& tq, const CUtensorMap& tkv, cons
   p.nblk = (p.q_rows + 127) / 128;
   p.reverse = reverse;
   {
-    static int handover = -1;  // VITK_ATTN_HANDOVER: chunk after which the exp2 turn is passed on
-    if (handover < 0) { const char* hv = getenv("VITK_ATTN_HANDOVER"); handover = hv ? atoi(hv) : 1000; if (handover < 0) handover = 0; }
+    static int handover = -1;  // VITK_ATTN_HANDOVER: chunk after which the exp2 turn is passed on (default 4 of 6.5;
+                               // 1000 = at the end of the pass, the round-1 behaviour)
+    if (handover < 0) { const char* hv = getenv("VITK_ATTN_HANDOVER"); handover = hv ? atoi(hv) : 4; if (handover < 0) handover = 0; }
     p.handover = handover;
     static int one_issuer = -1;  // VITK_ATTN_ISSUER=1: the round-1 single MMA-issuing thread
     if (one_issuer < 0) { const char* iv = getenv("VITK_ATTN_ISSUER"); one_issuer = (iv && atoi(iv) == 1) ? 1 : 0; }
