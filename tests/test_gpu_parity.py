@@ -369,6 +369,9 @@ def test_code_path_variants_agree():
     assert cos.min() > 0.9999, cos.min()        # measured 0.999989
     # last layer: Q projected for the CLS rows only vs for every token: same arithmetic for the rows read
     assert np.array_equal(base, _fingerprint({"VITK_SPLIT_LAST_QKV": "0"}))
+    # programmatic dependent launch of the GEMM / attention chain (default) vs plain stream order:
+    # the same kernels on the same data -- bit for bit, or the early launch read something too soon
+    assert np.array_equal(base, _fingerprint({"VITK_PDL": "0"}))
     # residual stream kept in bf16 in place (default) vs the fp32 master copy + bf16 copy of
     # round 1: one bf16 rounding per residual add separates them
     rf32 = _fingerprint({"VITK_RESID_F32": "1"})

@@ -400,6 +400,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   const int units = p.frames * p.heads;
   const int nblk = p.nblk;
 
+  griddep_launch_dependents();
   if (tid == 0) {
     tma_prefetch_desc(&tmQ);
     tma_prefetch_desc(&tmKV);
@@ -422,6 +423,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_slot;
+  griddep_wait();  // the QKV GEMM's output is read (and `out` written) only from here on
 
   if (warp == 0) {
     // ------------------------------ loader ------------------------------

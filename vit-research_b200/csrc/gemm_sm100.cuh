@@ -220,6 +220,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   // row unit of work unit t: ascending, or descending when the caller walks this GEMM backwards
   auto m_unit_of = [&](int t) { return p.reverse_m ? m_units - 1 - t / n_tiles : t / n_tiles; };
 
+  griddep_launch_dependents();
   if (warp == GEMM_PRODUCER_WARP && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
@@ -247,6 +248,9 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   else __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_slot;
+  // everything above touched only this CTA's shared / tensor memory and kernel parameters; from
+  // here on the previous kernel's output is read (and buffers it may still read are written)
+  griddep_wait();
 
   if (warp == GEMM_PRODUCER_WARP) {
     // ------------------------------ TMA producer ------------------------------

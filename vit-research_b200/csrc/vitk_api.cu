@@ -148,6 +148,15 @@ int num_sms() {
   return g_num_sms;
 }
 
+// Programmatic dependent launch for the GEMM and attention kernels of the forward (they call
+// griddepcontrol.wait before their first global access): the next kernel's CTAs take over each SM as
+// the previous kernel's leave it.  VITK_PDL=0 restores plain stream order (the parity tests run both).
+bool pdl_enabled() {
+  static int on = -1;
+  if (on < 0) { const char* v = getenv("VITK_PDL"); on = (v && atoi(v) == 0) ? 0 : 1; }
+  return on != 0;
+}
+
 template <int BN, int EPI, int CG, bool S6 = false>
 int launch_gemm_t(Err& e, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& c,
                   const CUtensorMap& r, const GemmParams& p, cudaStream_t st) {
@@ -167,13 +176,15 @@ int launch_gemm_t(Err& e, const CUtensorMap& a, const CUtensorMap& b, const CUte
   cfg.blockDim = dim3(GEMM_THREADS, 1, 1);
   cfg.dynamicSmemBytes = Cfg::kSmemBytes;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = CG;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = pdl_enabled() ? 2 : 1;
   CK(e, cudaLaunchKernelEx(&cfg, kern, a, b, c, r, p));
   return 0;
 }
@@ -339,7 +350,17 @@ int launch_attention(Err& e, const CUtensorMap& tq, const CUtensorMap& tkv, cons
     }
     const int units = frames * heads;
     const int grid = units < num_sms() ? units : num_sms();
-    attention_kernel<<<grid, ATT3_THREADS, L.total, st>>>(tq, tkv, to, p);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid, 1, 1);
+    cfg.blockDim = dim3(ATT3_THREADS, 1, 1);
+    cfg.dynamicSmemBytes = (size_t)L.total;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    CK(e, cudaLaunchKernelEx(&cfg, attention_kernel, tq, tkv, to, p));
   }
   CK(e, cudaGetLastError());
   return 0;

@@ -76,6 +76,16 @@ __device__ __forceinline__ bool mbar_test_wait(uint64_t* bar, uint32_t parity) {
 }
 // Bounded wait: a protocol bug must trap, never hang the box (a hung GPU is a strike).
 // try_wait itself sleeps in hardware for a bounded time, so this loop is cheap.
+// Programmatic dependent launch (kernels launched with cudaLaunchAttributeProgrammaticStreamSerialization;
+// no-ops otherwise).  launch_dependents: the NEXT kernel of the stream may be scheduled as soon as
+// every CTA of this grid has issued it or exited -- its CTAs become resident as ours leave and run
+// their prologue (barrier init, TMEM allocation, descriptor prefetch) instead of waiting for the
+// whole grid to drain.  wait: returns once the PREVIOUS grid has completed and its memory is
+// visible; nothing that grid wrote (or still reads) may be touched before it.
+__device__ __forceinline__ void griddep_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 // One lane of a fully converged warp (always the same one).  Code that reaches this through
 // warp-uniform control flow keeps its operands in uniform registers, so a tcgen05.mma / TMA issue
 // under `if (elect_one_sync())` is ONE instruction; under `if (lane == 0)` ptxas wraps every such
