@@ -392,6 +392,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   uint64_t* redo_bar = bars + 14;    // [2] slot: exact-path recomputation of S
   uint64_t* turn_bar = bars + 16;    // [2] group: "your turn on the exp2 units", count 4
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 18);
+  uint64_t* qk_empty = bars + 20;    // [2] stage, count 2: Q / K of the stage are dead (both blocks' passes done)
 
   const int tid = threadIdx.x;
   const int warp = uniform_warp_idx(), lane = tid & 31;
@@ -409,6 +410,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       mbar_init(&kv_full[i], 1);
       mbar_init(&v_full[i], 1);
       mbar_init(&stage_empty[i], 2);
+      mbar_init(&qk_empty[i], 2);
       mbar_init(&s_full[i], 1);
       mbar_init(&p_full[i], 4);
       mbar_init(&o_full[i], 1);
@@ -435,11 +437,17 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         const int uu = p.reverse ? units - 1 - u : u;
         const int frame = uu / p.heads, head = uu % p.heads;
         uint8_t* sb = smem + st * L.stage_bytes;
-        mbar_wait(&stage_empty[st], ph ^ 1u);
+        // Q and K of a stage die when both blocks' softmax passes are over (the exact-path redo, the
+        // last reader of Q / K, is decided there), V only when both P.V chains have retired ~800
+        // cycles later: the next-but-one unit's Q / K load -- 58 KB that take 2 200-3 300 cycles to
+        // land and sit on the critical path of the next S = Q K^T -- starts that much earlier
+        mbar_wait(&qk_empty[st], ph ^ 1u);
+        if (p.dbg != nullptr && blockIdx.x == 0 && j < 16) p.dbg[(2 * 16 + j) * 8 + 0] = clock64();
         mbar_arrive_expect_tx(&kv_full[st], 16384 * nblk + SK * 128);
         tma_load_3d(sb, &tmQ, &kv_full[st], head * ATT_D, 0, frame);
         if (nblk == 2) tma_load_3d(sb + 16384, &tmQ, &kv_full[st], head * ATT_D, 128, frame);
         tma_load_3d(sb + 32768, &tmKV, &kv_full[st], D + head * ATT_D, 0, frame);
+        mbar_wait(&stage_empty[st], ph ^ 1u);
         mbar_arrive_expect_tx(&v_full[st], SK * 128);
         tma_load_3d(sb + 32768 + L.kv_bytes, &tmKV, &v_full[st], 2 * D + head * ATT_D, 0, frame);
       }
@@ -468,8 +476,11 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           const uint32_t sph = (j >> 1) & 1, uph = j & 1;
           const int b = s ^ (j & 1);  // query block this slot holds in unit j
           uint8_t* sb = smem + st * L.stage_bytes;
+          const bool ldbg = p.dbg != nullptr && blockIdx.x == 0 && j < 16 && lane == 0;
           mbar_wait(&kv_full[st], sph);
+          if (ldbg) p.dbg[(2 * 16 + j) * 8 + 1 + s] = clock64();
           mbar_wait(&slot_free[s], uph ^ 1u);
+          if (ldbg) p.dbg[(2 * 16 + j) * 8 + 3 + s] = clock64();
           tc_fence_after_sync();
           if (elect_one_sync()) {
             if (b < nblk) {
@@ -584,6 +595,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       long long* dbg = p.dbg + (g * 16 + j) * 8;
       if (dbg_on) dbg[0] = clock64();
       mbar_wait(&s_full[g], uph);
+      if (dbg_on) p.dbg[(2 * 16 + j) * 8 + 5 + g] = clock64();
       // The two warpgroups take turns in the softmax: g0(unit j) -> g1(unit j) -> g0(unit j+1) ...
       // Left alone they run in lock-step — both in the exp2 loop at once (the MUFU pipe is the
       // loop's bound, so the pass takes twice as long), then both waiting while the single MMA
@@ -755,6 +767,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       if (lane == 0) {
         mbar_arrive(&p_full[g]);
         if (!handed) mbar_arrive(&turn_bar[g ^ 1]);  // hand the exp2 units to the other warpgroup
+        if (wq == 0) mbar_arrive(&qk_empty[st]);     // past the redo decision: this block is done with Q / K
       }
       if (dbg_on) dbg[3] = clock64();
 

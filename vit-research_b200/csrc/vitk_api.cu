@@ -2594,7 +2594,7 @@ extern "C" int vitk_op_chunk_head(const float* x, const float* w1, const float* 
   return 0;
 }
 
-// Developer hook (not in include/vitk.h): device buffer of 2*16*8 int64 clock samples written by
+// Developer hook (not in include/vitk.h): device buffer of 3*16*8 int64 clock samples written by
 // CTA 0 of the attention kernel; pass NULL to switch the instrumentation off.
 extern "C" int vitk_dev_attn_timeline(long long* buf_dev) {
   g_attn_dbg = buf_dev;
