@@ -437,6 +437,23 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
       const float nmr = -mean * rstd;  // y = rstd*acc + nmr*c1 + c2
       float st_s = 0.f, st_ss = 0.f;   // EPI_BIAS_RESID_F32: this warp's partial row statistics
+      // EPI_THRESH_POOL: this lane's survivors of the unit, entry e at word (e * 32 + lane) of the
+      // warp's staging tile(s) (conflict-free), flushed to the row's pool after the last chunk
+      // (the first staging tile holds the chunk's parked scores, the second the list: 16 entries per lane)
+      constexpr int kPoolList = (NBUF - 1) * (GEMM_STAGING_BYTES / (32 * 8));
+      uint2* pool_list = reinterpret_cast<uint2*>(swarp + GEMM_STAGING_BYTES) + lane;
+      int pool_nh = 0;
+      auto pool_flush = [&]() {
+        if constexpr (EpiTraits<EPI>::kPool) {
+          if (pool_nh > 0) {
+            const int base = atomicAdd(p.pool_n + row, pool_nh);
+            uint2* prow = p.pool + (size_t)row * p.pool_cap;
+            for (int e_ = 0; e_ < pool_nh; ++e_)
+              if (base + e_ < p.pool_cap) prow[base + e_] = pool_list[e_ * 32];
+            pool_nh = 0;
+          }
+        }
+      };
       if (edbg && ew == 0) p.dbg[ti * 8 + 3] = clock64();
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after_sync();
@@ -505,15 +522,30 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             }
             if (p.pool_direct) {
               if (row < p.M) {
+                // slot n of the row's pool = bank row n (a row the query's predicate rejects leaves an
+                // EMPTY slot, key bits 0).  Four entries = one 32-byte store: every lane writes whole
+                // sectors of its own pool row (8-byte stores touched 32 sectors per instruction for
+                // 256 useful bytes and made this stage LSU-bound).
+                uint2* prow = p.pool + (size_t)row * p.pool_cap;
 #pragma unroll
-                for (int j = 0; j < 32; ++j)
-                  if (col0 + j < p.N && col0 + j < p.pool_cap) {
-                    // a row the query's predicate rejects leaves an EMPTY slot (key bits 0)
+                for (int j = 0; j < 32; j += 4) {
+                  uint32_t w[8];
+#pragma unroll
+                  for (int i = 0; i < 4; ++i) {
                     bool ok = true;
-                    if constexpr (EpiTraits<EPI>::kFilt) ok = knn_filter_pass(p.filt, row, p.col_base + col0 + j);
-                    p.pool[(size_t)row * p.pool_cap + col0 + j] = make_uint2(
-                        static_cast<uint32_t>(p.col_base + col0 + j), ok ? float_order_bits(v[j]) : 0u);
+                    if constexpr (EpiTraits<EPI>::kFilt)
+                      ok = col0 + j + i < p.N && knn_filter_pass(p.filt, row, p.col_base + col0 + j + i);
+                    w[2 * i] = static_cast<uint32_t>(p.col_base + col0 + j + i);
+                    w[2 * i + 1] = ok ? float_order_bits(v[j + i]) : 0u;
                   }
+                  if (col0 + j + 3 < p.N && col0 + j + 3 < p.pool_cap) {
+                    st_global_256(prow + col0 + j, make_uint4(w[0], w[1], w[2], w[3]), make_uint4(w[4], w[5], w[6], w[7]));
+                  } else {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                      if (col0 + j + i < p.N && col0 + j + i < p.pool_cap) prow[col0 + j + i] = make_uint2(w[2 * i], w[2 * i + 1]);
+                  }
+                }
               }
             } else {
               // branch-free common case: one float compare per score against the key part of
@@ -522,16 +554,32 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
               for (int j = 0; j < 32; ++j) hits |= (v[j] >= pool_tf) ? (1u << j) : 0u;
               if (hits != 0u) {
+                // RARE path, kept small on purpose (fully unrolled it was ~650 instructions that
+                // fell out of the instruction cache between uses: ~2 700 cycles per chunk with a
+                // hit): the lane parks its 32 scores in the warp's staging tile and walks the set
+                // bits in a rolled loop.  Exact composite test + per-query predicate; survivors go
+                // to the lane's list and reach the pool at the END of the unit with one atomicAdd
+                // per row, after the accumulator has gone back to the MMA warp.
+                float* sv = reinterpret_cast<float*>(swarp) + lane;  // score j at sv[j * 32]: conflict-free
 #pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                  if (((hits >> j) & 1u) && col0 + j < p.N) {
-                    const uint32_t kb = float_order_bits(v[j]);
-                    const uint32_t bi = static_cast<uint32_t>(p.col_base + col0 + j);
-                    const unsigned long long comp = (static_cast<unsigned long long>(kb) << 32) | (~bi);
-                    // the predicate runs only for the rare score that beats the threshold
-                    bool take = comp > pool_t;
-                    if constexpr (EpiTraits<EPI>::kFilt) take = take && knn_filter_pass(p.filt, row, (int)bi);
-                    if (take) {
+                for (int j = 0; j < 32; ++j) sv[j * 32] = v[j];
+                uint32_t hrest = hits;
+#pragma unroll 1
+                while (hrest != 0u) {
+                  const int j = __ffs(hrest) - 1;
+                  hrest &= hrest - 1u;
+                  if (col0 + j >= p.N) break;
+                  const uint32_t kb = float_order_bits(sv[j * 32]);
+                  const uint32_t bi = static_cast<uint32_t>(p.col_base + col0 + j);
+                  const unsigned long long comp = (static_cast<unsigned long long>(kb) << 32) | (~bi);
+                  bool t = comp > pool_t;
+                  if constexpr (EpiTraits<EPI>::kFilt) t = t && knn_filter_pass(p.filt, row, (int)bi);
+                  if (t) {
+                    if constexpr (kPoolList > 0) {
+                      if (pool_nh == kPoolList) pool_flush();
+                      pool_list[pool_nh * 32] = make_uint2(bi, kb);
+                      ++pool_nh;
+                    } else {
                       const int pos = atomicAdd(p.pool_n + row, 1);
                       if (pos < p.pool_cap) p.pool[(size_t)row * p.pool_cap + pos] = make_uint2(bi, kb);
                     }
@@ -724,7 +772,10 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             else mbar_arrive(&tempty_bar[acc]);
           }
         }
-        if constexpr (EpiTraits<EPI>::kPool) continue;  // nothing is stored
+        if constexpr (EpiTraits<EPI>::kPool) {  // nothing is stored through TMA
+          if (c == kChunks - 1) pool_flush();   // after the accumulator went back to the MMA warp
+          continue;
+        }
         if ((VITK_GEMM_EPI_STUB >= 2) && EpiTraits<EPI>::kOutBf16) continue;
         fence_proxy_async_smem();
         __syncwarp();

@@ -1547,6 +1547,7 @@ int knn_stage(vitk_ctx* h, int n, int kc, int cap, int metric, int lo, int hi, i
   gp.pool_l2 = metric == METRIC_L2 ? 1 : (h->knn_pen_cur ? 2 : 0);
   gp.pool_direct = direct ? 1 : 0;
   gp.filt = filt;
+  gp.dbg = g_gemm_dbg;   // developer timeline (tools/dev_store_timeline.py); null in production
   if (launch_gemm(e, filt.active ? EPI_THRESH_POOL_FILT : EPI_THRESH_POOL, ta, tb, ta, ta, gp, st)) return 1;
   h->launches += 1;
   return launch_pool_select(h, cap, n, kc, direct ? hi - lo : -1, 0, 0, nullptr, h->knn_overflow + flag, st);
