@@ -333,18 +333,35 @@ __device__ __forceinline__ void knn_score_candidates(const float* q_smem, const 
       br[s] = bank + (size_t)(b < 0 ? 0 : b) * d;
       acc[s] = 0.f;
     }
-    for (int i = lane * 4; i < d; i += 128) {
+    // Three 128-column steps (12 float4 loads per lane) are issued before the first FMA: rolled one
+    // step at a time every step waited for its own L2 / DRAM round trip (6 per candidate group at
+    // d = 768) and the kernel was pure latency.  Same accumulation order as the rolled loop.
+    auto step = [&](const float4& a, const float4& b, int s_) {
+      if (metric == METRIC_L2) {
+        const float dx = a.x - b.x, dy = a.y - b.y, dz = a.z - b.z, dw = a.w - b.w;
+        acc[s_] += (dx * dx + dy * dy) + (dz * dz + dw * dw);
+      } else {
+        acc[s_] += (a.x * b.x + a.y * b.y) + (a.z * b.z + a.w * b.w);
+      }
+    };
+    int i = lane * 4;
+    for (; i + 256 < d; i += 384) {
+      float4 a[3], b[3][4];
+#pragma unroll
+      for (int u = 0; u < 3; ++u) {
+        a[u] = *reinterpret_cast<const float4*>(q_smem + i + 128 * u);
+#pragma unroll
+        for (int s = 0; s < 4; ++s) b[u][s] = __ldg(reinterpret_cast<const float4*>(br[s] + i + 128 * u));
+      }
+#pragma unroll
+      for (int u = 0; u < 3; ++u)
+#pragma unroll
+        for (int s = 0; s < 4; ++s) step(a[u], b[u][s], s);
+    }
+    for (; i < d; i += 128) {
       const float4 a = *reinterpret_cast<const float4*>(q_smem + i);
 #pragma unroll
-      for (int s = 0; s < 4; ++s) {
-        const float4 b = __ldg(reinterpret_cast<const float4*>(br[s] + i));
-        if (metric == METRIC_L2) {
-          const float dx = a.x - b.x, dy = a.y - b.y, dz = a.z - b.z, dw = a.w - b.w;
-          acc[s] += (dx * dx + dy * dy) + (dz * dz + dw * dw);
-        } else {
-          acc[s] += (a.x * b.x + a.y * b.y) + (a.z * b.z + a.w * b.w);
-        }
-      }
+      for (int s = 0; s < 4; ++s) step(a, __ldg(reinterpret_cast<const float4*>(br[s] + i)), s);
     }
 #pragma unroll
     for (int s = 0; s < 4; ++s) {
