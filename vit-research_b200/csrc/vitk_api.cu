@@ -421,10 +421,11 @@ int launch_patchify(Err& e, const void* pix, int fmt, __nv_bfloat16* out, int n,
   p.fmt = fmt;
   p.mean = u8_mean;  // default: HF ViTImageProcessor (rescale 1/255, mean .5, std .5, fused)
   p.std = u8_std;
-  long long total = (long long)n * (p.gh * p.gw + 1) * (p.K / 8);
-  long long blocks = (total + 255) / 256;
-  if (blocks > 148 * 32) blocks = 148 * 32;
-  patchify_kernel<<<(int)blocks, 256, 0, st>>>(p);
+  const long long rows = (long long)n * (p.gh * p.gw + 1);   // one CTA per output row
+  if (rows > 0x7fffffffLL) { e.set("patchify: too many rows"); return 1; }
+  const int kv_per_row = p.K / 8;
+  const int threads = kv_per_row >= 256 ? 256 : ((kv_per_row + 31) / 32) * 32;
+  patchify_kernel<<<(unsigned)rows, threads, 0, st>>>(p);
   CK(e, cudaGetLastError());
   return 0;
 }
