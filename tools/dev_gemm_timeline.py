@@ -12,7 +12,7 @@ bf = torch.bfloat16
 parts = 6
 st = stream_ptr()
 shapes = {"qkv": (3 * D, D, 0, True), "fc1": (F, D, 1, True), "fc1_nogelu": (F, D, 0, True),
-          "fc1_plain": (F, D, 0, False), "fc2": (D, F, 7, False), "proj": (D, D, 7, False)}
+          "fc1_plain": (F, D, 0, False), "fc2": (D, F, 7, False), "proj": (D, D, 7, False), "patch": (D, D, 8, False)}
 which = sys.argv[1:] or list(shapes)
 for name in which:
     N, K, epi, fold = shapes[name]
@@ -22,7 +22,10 @@ for name in which:
     bias, c1 = torch.zeros(N, device="cuda"), torch.zeros(N, device="cuda")
     stats = torch.zeros(M, parts, 2, device="cuda"); stats[:, 0, 1] = float(K)
     so = torch.zeros(M, 2 * ((N + 255) // 256), 2, device="cuda")
+    table = torch.randn(197, N, device="cuda")
     def run():
+        if epi == 8:   # patch embedding: acc + position / CLS / bias table -> bf16 stream
+            return lib.vitk_op_gemm(ptr(a), ptr(w), ptr(out), M, N, K, epi, None, None, ptr(table), 197, st)
         if epi == 7:
             return lib.vitk_op_gemm_fused(ptr(a), ptr(w), ptr(out), M, N, K, epi, ptr(bias), None, None, 0, 1e-12,
                                           ptr(out), None, ptr(so), st)
