@@ -1533,7 +1533,7 @@ int launch_pool_select(vitk_ctx* h, int cap, int n, int kc, int direct_rows, int
 // One stage of the large-store walk: bank rows [lo, hi) through the threshold-filter GEMM, then
 // the pool select (flag = overflow slot).
 int knn_stage(vitk_ctx* h, int n, int kc, int cap, int metric, int lo, int hi, int flag, bool direct,
-              const KnnFilter& filt, cudaStream_t st) {
+              const KnnFilter& filt, cudaStream_t st, int32_t* cand = nullptr) {
   Err& e = h->err;
   const int d = h->bank_d;
   CUtensorMap ta, tb;
@@ -1551,7 +1551,9 @@ int knn_stage(vitk_ctx* h, int n, int kc, int cap, int metric, int lo, int hi, i
   gp.dbg = g_gemm_dbg;   // developer timeline (tools/dev_store_timeline.py); null in production
   if (launch_gemm(e, filt.active ? EPI_THRESH_POOL_FILT : EPI_THRESH_POOL, ta, tb, ta, ta, gp, st)) return 1;
   h->launches += 1;
-  return launch_pool_select(h, cap, n, kc, direct ? hi - lo : -1, 0, 0, nullptr, h->knn_overflow + flag, st);
+  // cand != null: this is the walk's last stage -- its select also writes the candidate lists, which
+  // stand if no stage overflowed (the separate final select is then skipped)
+  return launch_pool_select(h, cap, n, kc, direct ? hi - lo : -1, 0, 0, cand, h->knn_overflow + flag, st);
 }
 
 // Candidate rows (h->knn_cand [n, kc]) for a bank of more than KNN_DIRECT_MAX rows.  All stages
@@ -1604,7 +1606,8 @@ int knn_large_candidates(vitk_ctx* h, int n, int kc, int metric, const KnnFilter
       CK(e, cudaMemsetAsync(h->knn_overflow, 0, KNN_MAX_STAGES * sizeof(int), st));
       for (size_t i = 0; i < cnt; ++i)
         if (knn_stage(h, n, kc, cap, metric, todo[base + i].lo, todo[base + i].hi, (int)i,
-                      first_pass && base + i == 0, filt, st))
+                      first_pass && base + i == 0, filt, st,
+                      base + i + 1 == todo.size() ? h->knn_cand : nullptr))
           return 1;
       CK(e, cudaMemcpyAsync(h->knn_overflow_host, h->knn_overflow, KNN_MAX_STAGES * sizeof(int),
                             cudaMemcpyDeviceToHost, st));
@@ -1624,10 +1627,11 @@ int knn_large_candidates(vitk_ctx* h, int n, int kc, int metric, const KnnFilter
         for (int lo = s.lo; lo < s.hi; lo += q4) next.push_back({lo, lo + q4 < s.hi ? lo + q4 : s.hi});
       }
     }
+    if (next.empty()) return 0;   // the last stage's select has already written the candidates
     todo.swap(next);
     first_pass = false;
   }
-  // final select: candidates for the fp32 re-rank
+  // (only reached with an empty walk) final select: candidates for the fp32 re-rank
   return launch_pool_select(h, cap, n, kc, -1, 0, 0, h->knn_cand, h->knn_overflow, st);
 }
 
