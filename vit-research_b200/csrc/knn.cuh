@@ -394,12 +394,13 @@ __device__ __forceinline__ void knn_score_candidates(const float* q_smem, const 
   }
 }
 
-// Exact fp32 re-rank of kc <= 128 candidates, ordered top-k, vote.  One CTA (4 warps) per query:
+// Exact fp32 re-rank of kc <= 128 candidates, ordered top-k, vote.  One CTA (8 warps) per query:
 // the four warps score the candidates, warp 0 then extracts the k best in (score, row) order and
 // votes.
 // Outputs: idx[nq,k], score[nq,k] in result order; counts[nq,n_classes]; label = first argmax
 // of counts (np.argmax semantics, chroma.py:128: ties -> left > right > none).
-__global__ void __launch_bounds__(128)
+constexpr int KNN_RERANK_THREADS = 256;
+__global__ void __launch_bounds__(KNN_RERANK_THREADS)
 knn_rerank_vote_kernel(const float* __restrict__ q, const float* __restrict__ bank,
                        const int32_t* __restrict__ labels, const int32_t* __restrict__ cand,
                        int nq, int m, int d, int kc, int k, int metric, int n_classes,
@@ -412,10 +413,10 @@ knn_rerank_vote_kernel(const float* __restrict__ q, const float* __restrict__ ba
   const int qi = blockIdx.x;
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (qi >= nq) return;
-  for (int i = threadIdx.x * 4; i < d; i += 128 * 4)
+  for (int i = threadIdx.x * 4; i < d; i += KNN_RERANK_THREADS * 4)
     *reinterpret_cast<float4*>(knn_q_smem + i) = *reinterpret_cast<const float4*>(q + (size_t)qi * d + i);
   __syncthreads();
-  knn_score_candidates<4>(knn_q_smem, bank, cand + (size_t)qi * kc, qi, m, d, kc, metric, row_mask, filt,
+  knn_score_candidates<KNN_RERANK_THREADS / 32>(knn_q_smem, bank, cand + (size_t)qi * kc, qi, m, d, kc, metric, row_mask, filt,
                           s_key, s_idx);
   __syncthreads();
   if (w != 0) return;

@@ -1736,7 +1736,7 @@ int knn_vote_impl(vitk_ctx* h, const float* q_dev, int n, int k, int metric, int
   }
   const int32_t* lab = h->bank_classes ? h->bank_labels : nullptr;
   if (kc <= KNN_MAX_CAND)
-    knn_rerank_vote_kernel<<<n, 128, (size_t)d * sizeof(float), st>>>(
+    knn_rerank_vote_kernel<<<n, KNN_RERANK_THREADS, (size_t)d * sizeof(float), st>>>(
         h->knn_q, h->bank, lab, h->knn_cand, n, m, d, kc, k, metric, h->bank_classes, idx_out,
         score_out, label_out, counts_out, row_mask_dev, filt);
   else
