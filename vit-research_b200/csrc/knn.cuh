@@ -237,13 +237,19 @@ knn_pool_select_kernel(uint2* __restrict__ pool, int* __restrict__ pool_n,
   }
   uint2* row = pool + (size_t)qi * CAP;
   uint32_t hi[KPL], lo[KPL];  // key bits | ~row; hi == 0 marks an empty slot
+  // every slot of the thread is requested first (slots past `count` hold stale entries of the same
+  // allocation and are ignored below): inside the `if (i < count)` the KPL loads went out one
+  // memory round trip after the other
+  uint2 ent[KPL];
+#pragma unroll
+  for (int j = 0; j < KPL; ++j) ent[j] = row[tid + THREADS * j];
 #pragma unroll
   for (int j = 0; j < KPL; ++j) {
     const int i = tid + THREADS * j;
     hi[j] = 0u;
     lo[j] = 0u;
     if (i < count) {
-      const uint2 e = row[i];
+      const uint2 e = ent[j];
       const bool excluded = (int)e.x >= ex_lo && (int)e.x < ex_hi;
       if (!excluded && e.y != 0u) { hi[j] = e.y; lo[j] = ~e.x; }
     }
