@@ -20,52 +20,65 @@ struct PatchifyParams {
 };
 
 // im2col for a stride==kernel convolution (HF modeling_vit.py:151,167): K index = (c, ky, kx).
-// One thread produces 8 consecutive kx of one (row, c, ky): one 16 B store.  One CTA per output
-// row: the (frame, patch) split is block-uniform 32-bit arithmetic instead of 64-bit divisions per
-// 16 bytes (the flat-index form spent more time dividing than moving data).
+// One thread produces 8 consecutive kx of one (row, c, ky): one 16 B store.  One CTA per
+// PATCHIFY_ROWS consecutive output rows: the (frame, patch) split is block-uniform 32-bit
+// arithmetic, the (c, ky, kx) split of a thread's K position is done once for all of its rows,
+// and the rows' loads are independent (the flat-index form spent more time in 64-bit divisions
+// than moving data; one row per CTA was still bound by index arithmetic).
+constexpr int PATCHIFY_ROWS = 4;   // <= tokens per frame (>= 5 for every supported geometry)
+__device__ __forceinline__ uint4 patchify_load8(const PatchifyParams& p, int f, int t, int c, int ky, int kx) {
+  uint4 o = make_uint4(0u, 0u, 0u, 0u);
+  if (t > 0) {
+    const int pidx = t - 1;
+    const int py = pidx / p.gw, px = pidx % p.gw;
+    const int y = py * p.ps + ky, x = px * p.ps + kx;
+    float v[8];
+    if (p.fmt == PIX_F32_NCHW) {
+      const float* s = reinterpret_cast<const float*>(p.pix) + (((size_t)f * p.C + c) * p.H + y) * p.W + x;
+      float4 a = *reinterpret_cast<const float4*>(s);
+      float4 b = *reinterpret_cast<const float4*>(s + 4);
+      o.x = pack_bf16x2(a.x, a.y); o.y = pack_bf16x2(a.z, a.w);
+      o.z = pack_bf16x2(b.x, b.y); o.w = pack_bf16x2(b.z, b.w);
+    } else if (p.fmt == PIX_BF16_NCHW) {
+      const __nv_bfloat16* s = reinterpret_cast<const __nv_bfloat16*>(p.pix) +
+                               (((size_t)f * p.C + c) * p.H + y) * p.W + x;
+      o = *reinterpret_cast<const uint4*>(s);
+    } else {
+      const uint8_t* s = reinterpret_cast<const uint8_t*>(p.pix) + (((size_t)f * p.H + y) * p.W + x) * p.C + c;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        // bit-identical to the HF processor's fused float32 rescale+normalise
+        // (transformers 5.5 image_processing_backends.py: tvF.normalize(x, 127.5, 127.5))
+        v[j] = __fdiv_rn(__fsub_rn((float)s[j * p.C], p.mean), p.std);
+      }
+      o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]);
+      o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
+    }
+  }
+  return o;
+}
 __global__ void __launch_bounds__(256) patchify_kernel(const PatchifyParams p) {
   const int kv_per_row = p.K >> 3;
   const int P1 = p.gh * p.gw + 1;
-  const long long row = blockIdx.x;
-  const int f = (int)(blockIdx.x / (unsigned)P1), t = (int)(blockIdx.x % (unsigned)P1);
+  const unsigned rows = (unsigned)p.n * (unsigned)P1;
+  const unsigned row0 = blockIdx.x * (unsigned)PATCHIFY_ROWS;
+  const int f0 = (int)(row0 / (unsigned)P1), t0 = (int)(row0 % (unsigned)P1);
+  const int pp = p.ps * p.ps;
   for (int kv = threadIdx.x; kv < kv_per_row; kv += blockDim.x) {
-    uint4 o = make_uint4(0u, 0u, 0u, 0u);
-    if (t > 0) {
-      const int pidx = t - 1;
-      const int py = pidx / p.gw, px = pidx % p.gw;
-      const int k0 = kv << 3;
-      const int pp = p.ps * p.ps;
-      const int c = k0 / pp, rem = k0 % pp;
-      const int ky = rem / p.ps, kx = rem % p.ps;
-      const int y = py * p.ps + ky, x = px * p.ps + kx;
-      float v[8];
-      if (p.fmt == PIX_F32_NCHW) {
-        const float* s = reinterpret_cast<const float*>(p.pix) +
-                         (((size_t)f * p.C + c) * p.H + y) * p.W + x;
-        float4 a = *reinterpret_cast<const float4*>(s);
-        float4 b = *reinterpret_cast<const float4*>(s + 4);
-        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
-        v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
-        o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]);
-        o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
-      } else if (p.fmt == PIX_BF16_NCHW) {
-        const __nv_bfloat16* s = reinterpret_cast<const __nv_bfloat16*>(p.pix) +
-                                 (((size_t)f * p.C + c) * p.H + y) * p.W + x;
-        o = *reinterpret_cast<const uint4*>(s);
-      } else {
-        const uint8_t* s = reinterpret_cast<const uint8_t*>(p.pix) +
-                           (((size_t)f * p.H + y) * p.W + x) * p.C + c;
+    const int k0 = kv << 3;
+    const int c = k0 / pp, rem = k0 % pp;
+    const int ky = rem / p.ps, kx = rem % p.ps;
+    uint4 o[PATCHIFY_ROWS];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          // bit-identical to the HF processor's fused float32 rescale+normalise
-          // (transformers 5.5 image_processing_backends.py: tvF.normalize(x, 127.5, 127.5))
-          v[j] = __fdiv_rn(__fsub_rn((float)s[j * p.C], p.mean), p.std);
-        }
-        o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]);
-        o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
-      }
+    for (int r = 0; r < PATCHIFY_ROWS; ++r) {
+      int t = t0 + r, f = f0;
+      if (t >= P1) { t -= P1; f += 1; }
+      o[r] = row0 + r < rows ? patchify_load8(p, f, t, c, ky, kx) : make_uint4(0u, 0u, 0u, 0u);
     }
-    *reinterpret_cast<uint4*>(p.out + row * p.K + ((size_t)kv << 3)) = o;
+#pragma unroll
+    for (int r = 0; r < PATCHIFY_ROWS; ++r)
+      if (row0 + r < rows)
+        *reinterpret_cast<uint4*>(p.out + (size_t)(row0 + r) * p.K + ((size_t)kv << 3)) = o[r];
   }
 }
 

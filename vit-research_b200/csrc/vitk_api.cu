@@ -421,11 +421,11 @@ int launch_patchify(Err& e, const void* pix, int fmt, __nv_bfloat16* out, int n,
   p.fmt = fmt;
   p.mean = u8_mean;  // default: HF ViTImageProcessor (rescale 1/255, mean .5, std .5, fused)
   p.std = u8_std;
-  const long long rows = (long long)n * (p.gh * p.gw + 1);   // one CTA per output row
+  const long long rows = (long long)n * (p.gh * p.gw + 1);   // one CTA per PATCHIFY_ROWS output rows
   if (rows > 0x7fffffffLL) { e.set("patchify: too many rows"); return 1; }
   const int kv_per_row = p.K / 8;
   const int threads = kv_per_row >= 256 ? 256 : ((kv_per_row + 31) / 32) * 32;
-  patchify_kernel<<<(unsigned)rows, threads, 0, st>>>(p);
+  patchify_kernel<<<(unsigned)((rows + PATCHIFY_ROWS - 1) / PATCHIFY_ROWS), threads, 0, st>>>(p);
   CK(e, cudaGetLastError());
   return 0;
 }
