@@ -335,11 +335,12 @@ __device__ __forceinline__ float2 att_exp2_pair(float2 x, int i) {
 // FADD2): 2.5 issue slots per element next to its one MUFU op — a single softmax warp per
 // scheduler is issue-limited, not MUFU-limited.  No exponent clamp: a row whose maximum lies far
 // above the shift overflows to +inf, the row sum becomes inf and the block is redone exactly.
-template <int NC>
+// FULL = 1: the caller knows that every column of the chunk is a valid key (no mask, no branch).
+template <int NC, int FULL = 0>
 __device__ __forceinline__ void att_exp_chunk(const uint32_t* v, int c0, int S, float scale, float mxs,
                                               float2 (&s2)[2], uint32_t t_slot) {
   uint32_t pk[NC / 2];
-  const bool full = c0 + NC <= S;
+  const bool full = FULL == 1 ? true : (c0 + NC <= S);
   const float2 sc2 = make_float2(scale, scale), nm2 = make_float2(-mxs, -mxs);
 #pragma unroll
   for (int i = 0; i < NC / 2; ++i) {
@@ -356,6 +357,7 @@ __device__ __forceinline__ void att_exp_chunk(const uint32_t* v, int c0, int S, 
   else tmem_st_32x32b_x8(t_slot + (c0 >> 1), *reinterpret_cast<const uint32_t(*)[8]>(pk));
 }
 
+template <int V> struct AttConst { static constexpr int value = V; };
 constexpr int ATT3_THREADS = 384;
 constexpr int ATT3_STAGES = 2;
 
@@ -705,23 +707,34 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         const float mxs = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])) * p.scale_log2e;
         float2 s4[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
         int c = 0;
-        for (; c + 2 <= n32; c += 2) {  // va holds chunk c
-          tmem_ld_32x32b_x32(t_slot + (c + 1) * 32, vb);
-          att_exp_chunk<32>(va, c * 32, S, p.scale_log2e, mxs, s4, t_slot);
-          if (c >= p.handover && !handed) {  // early hand-over: the other group's TMEM loads can run
-            handed = true;                   // under the rest of this pass's exp2 work
+        // two 32-column chunks: va holds chunk c_, vb receives c_ + 1, va is refilled with c_ + 2.
+        // kFull = 1: every column of both chunks is a valid key -- no mask and no branch in the exp2 code
+        auto pair = [&](int c_, auto full_tag) {
+          constexpr int kFull = decltype(full_tag)::value;
+          tmem_ld_32x32b_x32(t_slot + (c_ + 1) * 32, vb);
+          att_exp_chunk<32, kFull>(va, c_ * 32, S, p.scale_log2e, mxs, s4, t_slot);
+          if (c_ >= p.handover && !handed) {  // early hand-over: the other group's TMEM loads can run
+            handed = true;                    // under the rest of this pass's exp2 work
             __syncwarp();
             if (lane == 0) mbar_arrive(&turn_bar[g ^ 1]);
           }
           tmem_ld_wait();
           reg_fence16(vb);
           reg_fence16(vb + 16);
-          if (c + 2 < n32) tmem_ld_32x32b_x32(t_slot + (c + 2) * 32, va);
-          else if (tail) tmem_ld_32x32b_x16(t_slot + (c + 2) * 32, *reinterpret_cast<uint32_t(*)[16]>(va));
-          att_exp_chunk<32>(vb, (c + 1) * 32, S, p.scale_log2e, mxs, s4, t_slot);
+          if (c_ + 2 < n32) tmem_ld_32x32b_x32(t_slot + (c_ + 2) * 32, va);
+          else if (tail) tmem_ld_32x32b_x16(t_slot + (c_ + 2) * 32, *reinterpret_cast<uint32_t(*)[16]>(va));
+          att_exp_chunk<32, kFull>(vb, (c_ + 1) * 32, S, p.scale_log2e, mxs, s4, t_slot);
           tmem_ld_wait();
           reg_fence16(va);
           reg_fence16(va + 16);
+        };
+        if (SK == 208 && S > 192) {  // the ViT case, unrolled: chunks 0-5 hold valid keys only
+          pair(0, AttConst<1>{});
+          pair(2, AttConst<1>{});
+          pair(4, AttConst<1>{});
+          c = 6;
+        } else {
+          for (; c + 2 <= n32; c += 2) pair(c, AttConst<0>{});
         }
         if (c < n32) {  // odd number of 32-column chunks: va holds the last one
           if (tail) tmem_ld_32x32b_x16(t_slot + (c + 1) * 32, *reinterpret_cast<uint32_t(*)[16]>(vb));
