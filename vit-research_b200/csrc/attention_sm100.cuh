@@ -701,9 +701,14 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         if (n32 > 0) reg_fence16(va + 16);
         float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
         const int first = n32 > 0 ? 32 : 16;
+        if (SK == 208 && S > 192) {  // the ViT case: all 32 scores of the first chunk are valid keys
 #pragma unroll
-        for (int i = 0; i < 32; ++i)
-          if (i < first && i < S) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(va[i]));
+          for (int i = 0; i < 32; ++i) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(va[i]));
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (i < first && i < S) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(va[i]));
+        }
         const float mxs = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])) * p.scale_log2e;
         float2 s4[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
         int c = 0;
