@@ -58,6 +58,8 @@ __device__ __forceinline__ uint4 patchify_load8(const PatchifyParams& p, int f, 
   return o;
 }
 __global__ void __launch_bounds__(256) patchify_kernel(const PatchifyParams p) {
+  griddep_launch_dependents();
+  griddep_wait();   // the previous step's kernels may still read `out` (the activation buffer)
   const int kv_per_row = p.K >> 3;
   const int P1 = p.gh * p.gw + 1;
   const unsigned rows = (unsigned)p.n * (unsigned)P1;
@@ -163,6 +165,8 @@ cls_tail_kernel(const float* __restrict__ resid, const __nv_bfloat16* __restrict
                 const float* __restrict__ beta, float* __restrict__ out_f32,
                 __nv_bfloat16* __restrict__ out_bf16, int n, int tokens, float eps, int l2norm) {
   constexpr int D = 128 * VEC;
+  griddep_launch_dependents();
+  griddep_wait();
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (warp >= n) return;

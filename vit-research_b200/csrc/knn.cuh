@@ -27,6 +27,8 @@ constexpr int KNN_MAX_CLASSES = 8;
 __global__ void __launch_bounds__(256)
 prep_queries_kernel(const float* __restrict__ q, float* __restrict__ q_out,
                     __nv_bfloat16* __restrict__ q_bf16, int n, int d, int normalise) {
+  griddep_launch_dependents();
+  griddep_wait();
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (warp >= n) return;
@@ -111,6 +113,8 @@ __global__ void __launch_bounds__(128)
 knn_candidates_reg_kernel(const float* __restrict__ scores, int ld,
                           const float* __restrict__ bank_sqnorm, int nq, int m, int kc, int metric,
                           int32_t* __restrict__ cand, const float* __restrict__ pen, const KnnFilter filt) {
+  griddep_launch_dependents();
+  griddep_wait();
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (warp >= nq) return;
@@ -416,6 +420,8 @@ knn_rerank_vote_kernel(const float* __restrict__ q, const float* __restrict__ ba
   extern __shared__ float knn_q_smem[];  // [d] query row
   __shared__ float s_key[KNN_MAX_CAND];
   __shared__ int s_idx[KNN_MAX_CAND];
+  griddep_launch_dependents();
+  griddep_wait();
   const int qi = blockIdx.x;
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (qi >= nq) return;

@@ -14,6 +14,7 @@
 #include <mutex>
 #include <set>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/vitk.h"
@@ -155,6 +156,23 @@ bool pdl_enabled() {
   static int on = -1;
   if (on < 0) { const char* v = getenv("VITK_PDL"); on = (v && atoi(v) == 0) ? 0 : 1; }
   return on != 0;
+}
+
+// <<<grid, block, smem, st>>> with the programmatic-dependent-launch attribute (kernels that call
+// griddep_launch_dependents() / griddep_wait() at their top: the small kernels around the forward)
+template <typename... KArgs, typename... Args>
+cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
 }
 
 template <int BN, int EPI, int CG, bool S6 = false>
@@ -425,7 +443,7 @@ int launch_patchify(Err& e, const void* pix, int fmt, __nv_bfloat16* out, int n,
   if (rows > 0x7fffffffLL) { e.set("patchify: too many rows"); return 1; }
   const int kv_per_row = p.K / 8;
   const int threads = kv_per_row >= 256 ? 256 : ((kv_per_row + 31) / 32) * 32;
-  patchify_kernel<<<(unsigned)((rows + PATCHIFY_ROWS - 1) / PATCHIFY_ROWS), threads, 0, st>>>(p);
+  CK(e, launch_pdl(patchify_kernel, dim3((unsigned)((rows + PATCHIFY_ROWS - 1) / PATCHIFY_ROWS)), dim3(threads), 0, st, p));
   CK(e, cudaGetLastError());
   return 0;
 }
@@ -1191,11 +1209,11 @@ int forward_chunk(vitk_ctx* c, const void* pix, int fmt, int n, float* emb_f32,
   const float* rs_f32 = rf32 ? c->resid : nullptr;
   const __nv_bfloat16* rs_bf16 = rf32 ? nullptr : c->xb;
   if (D == 768)
-    cls_tail_kernel<6><<<blocks, 128, 0, st>>>(rs_f32, rs_bf16, c->lnf_g, c->lnf_b, emb_f32, emb_bf16, n,
-                                               c->S, cfg.ln_eps, l2norm);
+    CK(e, launch_pdl(cls_tail_kernel<6>, dim3(blocks), dim3(128), 0, st, rs_f32, rs_bf16, c->lnf_g, c->lnf_b, emb_f32,
+                     emb_bf16, n, c->S, cfg.ln_eps, l2norm));
   else
-    cls_tail_kernel<8><<<blocks, 128, 0, st>>>(rs_f32, rs_bf16, c->lnf_g, c->lnf_b, emb_f32, emb_bf16, n,
-                                               c->S, cfg.ln_eps, l2norm);
+    CK(e, launch_pdl(cls_tail_kernel<8>, dim3(blocks), dim3(128), 0, st, rs_f32, rs_bf16, c->lnf_g, c->lnf_b, emb_f32,
+                     emb_bf16, n, c->S, cfg.ln_eps, l2norm));
   CK(e, cudaGetLastError());
   c->launches += 1;
   return 0;
@@ -1689,8 +1707,8 @@ int knn_vote_impl(vitk_ctx* h, const float* q_dev, int n, int k, int metric, int
     h->knn_cap_m = cm;
     h->knn_cap_kc = ckc;
   }
-  prep_queries_kernel<<<(n + 7) / 8, 256, 0, st>>>(q_dev, h->knn_q, h->knn_qb, n, d,
-                                                   normalise_queries);
+  CK(e, launch_pdl(prep_queries_kernel, dim3((n + 7) / 8), dim3(256), 0, st, q_dev, h->knn_q, h->knn_qb, n, d,
+                   normalise_queries));
   CK(e, cudaGetLastError());
   h->launches += 1;
   const float* pen = nullptr;
@@ -1726,19 +1744,19 @@ int knn_vote_impl(vitk_ctx* h, const float* q_dev, int n, int k, int metric, int
     const float* sc = h->knn_scores;
     const float* sq = h->bank_sqnorm;
     int32_t* cd = h->knn_cand;
-    if (m <= 256) knn_candidates_reg_kernel<8><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd, pen, filt);
-    else if (m <= 512) knn_candidates_reg_kernel<16><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd, pen, filt);
-    else if (m <= 1024) knn_candidates_reg_kernel<32><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd, pen, filt);
-    else if (m <= 1536) knn_candidates_reg_kernel<48><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd, pen, filt);
-    else knn_candidates_reg_kernel<64><<<blocks, 128, 0, st>>>(sc, ld, sq, n, m, kc, metric, cd, pen, filt);
+    if (m <= 256) CK(e, launch_pdl(knn_candidates_reg_kernel<8>, dim3(blocks), dim3(128), 0, st, sc, ld, sq, n, m, kc, metric, cd, pen, filt));
+    else if (m <= 512) CK(e, launch_pdl(knn_candidates_reg_kernel<16>, dim3(blocks), dim3(128), 0, st, sc, ld, sq, n, m, kc, metric, cd, pen, filt));
+    else if (m <= 1024) CK(e, launch_pdl(knn_candidates_reg_kernel<32>, dim3(blocks), dim3(128), 0, st, sc, ld, sq, n, m, kc, metric, cd, pen, filt));
+    else if (m <= 1536) CK(e, launch_pdl(knn_candidates_reg_kernel<48>, dim3(blocks), dim3(128), 0, st, sc, ld, sq, n, m, kc, metric, cd, pen, filt));
+    else CK(e, launch_pdl(knn_candidates_reg_kernel<64>, dim3(blocks), dim3(128), 0, st, sc, ld, sq, n, m, kc, metric, cd, pen, filt));
     CK(e, cudaGetLastError());
     h->launches += 2;
   }
   const int32_t* lab = h->bank_classes ? h->bank_labels : nullptr;
   if (kc <= KNN_MAX_CAND)
-    knn_rerank_vote_kernel<<<n, KNN_RERANK_THREADS, (size_t)d * sizeof(float), st>>>(
-        h->knn_q, h->bank, lab, h->knn_cand, n, m, d, kc, k, metric, h->bank_classes, idx_out,
-        score_out, label_out, counts_out, row_mask_dev, filt);
+    CK(e, launch_pdl(knn_rerank_vote_kernel, dim3(n), dim3(KNN_RERANK_THREADS), (size_t)d * sizeof(float), st,
+                     h->knn_q, h->bank, lab, h->knn_cand, n, m, d, kc, k, metric, h->bank_classes, idx_out,
+                     score_out, label_out, counts_out, row_mask_dev, filt));
   else
     knn_rerank_sort_kernel<<<n, 256, (size_t)d * sizeof(float), st>>>(
         h->knn_q, h->bank, lab, h->knn_cand, n, m, d, kc, k, metric, h->bank_classes, idx_out,
