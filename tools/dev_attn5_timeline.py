@@ -1,5 +1,6 @@
 """Developer diagnostic: clock64 timeline of CTA 0 of the v5 attention kernel (VITK_ATTN=5):
-loader warp 4 and math warp 8, first 16 (unit, slot) items."""
+loader warp 4 and math warp 8, first 16 (unit, slot) items.
+Needs a developer build of the library: VITK_NVCC_EXTRA=-DVITK_ATT_TIMELINE=1 (the stamps are compiled out of production builds)."""
 import ctypes as C, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch

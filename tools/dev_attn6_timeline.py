@@ -1,4 +1,5 @@
-"""Developer diagnostic: clock64 timeline of CTA 0 of the v6 attention kernel (VITK_ATTN=6)."""
+"""Developer diagnostic: clock64 timeline of CTA 0 of the v6 attention kernel (VITK_ATTN=6).
+Needs a developer build of the library: VITK_NVCC_EXTRA=-DVITK_ATT_TIMELINE=1 (the stamps are compiled out of production builds)."""
 import ctypes as C, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch

@@ -1,4 +1,5 @@
-"""Developer diagnostic: per-phase clock64 timeline of CTA 0 of the attention kernel."""
+"""Developer diagnostic: per-phase clock64 timeline of CTA 0 of the attention kernel.
+Needs a developer build of the library: VITK_NVCC_EXTRA=-DVITK_ATT_TIMELINE=1 (the stamps are compiled out of production builds)."""
 import ctypes as C, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch

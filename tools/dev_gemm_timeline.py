@@ -1,5 +1,6 @@
 """Developer diagnostic: per-work-unit clock64 timeline of CTA 0 of the persistent GEMM (MMA thread,
-epilogue warps 4 and 8, TMA producer) at the four layer shapes."""
+epilogue warps 4 and 8, TMA producer) at the four layer shapes.
+Needs a developer build of the library: VITK_NVCC_EXTRA=-DVITK_GEMM_TIMELINE=1 (the stamps are compiled out of production builds)."""
 import ctypes as C, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch

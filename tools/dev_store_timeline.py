@@ -1,5 +1,6 @@
 """Developer diagnostic: per-unit timeline (CTA 0) of the LAST threshold-filter GEMM stage of a
-1 M-row store search (the stage that walks 83 % of the rows)."""
+1 M-row store search (the stage that walks 83 % of the rows).
+Needs a developer build of the library: VITK_NVCC_EXTRA=-DVITK_GEMM_TIMELINE=1 (the stamps are compiled out of production builds)."""
 import ctypes as C, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np

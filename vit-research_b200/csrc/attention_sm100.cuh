@@ -309,6 +309,10 @@ __device__ __forceinline__ void reg_fence16(uint32_t* r) {
 // exact redo.  The softmax pass is MUFU-bound (one ex2 per score, 8 cycles per warp instruction); the
 // pairs selected by VITK_ATT_POLY_MASK (bit i%16 of the pair index inside a chunk) take this route
 // instead, so that the MUFU and the FMA pipe share the exponentials (cf. FlashAttention-4's software exp2).
+// 1: clock64 stamps for tools/dev_attn*_timeline.py are compiled in (developer builds: VITK_NVCC_EXTRA=-DVITK_ATT_TIMELINE=1)
+#ifndef VITK_ATT_TIMELINE
+#define VITK_ATT_TIMELINE 0
+#endif
 #ifndef VITK_ATT_POLY_MASK
 #define VITK_ATT_POLY_MASK 0u
 #endif
@@ -444,7 +448,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         // cycles later: the next-but-one unit's Q / K load -- 58 KB that take 2 200-3 300 cycles to
         // land and sit on the critical path of the next S = Q K^T -- starts that much earlier
         mbar_wait(&qk_empty[st], ph ^ 1u);
-        if (p.dbg != nullptr && blockIdx.x == 0 && j < 16) p.dbg[(2 * 16 + j) * 8 + 0] = clock64();
+        if ((VITK_ATT_TIMELINE && p.dbg != nullptr) && blockIdx.x == 0 && j < 16) p.dbg[(2 * 16 + j) * 8 + 0] = clock64();
         mbar_arrive_expect_tx(&kv_full[st], 16384 * nblk + SK * 128);
         tma_load_3d(sb, &tmQ, &kv_full[st], head * ATT_D, 0, frame);
         if (nblk == 2) tma_load_3d(sb + 16384, &tmQ, &kv_full[st], head * ATT_D, 128, frame);
@@ -478,7 +482,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           const uint32_t sph = (j >> 1) & 1, uph = j & 1;
           const int b = s ^ (j & 1);  // query block this slot holds in unit j
           uint8_t* sb = smem + st * L.stage_bytes;
-          const bool ldbg = p.dbg != nullptr && blockIdx.x == 0 && j < 16 && lane == 0;
+          const bool ldbg = (VITK_ATT_TIMELINE && p.dbg != nullptr) && blockIdx.x == 0 && j < 16 && lane == 0;
           mbar_wait(&kv_full[st], sph);
           if (ldbg) p.dbg[(2 * 16 + j) * 8 + 1 + s] = clock64();
           mbar_wait(&slot_free[s], uph ^ 1u);
@@ -498,7 +502,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           mbar_wait(&p_full[s], uph);
           mbar_wait(&v_full[st], sph);
           tc_fence_after_sync();
-          const bool mdbg = p.dbg != nullptr && blockIdx.x == 0 && j < 16 && lane == 0;
+          const bool mdbg = (VITK_ATT_TIMELINE && p.dbg != nullptr) && blockIdx.x == 0 && j < 16 && lane == 0;
           if (mdbg) p.dbg[(s * 16 + j) * 8 + 6] = clock64();
           if (elect_one_sync()) {
             if (b < nblk) {
@@ -545,7 +549,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           } else {
             if (!mbar_test_wait(&p_full[s], uph) || !mbar_test_wait(&v_full[st], sph)) continue;
             tc_fence_after_sync();
-            const bool mdbg = p.dbg != nullptr && blockIdx.x == 0 && j < 16;
+            const bool mdbg = (VITK_ATT_TIMELINE && p.dbg != nullptr) && blockIdx.x == 0 && j < 16;
             if (mdbg) p.dbg[(s * 16 + j) * 8 + 6] = clock64();
             if (b < nblk) {
               const uint32_t sv = smem_u32(sb + 32768 + L.kv_bytes);
@@ -593,7 +597,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       const bool warp_active = wq * 32 < rows_valid;
       uint8_t* sO = smem + L.off_o + g * 16384;  // this warpgroup's private output staging
 
-      const bool dbg_on = p.dbg != nullptr && blockIdx.x == 0 && wq == 0 && lane == 0 && j < 16;
+      const bool dbg_on = (VITK_ATT_TIMELINE && p.dbg != nullptr) && blockIdx.x == 0 && wq == 0 && lane == 0 && j < 16;
       long long* dbg = p.dbg + (g * 16 + j) * 8;
       if (dbg_on) dbg[0] = clock64();
       mbar_wait(&s_full[g], uph);
@@ -1090,7 +1094,7 @@ attention_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         const bool warp_active = wq * 32 < rows_valid;
         const uint32_t t_slot = tmem_base + s * 256 + lane_off;
         const int item = 2 * j + s;
-        const bool dbg_on = p.dbg != nullptr && blockIdx.x == 0 && wq == 0 && lane == 0 && item < 16;
+        const bool dbg_on = (VITK_ATT_TIMELINE && p.dbg != nullptr) && blockIdx.x == 0 && wq == 0 && lane == 0 && item < 16;
         long long* dbg = p.dbg + (0 * 16 + item) * 8;
         if (dbg_on) dbg[0] = clock64();
         mbar_wait(&s_full[s], uph);
@@ -1153,7 +1157,7 @@ attention_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         const bool warp_active = wq * 32 < rows_valid;
         const uint32_t t_slot = tmem_base + s * 256 + lane_off;
         const int item = 2 * j + s;
-        const bool dbg_on = p.dbg != nullptr && blockIdx.x == 0 && wq == 0 && lane == 0 && item < 16;
+        const bool dbg_on = (VITK_ATT_TIMELINE && p.dbg != nullptr) && blockIdx.x == 0 && wq == 0 && lane == 0 && item < 16;
         long long* dbg = p.dbg + (1 * 16 + item) * 8;
         if (dbg_on) dbg[0] = clock64();
         mbar_wait(&s_full[s], uph);
@@ -1502,7 +1506,7 @@ attention_smemp_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
       uint8_t* sb = smem + st * L.stage_bytes;
       uint8_t* sO = sb + b * 16384;   // this block's Q tile: dead once S = Q K^T (and any redo) is done
 
-      const bool dbg_on = p.dbg != nullptr && blockIdx.x == 0 && wq == 0 && lane == 0 && j < 16;
+      const bool dbg_on = (VITK_ATT_TIMELINE && p.dbg != nullptr) && blockIdx.x == 0 && wq == 0 && lane == 0 && j < 16;
       long long* dbg = p.dbg + (g * 16 + j) * 8;
       if (dbg_on) dbg[0] = clock64();
       mbar_wait(&s_full[g], uph);

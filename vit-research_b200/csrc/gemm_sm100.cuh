@@ -115,6 +115,11 @@ constexpr int GEMM_EPI_WARPS = 8;
 // with: as warps 0 / 1 they lost every arbitration against a busy epilogue and the mainloop slowed
 // down with the epilogue's instruction count (tools/dev_gemm_timeline.py).  -DVITK_GEMM_ISSUE_LOW=1
 // restores the round-1 numbering for A/B runs.
+// 1: clock64 stamps for tools/dev_gemm_timeline.py / dev_store_timeline.py are compiled in
+// (developer builds: VITK_NVCC_EXTRA=-DVITK_GEMM_TIMELINE=1)
+#ifndef VITK_GEMM_TIMELINE
+#define VITK_GEMM_TIMELINE 0
+#endif
 #ifndef VITK_GEMM_EPI_STUB
 #define VITK_GEMM_EPI_STUB 0   // developer probes of the bf16-output epilogue (tools/dev_gemm_timeline.py)
 #endif
@@ -261,7 +266,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       int ti = 0;
       for (int tile = first_unit; tile < num_tiles; tile += unit_stride, ++ti) {
         const int m_blk = m_unit_of(tile) * CG + (int)rank, n_blk = tile % n_tiles;
-        if (p.dbg != nullptr && blockIdx.x == 0 && ti < 40 && lane == 0) p.dbg[ti * 8 + 7] = clock64();
+        if ((VITK_GEMM_TIMELINE && p.dbg != nullptr) && blockIdx.x == 0 && ti < 40 && lane == 0) p.dbg[ti * 8 + 7] = clock64();
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1u);
           uint8_t* a_dst = sA + stage * Cfg::kABytes;
@@ -300,7 +305,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       int acc = 0;
       uint32_t acc_phase = 0;
       int ti = 0;
-      const bool dbg0 = p.dbg != nullptr && blockIdx.x == 0 && lane == 0;
+      const bool dbg0 = (VITK_GEMM_TIMELINE && p.dbg != nullptr) && blockIdx.x == 0 && lane == 0;
       if (dbg0) { p.dbg[320] = clock64(); p.dbg[321] = (long long)global_timer_ns(); }
       for (int tile = first_unit; tile < num_tiles; tile += unit_stride, ++ti) {
         const bool mdbg = dbg0 && ti < 40;
@@ -396,7 +401,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     int ti = 0;
     for (int tile = first_unit; tile < num_tiles; tile += unit_stride, ++ti) {
       const int m_blk = m_unit_of(tile) * CG + (int)rank, n_blk = tile % n_tiles;
-      const bool edbg = p.dbg != nullptr && blockIdx.x == 0 && lane == 0 && ti < 40;
+      const bool edbg = (VITK_GEMM_TIMELINE && p.dbg != nullptr) && blockIdx.x == 0 && lane == 0 && ti < 40;
       const int row0 = m_blk * GEMM_BM + q * 32;
       const int row = row0 + lane;
       if constexpr (EpiTraits<EPI>::kUsesVec) {
