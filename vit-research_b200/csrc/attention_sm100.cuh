@@ -313,8 +313,12 @@ __device__ __forceinline__ void reg_fence16(uint32_t* r) {
 #ifndef VITK_ATT_TIMELINE
 #define VITK_ATT_TIMELINE 0
 #endif
+// Default 0x8420: pairs 5, 10 and 15 of every 16 (19 % of the scores).  Measured on the final kernel
+// (147 registers): none 70.2 us, 0x8000 69.3, 0x8080 67.5, 0x8420 67.1, 0x8888 68.6, 0x4924 70.8, 0xaaaa 77.0
+// (profiles/r02_attn_handover.txt); on the round-1 / mid-round kernels, which sat at the register limit,
+// every mask was slower.  -DVITK_ATT_POLY_MASK=0u restores the all-MUFU form.
 #ifndef VITK_ATT_POLY_MASK
-#define VITK_ATT_POLY_MASK 0u
+#define VITK_ATT_POLY_MASK 0x8420u
 #endif
 __device__ __forceinline__ float2 exp2_poly2(float2 x) {
   const float2 xc = make_float2(fminf(fmaxf(x.x, -126.0f), 127.9f), fminf(fmaxf(x.y, -126.0f), 127.9f));
