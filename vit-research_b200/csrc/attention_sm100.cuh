@@ -61,6 +61,7 @@ struct AttnParams {
   int nblk;     // query blocks per (frame, head): 1 if q_rows <= 128 else 2
   int reverse;  // v3: walk the (frame, head) units from the last to the first ("snake" order)
   int one_issuer; // v3: 1 = both TMEM slots' MMAs issued by one polling thread (round-1 form)
+  int early_pv; // v3, S padded to 208 keys: P.V of the keys 96-191 issued in the middle of the softmax pass
   int handover; // v3: 32-column chunk of the softmax pass after which the exp2 turn passes to the
                 // other warpgroup (>= number of chunks: at the end of the pass)
   float scale_log2e;  // (1/sqrt(d)) * log2(e)
@@ -344,9 +345,10 @@ __device__ __forceinline__ float2 att_exp2_pair(float2 x, int i) {
 // scheduler is issue-limited, not MUFU-limited.  No exponent clamp: a row whose maximum lies far
 // above the shift overflows to +inf, the row sum becomes inf and the block is redone exactly.
 // FULL = 1: the caller knows that every column of the chunk is a valid key (no mask, no branch).
+// p_col >= 0 overrides the destination column of the packed probabilities.
 template <int NC, int FULL = 0>
 __device__ __forceinline__ void att_exp_chunk(const uint32_t* v, int c0, int S, float scale, float mxs,
-                                              float2 (&s2)[2], uint32_t t_slot) {
+                                              float2 (&s2)[2], uint32_t t_slot, int p_col = -1) {
   uint32_t pk[NC / 2];
   const bool full = FULL == 1 ? true : (c0 + NC <= S);
   const float2 sc2 = make_float2(scale, scale), nm2 = make_float2(-mxs, -mxs);
@@ -361,8 +363,9 @@ __device__ __forceinline__ void att_exp_chunk(const uint32_t* v, int c0, int S, 
     s2[i & 1] = __fadd2_rn(s2[i & 1], e);
     pk[i] = pack_bf16x2(e.x, e.y);
   }
-  if constexpr (NC == 32) tmem_st_32x32b_x16(t_slot + (c0 >> 1), *reinterpret_cast<const uint32_t(*)[16]>(pk));
-  else tmem_st_32x32b_x8(t_slot + (c0 >> 1), *reinterpret_cast<const uint32_t(*)[8]>(pk));
+  const uint32_t dst = t_slot + static_cast<uint32_t>(p_col >= 0 ? p_col : (c0 >> 1));
+  if constexpr (NC == 32) tmem_st_32x32b_x16(dst, *reinterpret_cast<const uint32_t(*)[16]>(pk));
+  else tmem_st_32x32b_x8(dst, *reinterpret_cast<const uint32_t(*)[8]>(pk));
 }
 
 template <int V> struct AttConst { static constexpr int value = V; };
@@ -383,6 +386,11 @@ __host__ __device__ inline Attn3SmemLayout attn3_smem_layout(int S) {
   return L;
 }
 
+// EARLY = true: the instantiation for 193-208 keys (the ViT case) whose softmax pass takes the chunks
+// in the order 3, 4, 5 | 0, 1, 2, tail and lets the MMA warp start O = P V in the middle of it; it
+// contains ONLY that pass (both passes in one kernel push ptxas over the register budget and the
+// spills cost more than the early start wins).  EARLY = false: any S <= 256.
+template <bool EARLY>
 __global__ void __launch_bounds__(ATT3_THREADS, 1)
 attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
                  const __grid_constant__ CUtensorMap tmO, const AttnParams p) {
@@ -402,6 +410,9 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   uint64_t* redo_bar = bars + 14;    // [2] slot: exact-path recomputation of S
   uint64_t* turn_bar = bars + 16;    // [2] group: "your turn on the exp2 units", count 4
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 18);
+  uint64_t* p_half = bars + 22;      // [2] slot, count 4: P of keys 96-191 written, S columns 96-191 read (early P.V)
+  uint64_t* epv_done = bars + 24;    // [2] slot: the early P.V instructions have been issued
+  volatile int* redo_flag = reinterpret_cast<volatile int*>(bars + 26);  // [2] slot: this unit took the exact path
   uint64_t* qk_empty = bars + 20;    // [2] stage, count 2: Q / K of the stage are dead (both blocks' passes done)
 
   const int tid = threadIdx.x;
@@ -421,6 +432,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       mbar_init(&v_full[i], 1);
       mbar_init(&stage_empty[i], 2);
       mbar_init(&qk_empty[i], 2);
+      mbar_init(&p_half[i], 4);
+      mbar_init(&epv_done[i], 1);
       mbar_init(&s_full[i], 1);
       mbar_init(&p_full[i], 4);
       mbar_init(&o_full[i], 1);
@@ -503,11 +516,43 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
             umma_commit(&s_full[s]);
           }
           __syncwarp();
+          constexpr bool early = EARLY;
+          if (early) {
+            // keys 96-191 (k-steps 6-11): their probabilities sit in the slot's spare columns
+            // 208-255 and the S columns under the O accumulator (104-167) have been read by all
+            // four warps, so these six instructions run under the rest of the softmax pass
+            mbar_wait(&p_half[s], uph);
+            mbar_wait(&v_full[st], sph);
+            tc_fence_after_sync();
+            if (elect_one_sync()) {
+              if (b < nblk) {
+                const uint64_t dv0 = make_smem_desc_sw128(smem_u32(sb + 32768 + L.kv_bytes), 1024, 1024);
+#pragma unroll
+                for (int kk = 6; kk < 12; ++kk)
+                  umma_bf16_ts(t_slot + 104, t_slot + 208 + (kk - 6) * 8, dv0 + (uint64_t)(kk * 128), idesc_o,
+                               kk != 6 ? 1u : 0u);
+              }
+              mbar_arrive(&epv_done[s]);
+            }
+            __syncwarp();
+          }
           mbar_wait(&p_full[s], uph);
           mbar_wait(&v_full[st], sph);
           tc_fence_after_sync();
           const bool mdbg = (VITK_ATT_TIMELINE && p.dbg != nullptr) && blockIdx.x == 0 && j < 16 && lane == 0;
           if (mdbg) p.dbg[(s * 16 + j) * 8 + 6] = clock64();
+          if (early && redo_flag[s] == 0) {
+            if (elect_one_sync()) {
+              if (b < nblk) {
+                const uint64_t dv0 = make_smem_desc_sw128(smem_u32(sb + 32768 + L.kv_bytes), 1024, 1024);
+#pragma unroll
+                for (int kk = 0; kk < 6; ++kk)
+                  umma_bf16_ts(t_slot + 104, t_slot + kk * 8, dv0 + (uint64_t)(kk * 128), idesc_o, 1u);
+                umma_bf16_ts(t_slot + 104, t_slot + 96, dv0 + (uint64_t)(12 * 128), idesc_o, 1u);
+              }
+              umma_commit(&o_full[s]);
+            }
+          } else
           if (elect_one_sync()) {
             if (b < nblk) {
               const uint32_t sv = smem_u32(sb + 32768 + L.kv_bytes);
@@ -694,7 +739,74 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       // ~100 binades or more above m0 (never observed on real activations) overflows towards
       // +inf and shows up as a huge / non-finite sum ...
       bool redo = false;
-      if (warp_active) {
+      constexpr bool early = EARLY;
+      if constexpr (EARLY) {
+        // 197 keys padded to 208, the ViT case.  The 32-key chunks are taken in the order
+        // 3, 4, 5 | 0, 1, 2, tail: chunks 3-5 are the S columns that lie under the O accumulator
+        // (104-167), and their probabilities go to the slot's spare columns 208-255 instead of
+        // over S.  After them the MMA warp starts O = P V with those six k-steps while this warp
+        // is still in the exp2 loop of the other chunks.
+        if (warp_active) {
+          uint32_t va[32], vb[32];
+          auto ld32 = [&](uint32_t (&dst)[32], int col) { tmem_ld_32x32b_x32(t_slot + col, dst); };
+          auto landed = [&](uint32_t (&dst)[32]) { tmem_ld_wait(); reg_fence16(dst); reg_fence16(dst + 16); };
+          ld32(va, 96);
+          landed(va);
+          float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+          for (int i = 0; i < 32; ++i) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(va[i]));
+          const float mxs = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])) * p.scale_log2e;
+          float2 s4[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
+          // the exp2 turn passes on after the fifth chunk (p.handover <= 4) or at the end of the pass
+          auto maybe_hand_over = [&]() {};
+          auto hand_over_now = [&]() {
+            if (p.handover <= 4 && !handed) {
+              handed = true;
+              __syncwarp();
+              if (lane == 0) mbar_arrive(&turn_bar[g ^ 1]);
+            }
+          };
+          ld32(vb, 128);
+          att_exp_chunk<32, 1>(va, 96, S, p.scale_log2e, mxs, s4, t_slot, 208);
+          maybe_hand_over();
+          landed(vb);
+          ld32(va, 160);
+          att_exp_chunk<32, 1>(vb, 128, S, p.scale_log2e, mxs, s4, t_slot, 224);
+          maybe_hand_over();
+          landed(va);
+          ld32(vb, 0);
+          att_exp_chunk<32, 1>(va, 160, S, p.scale_log2e, mxs, s4, t_slot, 240);
+          maybe_hand_over();
+          // columns 96-191 of S are consumed and their P is on its way to TMEM
+          tmem_st_wait();
+          tc_fence_before_sync();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&p_half[g]);
+          landed(vb);
+          ld32(va, 32);
+          att_exp_chunk<32, 1>(vb, 0, S, p.scale_log2e, mxs, s4, t_slot);
+          maybe_hand_over();
+          landed(va);
+          ld32(vb, 64);
+          att_exp_chunk<32, 1>(va, 32, S, p.scale_log2e, mxs, s4, t_slot);
+          hand_over_now();
+          landed(vb);
+          tmem_ld_32x32b_x16(t_slot + 192, *reinterpret_cast<uint32_t(*)[16]>(va));
+          att_exp_chunk<32, 1>(vb, 64, S, p.scale_log2e, mxs, s4, t_slot);
+          maybe_hand_over();
+          tmem_ld_wait();
+          reg_fence16(va);
+          att_exp_chunk<16>(va, 192, S, p.scale_log2e, mxs, s4, t_slot);
+          tmem_st_wait();
+          sum = (s4[0].x + s4[0].y) + (s4[1].x + s4[1].y);
+          redo = !(sum < 1.0e30f);
+        } else {
+          tc_fence_before_sync();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&p_half[g]);
+        }
+      } else
+      if (!EARLY && warp_active) {
         // Software-pipelined: the tcgen05.ld of chunk c+1 is in flight while chunk c goes
         // through the exp2 loop (two register buffers), and the first chunk serves both the
         // shift estimate and the first exp2 pass — with two softmax warps per scheduler the
@@ -766,8 +878,13 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       // ... in which case the whole query block takes the EXACT PATH: S = Q K^T is recomputed
       // into the slot (P has overwritten it) and the classic max pass + exp pass run.
       tc_fence_before_sync();
-      if (named_bar_or(2 + g, 128, redo)) {
+      const bool took_redo = named_bar_or(2 + g, 128, redo);
+      if (early && wq == 0 && lane == 0) redo_flag[g] = took_redo ? 1 : 0;  // read by the MMA warp after p_full
+      if (took_redo) {
         if (wq == 0 && lane == 0 && blk_active) {
+          // the early P.V instructions write O over S columns 104-167: they must be in the tensor
+          // pipe BEFORE S is recomputed (they then run first and the recomputed S overwrites them)
+          if (early) mbar_wait(&epv_done[g], uph);
           tc_fence_after_sync();
           uint8_t* sb = smem + st * L.stage_bytes;
           const uint32_t idesc_s = make_idesc_bf16_f32(128, (uint32_t)SK, false, false);

@@ -310,9 +310,13 @@ int launch_attention(Err& e, const CUtensorMap& tq, const CUtensorMap& tkv, cons
                                // 1000 = at the end of the pass, the round-1 behaviour)
     if (handover < 0) { const char* hv = getenv("VITK_ATTN_HANDOVER"); handover = hv ? atoi(hv) : 4; if (handover < 0) handover = 0; }
     p.handover = handover;
+    static int early_pv = -1;  // VITK_ATTN_EARLY_PV=0: all thirteen P.V instructions after the softmax pass (the in-order pass)
+    if (early_pv < 0) { const char* ev = getenv("VITK_ATTN_EARLY_PV"); early_pv = (ev && atoi(ev) == 0) ? 0 : 1; }
+    p.early_pv = early_pv;
     static int one_issuer = -1;  // VITK_ATTN_ISSUER=1: the round-1 single MMA-issuing thread
     if (one_issuer < 0) { const char* iv = getenv("VITK_ATTN_ISSUER"); one_issuer = (iv && atoi(iv) == 1) ? 1 : 0; }
     p.one_issuer = one_issuer;
+    if (one_issuer) p.early_pv = 0;
   }
   p.scale_log2e = 0.125f * 1.4426950408889634f;  // head dim 64 -> 1/sqrt(64)
   p.dbg = g_attn_dbg;
@@ -362,8 +366,8 @@ int launch_attention(Err& e, const CUtensorMap& tq, const CUtensorMap& tkv, cons
     const Attn3SmemLayout L = attn3_smem_layout(S);
     static int attr_bytes3 = 0;
     if (L.total > attr_bytes3) {
-      CK(e, cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 L.total));
+      CK(e, cudaFuncSetAttribute(attention_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total));
+      CK(e, cudaFuncSetAttribute(attention_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total));
       attr_bytes3 = L.total;
     }
     const int units = frames * heads;
@@ -378,7 +382,8 @@ int launch_attention(Err& e, const CUtensorMap& tq, const CUtensorMap& tkv, cons
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl_enabled() ? 1 : 0;
-    CK(e, cudaLaunchKernelEx(&cfg, attention_kernel, tq, tkv, to, p));
+    if (p.early_pv && L.sk == 208) CK(e, cudaLaunchKernelEx(&cfg, attention_kernel<true>, tq, tkv, to, p));
+    else CK(e, cudaLaunchKernelEx(&cfg, attention_kernel<false>, tq, tkv, to, p));
   }
   CK(e, cudaGetLastError());
   return 0;
